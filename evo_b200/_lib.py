@@ -1,0 +1,98 @@
+"""ctypes binding of libevo_b200.so (the C-ABI declared in include/evo_b200.h).
+
+There is no CPU fallback: if the shared library is missing or a call fails this module raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libevo_b200.so")
+
+SEL = {"fit": 0, "rand": 1}
+MUT = {"randflip": 0, "sparseflip": 1, "cross": 2, "cross_randflip": 3, "cross_sparseflip": 4}
+EVAL_BSC_GRAM, EVAL_BSC_DIRECT, EVAL_ES3C = 0, 1, 2
+
+
+class EvoError(RuntimeError):
+    pass
+
+
+class EstepArgs(C.Structure):
+    """Mirror of `evo_estep_args` (include/evo_b200.h)."""
+
+    _fields_ = [
+        ("N", C.c_int64), ("n_offset", C.c_int64),
+        ("D", C.c_int32), ("H", C.c_int32), ("S", C.c_int32), ("S_perm", C.c_int32), ("Mprime", C.c_int32),
+        ("n_parents", C.c_int32), ("n_children", C.c_int32), ("n_generations", C.c_int32),
+        ("selection", C.c_int32), ("mutation", C.c_int32), ("background", C.c_int32),
+        ("bitflip_prob", C.c_double), ("sparseness", C.c_double),
+        ("seed", C.c_uint64), ("iteration", C.c_uint32), ("eval", C.c_int32),
+        ("states", C.c_void_p), ("lpj", C.c_void_p),
+        ("inj_children", C.c_void_p), ("inj_count", C.c_void_p), ("inj_cmax", C.c_int32), ("_pad0", C.c_int32),
+        ("W", C.c_void_p), ("Y", C.c_void_p), ("mask", C.c_void_p),
+        ("G", C.c_void_p), ("B", C.c_void_p), ("ynorm2", C.c_void_p),
+        ("pre1", C.c_double), ("pil_bar", C.c_double),
+        ("pil_bar_h", C.c_void_p), ("mus", C.c_void_p), ("Psi", C.c_void_p),
+        ("sigma2", C.c_double),
+        ("acc", C.c_void_p),
+    ]
+
+
+_vp, _i, _i64, _d, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_uint64
+
+SIGNATURES = {
+    "evo_last_error": (C.c_char_p, []),
+    "evo_version": (_i, []),
+    "evo_device_sm_count": (_i, []),
+    "evo_states_pack": (_i, [_vp, _vp, _i64, _i, _vp]),
+    "evo_states_unpack": (_i, [_vp, _vp, _i64, _i, _vp]),
+    "evo_states_init": (_i, [_vp, _i64, _i, _i, _i, _i, _d, _u64, _i64, _vp]),
+    "evo_bsc_prepare": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp, _vp, _vp]),
+    "evo_bsc_lpj": (_i, [_i, _vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _d, _d, _vp, _i64, _vp, _vp]),
+    "evo_estep": (_i, [C.POINTER(EstepArgs), _vp]),
+    "evo_select_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp]),
+    "evo_free_energy": (_i, [_vp, _i64, _i, _i64, _vp, _vp]),
+    "evo_bsc_suffstats": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp]),
+    "evo_bsc_reconstruct": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Load the shared library once; raise loudly if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise EvoError(
+            "evo_b200: %s is missing -- build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback)" % LIB_PATH
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().evo_last_error()
+        raise EvoError("%s failed (%d): %s" % (what, rc, msg.decode() if msg else "?"))
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (or None)."""
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "evo_b200 kernels need contiguous CUDA tensors"
+    return C.c_void_p(t.data_ptr())
+
+
+def stream():
+    import torch
+
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

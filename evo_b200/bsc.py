@@ -1,0 +1,263 @@
+"""Binary Sparse Coding on the GPU -- drop-in for the reference's `BSC` (evo/models/bsc.py:14-287).
+
+E-step: `evo_bsc_prepare` (G = W'W, B = Y W) then the fused `evo_estep` kernel; complete data uses
+the sparse quadratic form, incomplete data the masked residual.  M-step: `evo_bsc_suffstats`, one
+all-reduce of the packed statistics, replicated solve.
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from .model import ACC_LEN, Model, _dev
+
+
+class BSC(Model):
+    def __init__(self, D, H, S, to_learn=("W", "pi", "sigma"), comm=None, device=None):
+        Model.__init__(self, D, H, S, to_learn, comm, device)
+        self.eps_lpj = np.finfo(np.float64).min  # bsc.py:23-24
+
+    # ---- generative model (bsc.py:27-57), cold path ---------------------------------------------
+    def generate_from_hidden(self, model_params, my_hdata):
+        W = np.asarray(model_params["W"].cpu() if isinstance(model_params["W"], torch.Tensor) else model_params["W"])
+        sigma = float(model_params["sigma"])
+        s = np.asarray(my_hdata["s"])
+        my_N = s.shape[0]
+        D = W.shape[0]
+        y_mean = s.astype(np.float64) @ W.T
+        y = y_mean + np.random.normal(scale=sigma, size=(my_N, D))
+        return {"y": y, "s": s, "y_mean": y_mean}
+
+    # ---- standard_init (_models.py:206-283): data mean + noise, pi = 1/H, sigma = data std -----
+    def standard_init(self, my_data, W_init=None, pi_init=None, sigma_init=None):
+        dd = self.device_data(my_data)
+        D, H = self.D, self.H
+        Y = dd.Y.double()
+        if not dd.incomplete:
+            tot = torch.cat([Y.sum(0), (Y * Y).sum(0)])
+            self.comm.allreduce_(tot)
+            y_mean = tot[:D] / dd.N_total
+            var = tot[D:] / dd.N_total - y_mean * y_mean
+            sig = float(torch.sqrt(var.clamp_min(0).sum() / D).item())
+        else:
+            m = dd.mask.double()
+            tot = torch.cat([(Y * m).sum(0), m.sum(0)])
+            self.comm.allreduce_(tot)
+            y_mean = tot[:D] / tot[D:].clamp_min(1.0)
+            r = (((Y - y_mean) * m) ** 2).sum().reshape(1)
+            self.comm.allreduce_(r)
+            sig = float(torch.sqrt(r / dd.n_obs_total).item())
+        if sigma_init is None:
+            sigma_init = sig
+            assert sigma_init > 0.0
+        y_mean = y_mean.cpu().numpy()
+        if not isinstance(W_init, np.ndarray):
+            if W_init == "random_uniform":
+                W_init = self.comm.bcast(np.random.random((D, H)))
+            elif W_init == "normal":
+                W_init = self.comm.bcast(np.random.normal(0, 5, [D, H]))
+            elif W_init == "data_mean":
+                W_init = np.tile(y_mean[:, None], (1, H))
+            else:
+                noise = self.comm.bcast(np.random.normal(scale=sigma_init / 4.0, size=[D, H]))
+                W_init = y_mean[:, None] + noise
+        if pi_init is None:
+            pi_init = 1.0 / H
+        return {"W": W_init, "pi": pi_init, "sigma": sigma_init}
+
+    # ---- state-independent terms (bsc.py:100-125) ---------------------------------------------------
+    def E_step_precompute(self, model_params, my_suff_stat, my_data):
+        dd = self.device_data(my_data)
+        D, H = self.D, self.H
+        pi, sigma = float(model_params["pi"]), float(model_params["sigma"])
+        model_params["piH"] = pi * H
+        model_params["pre1"] = -1.0 / 2.0 / sigma / sigma
+        model_params["pil_bar"] = float(np.log(pi / (1.0 - pi)))
+        if dd.incomplete:
+            model_params["ljc"] = float(H * np.log(1.0 - pi)
+                                        - np.log(2 * np.pi * sigma * sigma) * dd.n_obs_total / dd.N_total / 2)
+        else:
+            model_params["ljc"] = float(H * np.log(1.0 - pi) - D / 2 * np.log(2 * np.pi * sigma * sigma))
+        for k in ("reset_lpj_isnan", "reset_lpj_smaller_eps_lpj", "reset_lpj_isinf"):
+            dict.__setitem__(my_suff_stat, k, 0)
+
+    def _tables(self, model_params, dd):
+        """W on the device; for complete data also G = W'W and B = Y W (|y|^2 once per dataset)."""
+        Wd = _dev(model_params["W"], self.device, torch.float64)
+        c = dd.cache
+        c["W"] = Wd
+        if dd.incomplete:
+            return
+        H = self.H
+        if "G" not in c:
+            c["G"] = torch.empty((H, H), dtype=torch.float64, device=self.device)
+            c["B"] = torch.empty((dd.N, H), dtype=torch.float64, device=self.device)
+        yn = None
+        if "ynorm2" not in c:
+            c["ynorm2"] = torch.empty((dd.N,), dtype=torch.float64, device=self.device)
+            yn = c["ynorm2"]
+        self._call("evo_bsc_prepare", _lib.ptr(Wd), _lib.ptr(dd.Y), dd.N, self.D, H, _lib.ptr(c["G"]), _lib.ptr(c["B"]),
+                   _lib.ptr(yn))
+
+    def _fill_eval(self, a, model_params, dd):
+        c = dd.cache
+        a.pre1, a.pil_bar = float(model_params["pre1"]), float(model_params["pil_bar"])
+        a.sparseness = float(model_params["piH"])
+        a.W, a.Y = c["W"].data_ptr(), dd.Y.data_ptr()
+        if dd.incomplete:
+            a.eval = _lib.EVAL_BSC_DIRECT
+            a.mask = dd.mask.data_ptr()
+        else:
+            a.eval = _lib.EVAL_BSC_GRAM
+            a.G, a.B, a.ynorm2 = c["G"].data_ptr(), c["B"].data_ptr(), c["ynorm2"].data_ptr()
+        return None
+
+    # ---- E-step (_models.py:454-565) -----------------------------------------------------------------
+    def E_step(self, model_params, my_suff_stat, my_data):
+        dd = self.device_data(my_data)
+        self.E_step_precompute(model_params, my_suff_stat, my_data)
+        self._tables(model_params, dd)
+        acc = torch.zeros(ACC_LEN, dtype=torch.float64, device=self.device)
+        self._estep_launch(my_suff_stat, dd, acc, lambda a: self._fill_eval(a, model_params, dd))
+        dd.cache["acc"] = acc
+        red = acc.clone()
+        self.comm.allreduce_(red)
+        r = red.cpu().numpy()
+        for i, k in enumerate(("reset_lpj_isnan", "reset_lpj_smaller_eps_lpj", "reset_lpj_isinf")):
+            dict.__setitem__(my_suff_stat, k, int(r[3 + i]))
+        self.last_counts = {"lpj_evaluated": float(r[6])}
+        F = model_params["ljc"] + r[0] / dd.N_total
+        return float(F), float(r[1] / dd.N_total), float(r[2] / dd.N_total)
+
+    # ---- stand-alone lpj with the reference's per-datapoint signature (bsc.py:60-97) -----------------
+    def log_pseudo_joint(self, model_params, my_suff_stat, my_data):
+        states = np.asarray(my_suff_stat["this_states"], dtype=bool)
+        y = np.asarray(my_data["this_y"], dtype=np.float64)[None]
+        x = np.asarray(my_data["this_x_infr"], dtype=bool)[None]
+        from .variational import pack_states
+
+        st = pack_states(states[None], self.device)
+        Wd = _dev(model_params["W"], self.device, torch.float64)
+        Yd = _dev(np.where(x, y, 0.0), self.device, torch.float32)
+        md = _dev(x, self.device, torch.uint8)
+        out = torch.empty((1, states.shape[0]), dtype=torch.float64, device=self.device)
+        cnt = torch.zeros(3, dtype=torch.int64, device=self.device)
+        self._call("evo_bsc_lpj", _lib.EVAL_BSC_DIRECT, _lib.ptr(st), 0, 1, states.shape[0], self.D, self.H, _lib.ptr(Wd),
+                   _lib.ptr(Yd), _lib.ptr(md), None, None, None, float(model_params["pre1"]),
+                   float(model_params["pil_bar"]), _lib.ptr(out), states.shape[0], _lib.ptr(cnt))
+        c = cnt.cpu().numpy()
+        for i, k in enumerate(("reset_lpj_isnan", "reset_lpj_smaller_eps_lpj", "reset_lpj_isinf")):
+            if k in my_suff_stat:
+                dict.__setitem__(my_suff_stat, k, my_suff_stat[k] + int(c[i]))
+        return out[0].cpu().numpy()
+
+    def log_pseudo_joint_permanent_states(self, model_params, my_suff_stat, my_data):
+        y = np.asarray(my_data["this_y"], dtype=np.float64)
+        x = np.asarray(my_data["this_x_infr"], dtype=bool)
+        saved = my_suff_stat["this_states"] if "this_states" in my_suff_stat else None
+        dict.__setitem__(my_suff_stat, "this_states", np.zeros((1, self.H), dtype=bool))
+        out = self.log_pseudo_joint(model_params, my_suff_stat, {"this_y": y, "this_x_infr": x})
+        if saved is not None:
+            dict.__setitem__(my_suff_stat, "this_states", saved)
+        return out
+
+    def lpj_all(self, model_params, my_data, states_dev, shared=False):
+        """lpj of `states_dev` ([N][S'][Hw], or one [S'][Hw] table for every datapoint) under
+        `model_params`; batched form of log_pseudo_joint used by free_energy."""
+        dd = self.device_data(my_data)
+        self._tables(model_params, dd)
+        c = dd.cache
+        Sp = states_dev.shape[-2]
+        out = torch.empty((dd.N, Sp), dtype=torch.float64, device=self.device)
+        ev = _lib.EVAL_BSC_DIRECT if dd.incomplete else _lib.EVAL_BSC_GRAM
+        self._call("evo_bsc_lpj", ev, _lib.ptr(states_dev), int(shared), dd.N, Sp, self.D, self.H, _lib.ptr(c["W"]),
+                   _lib.ptr(dd.Y), _lib.ptr(dd.mask), _lib.ptr(c.get("G")), _lib.ptr(c.get("B")),
+                   _lib.ptr(c.get("ynorm2")), float(model_params["pre1"]), float(model_params["pil_bar"]),
+                   _lib.ptr(out), Sp, None)
+        return out
+
+    def free_energy(self, my_data, model_params, my_suff_stat, full=True, compute_lpj=True):
+        """Free energy over the current K sets, or the exact log-likelihood over all 2^H states
+        (`full=True`, H < 12) (_models.py:334-451)."""
+        from .variational import pack_states
+
+        dd = self.device_data(my_data)
+        self.E_step_precompute(model_params, my_suff_stat, my_data)
+        if full:
+            sm = my_suff_stat["sm"]
+            assert sm is not None, "full free energy needs the table of all states (H < 12)"
+            tab = pack_states(sm, self.device)  # includes the all-zero row: same value as the permanent state
+            lpj = self.lpj_all(model_params, my_data, tab, shared=True)
+        elif compute_lpj:
+            lpj = self.lpj_all(model_params, my_data, my_suff_stat["ss_dev"])
+            if my_suff_stat["S_perm"] > 0:
+                z = torch.zeros((1, my_suff_stat["ss_dev"].shape[-1]), dtype=torch.int32, device=self.device)
+                lpj = torch.cat([self.lpj_all(model_params, my_data, z, shared=True), lpj], dim=1).contiguous()
+        else:
+            lpj = my_suff_stat["lpj_dev"]
+        Fs = self._sum_logsumexp(lpj)
+        self.comm.allreduce_(Fs)
+        return float(model_params["ljc"] + Fs.item() / dd.N_total)
+
+    # ---- estimator (_models.py:614-665, bsc.py:279-287) --------------------------------------------------
+    def reconstruct(self, my_data, my_suff_stat, model_params):
+        dd = self.device_data(my_data)
+        Wd = _dev(model_params["W"], self.device, torch.float64)
+        if dd.Yrec is None:
+            dd.Yrec = torch.empty_like(dd.Y)
+        ss = my_suff_stat
+        self._call("evo_bsc_reconstruct", _lib.ptr(ss["ss_dev"]), _lib.ptr(ss["lpj_dev"]), _lib.ptr(Wd), _lib.ptr(dd.Y),
+                   _lib.ptr(dd.keep), _lib.ptr(dd.mask), dd.N, self.D, self.H, int(ss["ss_dev"].shape[1]),
+                   int(ss["S_perm"]), _lib.ptr(dd.Yrec))
+        my_data["y_reconstructed_dev"] = dd.Yrec
+        if not isinstance(my_data["y"], torch.Tensor):
+            my_data["y_reconstructed"] = dd.Yrec.double().cpu().numpy()
+
+    # ---- M-step (bsc.py:128-277) ------------------------------------------------------------------------
+    def M_step(self, model_params, my_suff_stat, my_data):
+        dd = self.device_data(my_data)
+        D, H = self.D, self.H
+        ss = my_suff_stat
+        if dd.incomplete:
+            assert dd.Yrec is not None, "missing data: call reconstruct() before the M-step (bsc.py:186)"
+            Ym = dd.Yrec
+        else:
+            Ym = dd.Y
+        stats = torch.zeros(H * D + H * H + H + 1, dtype=torch.float64, device=self.device)
+        self._call("evo_bsc_suffstats", _lib.ptr(ss["ss_dev"]), _lib.ptr(ss["lpj_dev"]), _lib.ptr(Ym), dd.N, D, H,
+                   int(ss["ss_dev"].shape[1]), int(ss["S_perm"]), int(bool(ss["permanent"]["allzero"])),
+                   float(model_params["pre1"]), float(model_params["pil_bar"]), _lib.ptr(stats), None)
+        self.comm.allreduce_(stats)
+        Wp = stats[: H * D].view(H, D)
+        Wq = stats[H * D: H * D + H * H].view(H, H)
+        Wq = torch.tril(Wq) + torch.tril(Wq, -1).T
+        pies = stats[H * D + H * H: H * D + H * H + H]
+        N = dd.N_total
+        as_numpy = not isinstance(model_params["W"], torch.Tensor)
+        sigma_old = float(model_params["sigma"])
+        if "W" in self.to_learn:
+            Wn = self._solve(Wq, Wp)  # (H, D) = lstsq(Wq, Wp)
+            model_params["W"] = Wn.T.contiguous().cpu().numpy() if as_numpy else Wn.T.contiguous()
+        if "pi" in self.to_learn:
+            p = pies / N
+            if ss["permanent"]["background"]:
+                p[-1] = 1.0 - 1.1e-5
+            model_params["pi"] = float((p.sum() / H).item())
+            model_params["pies"] = p.cpu().numpy() if as_numpy else p
+        if "sigma" in self.to_learn:
+            sig = float(stats[-1].item())
+            if dd.incomplete:
+                model_params["sigma"] = float(np.sqrt((sig + dd.n_obs_total * sigma_old ** 2) / N / D))
+            else:
+                model_params["sigma"] = float(np.sqrt(sig / N / D))
+        return model_params
+
+    def _solve(self, Wq, Wp):
+        """lstsq(Wq, Wp) (bsc.py:232-237).  Wq is symmetric PSD: Cholesky on the device when it is
+        positive definite, otherwise the reference's minimum-norm lstsq (rcond=-1) on the host."""
+        L, info = torch.linalg.cholesky_ex(Wq)
+        if int(info.item()) == 0:
+            sol = torch.cholesky_solve(Wp, L)
+            if bool(torch.isfinite(sol).all().item()):
+                return sol
+        sol = np.linalg.lstsq(Wq.cpu().numpy(), Wp.cpu().numpy(), rcond=-1)[0]
+        return torch.as_tensor(sol, device=self.device)

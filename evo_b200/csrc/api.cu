@@ -1,0 +1,241 @@
+// C-ABI glue: error reporting, E-step launcher, stand-alone top-K replacement.
+#include <stdarg.h>
+
+#include "common.cuh"
+#include "estep.cuh"
+#include "es3c.cuh"
+
+namespace evo {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+int check_cuda(cudaError_t e, const char *what) {
+  if (e == cudaSuccess) return EVO_OK;
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return EVO_ERR_CUDA;
+}
+int sm_count() {
+  static int cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+// ------------------------------------------------------------------------------------------
+// vary_Kn alone (evo/variational/utils.py:231-337).  One CTA per datapoint; new candidates that
+// equal a permanent state, a member of K^n or an earlier candidate are dropped; ties between
+// equal lpj are broken lexicographically (latent 0 most significant), which is the order the
+// reference's np.unique + stable sort produce.
+// ------------------------------------------------------------------------------------------
+template <int T>
+__global__ void __launch_bounds__(T) select_topk_kernel(uint32_t *__restrict__ states, double *__restrict__ lpj,
+                                                        int64_t N, int S, int S_perm, int Hw, int Mprime,
+                                                        const uint32_t *__restrict__ new_states,
+                                                        const double *__restrict__ lpj_new,
+                                                        const int32_t *__restrict__ n_new, int U,
+                                                        int32_t *__restrict__ out_counts) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ double red_d[8];
+  __shared__ int red_i[8];
+  unsigned char *dead = smem_raw;       // [U] 1 = duplicate / taken
+  unsigned char *taken_old = dead + U;  // [S]
+  for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
+    __syncthreads();
+    uint32_t *old = states + n * (int64_t)S * Hw;
+    double *lrow = lpj + n * (int64_t)(S + S_perm) + S_perm;
+    const uint32_t *nw = new_states + n * (int64_t)U * Hw;
+    const double *lnew = lpj_new + n * (int64_t)U;
+    int un = n_new ? n_new[n] : U;
+    int uniq = 0;
+    for (int i = threadIdx.x; i < S; i += T) taken_old[i] = 0;
+    for (int i = threadIdx.x; i < un; i += T) {
+      const uint32_t *si = nw + (int64_t)i * Hw;
+      bool dup = (S_perm > 0 && popc_state(si, Hw) == 0);
+      for (int k = 0; k < S && !dup; ++k) dup = same_state(old + (int64_t)k * Hw, si, Hw);
+      for (int j = 0; j < i && !dup; ++j) dup = same_state(nw + (int64_t)j * Hw, si, Hw);
+      dead[i] = dup;
+      uniq += !dup;
+    }
+    uniq = group_sum_i<T>(uniq, red_i);
+    __syncthreads();
+    int Mp = uniq < Mprime ? uniq : Mprime;
+    int n_sub = 0;
+    for (int j = 0; j < Mp; ++j) {
+      // best remaining new (ties: lexicographically smaller state first)
+      KeyIdx bn; bn.key = 0; bn.idx = -1;
+      for (int i = threadIdx.x; i < un; i += T) {
+        if (dead[i]) continue;
+        double v = lnew[i];
+        if (bn.idx < 0 || v > bn.key ||
+            (v == bn.key && lex_less(nw + (int64_t)i * Hw, nw + (int64_t)bn.idx * Hw, Hw))) { bn.key = v; bn.idx = i; }
+      }
+      // group reduction with the same tie rule
+      for (int o = 16; o > 0; o >>= 1) {
+        KeyIdx ot; ot.key = __shfl_xor_sync(0xffffffffu, bn.key, o); ot.idx = __shfl_xor_sync(0xffffffffu, bn.idx, o);
+        if (ot.idx >= 0 && (bn.idx < 0 || ot.key > bn.key ||
+                            (ot.key == bn.key && ot.idx != bn.idx &&
+                             lex_less(nw + (int64_t)ot.idx * Hw, nw + (int64_t)bn.idx * Hw, Hw)))) bn = ot;
+      }
+      if (T > 32) {
+        __shared__ double sk[T / 32];
+        __shared__ int si[T / 32];
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) { sk[threadIdx.x >> 5] = bn.key; si[threadIdx.x >> 5] = bn.idx; }
+        __syncthreads();
+        bn.key = sk[0]; bn.idx = si[0];
+        for (int w = 1; w < T / 32; ++w) {
+          if (si[w] >= 0 && (bn.idx < 0 || sk[w] > bn.key ||
+                             (sk[w] == bn.key && lex_less(nw + (int64_t)si[w] * Hw, nw + (int64_t)bn.idx * Hw, Hw)))) {
+            bn.key = sk[w]; bn.idx = si[w];
+          }
+        }
+      }
+      KeyIdx wo; wo.key = 0; wo.idx = -1;
+      for (int i = threadIdx.x; i < S; i += T)
+        if (!taken_old[i]) { KeyIdx c; c.key = -lrow[i]; c.idx = i; wo = better(wo, c); }
+      wo = group_argmax<T>(wo, red_d, red_i);
+      if (bn.idx < 0 || wo.idx < 0 || !(bn.key > -wo.key)) break;
+      __syncthreads();
+      for (int w = threadIdx.x; w < Hw; w += T) old[(int64_t)wo.idx * Hw + w] = nw[(int64_t)bn.idx * Hw + w];
+      if (threadIdx.x == 0) { lrow[wo.idx] = bn.key; taken_old[wo.idx] = 1; dead[bn.idx] = 1; }
+      ++n_sub;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0 && out_counts) { out_counts[2 * n] = uniq; out_counts[2 * n + 1] = n_sub; }
+  }
+}
+
+template <class Eval>
+static int launch_estep(const EstepDev &dv, Eval ev, cudaStream_t st) {
+  size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes();
+  int work = dv.S > dv.Cg ? dv.S : dv.Cg;
+  int T = ev.threads_hint(work);
+#define EVO_LAUNCH_T(TT)                                                                              \
+  {                                                                                                   \
+    auto k = estep_kernel<Eval, TT>;                                                                  \
+    if (smem > 48 * 1024)                                                                             \
+      EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
+    int per_sm = 1;                                                                                   \
+    EVO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, TT, smem));                    \
+    if (per_sm < 1) {                                                                                 \
+      set_error("evo_estep: %zu bytes of shared memory per datapoint exceed the SM", smem);           \
+      return EVO_ERR_UNSUPPORTED;                                                                     \
+    }                                                                                                 \
+    int64_t g = (int64_t)sm_count() * per_sm;                                                         \
+    if (g > dv.N) g = dv.N;                                                                           \
+    k<<<(int)g, TT, smem, st>>>(dv, ev);                                                              \
+  }
+  if (smem > 227 * 1024) {
+    set_error("evo_estep: %zu bytes of shared memory per datapoint exceed 227 KB", smem);
+    return EVO_ERR_UNSUPPORTED;
+  }
+  if (T <= 32) EVO_LAUNCH_T(32)
+  else if (T <= 64) EVO_LAUNCH_T(64)
+  else EVO_LAUNCH_T(128)
+#undef EVO_LAUNCH_T
+  EVO_LAUNCH_CHECK("estep");
+  return EVO_OK;
+}
+
+}  // namespace evo
+
+using namespace evo;
+
+extern "C" const char *evo_last_error(void) { return g_err; }
+extern "C" int evo_version(void) { return 100; }
+extern "C" int evo_device_sm_count(void) { return sm_count(); }
+
+extern "C" int evo_estep(const evo_estep_args *x, void *stream) {
+  EVO_REQUIRE(x != nullptr, "null args");
+  EVO_REQUIRE(x->N >= 0 && x->H > 0 && x->S > 0 && x->D > 0, "bad sizes");
+  EVO_REQUIRE(x->S_perm == 0 || x->S_perm == 1, "S_perm must be 0 or 1 (only the all-zero state is implemented)");
+  EVO_REQUIRE(!(x->background && x->S_perm), "background unit and permanent all-zero state are exclusive");
+  EVO_REQUIRE(x->n_generations >= 0 && x->n_generations < 256, "bad n_generations");
+  EVO_REQUIRE(x->states && x->lpj, "states/lpj null");
+  EVO_REQUIRE(x->selection == EVO_SEL_FIT || x->selection == EVO_SEL_RAND, "bad selection");
+  EVO_REQUIRE(x->mutation >= EVO_MUT_RANDFLIP && x->mutation <= EVO_MUT_CROSS_SPARSEFLIP, "bad mutation");
+  if (x->N == 0) return EVO_OK;
+  EstepDev dv;
+  memset(&dv, 0, sizeof(dv));
+  dv.N = x->N; dv.n_offset = x->n_offset;
+  dv.D = x->D; dv.H = x->H; dv.Hw = words_for(x->H); dv.S = x->S; dv.S_perm = x->S_perm;
+  dv.Mprime = x->Mprime > 0 ? x->Mprime : x->S;
+  dv.n_parents = x->n_parents; dv.n_children = x->n_children; dv.n_generations = x->n_generations;
+  dv.selection = x->selection; dv.mutation = x->mutation; dv.background = x->background;
+  dv.p_bf = x->bitflip_prob; dv.sparseness = x->sparseness;
+  dv.seed = x->seed; dv.iteration = x->iteration;
+  dv.states = x->states; dv.lpj = x->lpj;
+  dv.inj_children = x->inj_children; dv.inj_count = x->inj_count; dv.inj_cmax = x->inj_cmax;
+  dv.acc = x->acc;
+  int P = x->n_parents < x->S ? x->n_parents : x->S;
+  int Cg;
+  if (x->inj_children) {
+    EVO_REQUIRE(x->inj_count && x->inj_cmax > 0, "injected children need counts and a capacity");
+    Cg = x->inj_cmax;
+  } else {
+    EVO_REQUIRE(x->n_generations == 0 || x->n_parents >= 1, "n_parents must be >= 1");
+    if (x->mutation == EVO_MUT_RANDFLIP || x->mutation == EVO_MUT_SPARSEFLIP) {
+      EVO_REQUIRE(x->n_generations == 0 || x->n_children >= 1, "n_children must be >= 1");
+      Cg = P * x->n_children;
+    } else {
+      Cg = P * (P - 1);
+    }
+    if (x->mutation == EVO_MUT_SPARSEFLIP || x->mutation == EVO_MUT_CROSS_SPARSEFLIP)
+      EVO_REQUIRE(x->bitflip_prob > 0.0, "Please specify the bitflip probability");  // eas.py:68
+  }
+  if (Cg < 1) Cg = 1;
+  dv.Cg = Cg;
+  dv.Ctot = Cg * (x->n_generations > 0 ? x->n_generations : 1);
+  int need = 2 * (dv.S + dv.Ctot);
+  int HT = 64;
+  while (HT < need) HT <<= 1;
+  dv.HT = HT;
+  dv.PK = dv.S > Cg ? dv.S : Cg;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (x->eval == EVO_EVAL_BSC_GRAM) {
+    EVO_REQUIRE(x->G && x->B && x->ynorm2, "gram evaluator needs G, B, ynorm2");
+    EVO_REQUIRE(x->mask == nullptr, "gram evaluator needs complete data");
+    BscGramEval ev{x->G, x->B, x->ynorm2, x->pre1, x->pil_bar, dv.H, dv.Hw, nullptr, 0.0};
+    return launch_estep(dv, ev, st);
+  } else if (x->eval == EVO_EVAL_BSC_DIRECT) {
+    EVO_REQUIRE(x->W && x->Y, "direct evaluator needs W, Y");
+    BscDirectEval ev{x->W, x->Y, x->mask, x->pre1, x->pil_bar, dv.D, dv.H, dv.Hw, nullptr, nullptr, 0.0};
+    return launch_estep(dv, ev, st);
+  } else if (x->eval == EVO_EVAL_ES3C) {
+    return es3c_launch_estep(dv, x, st);
+  }
+  set_error("evo_estep: unknown evaluator %d", x->eval);
+  return EVO_ERR_ARG;
+}
+
+extern "C" int evo_select_topk(uint32_t *states, double *lpj, int64_t N, int S, int S_perm, int H, int Mprime,
+                               const uint32_t *new_states, const double *lpj_new, const int32_t *n_new, int U,
+                               int32_t *out_counts, void *stream) {
+  EVO_REQUIRE(N >= 0 && S > 0 && H > 0 && U >= 0, "bad sizes");
+  if (N == 0 || U == 0) {
+    if (out_counts && N > 0) EVO_CUDA(cudaMemsetAsync(out_counts, 0, sizeof(int32_t) * 2 * N, (cudaStream_t)stream));
+    return EVO_OK;
+  }
+  int Hw = words_for(H);
+  size_t smem = (size_t)U + S + 16;
+  constexpr int T = 64;
+  auto k = select_topk_kernel<T>;
+  if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t g = (int64_t)sm_count() * 8;
+  if (g > N) g = N;
+  k<<<(int)g, T, smem, (cudaStream_t)stream>>>(states, lpj, N, S, S_perm, Hw, Mprime > 0 ? Mprime : S, new_states,
+                                               lpj_new, n_new, U, out_counts);
+  EVO_LAUNCH_CHECK("select_topk");
+  return EVO_OK;
+}

@@ -1,0 +1,434 @@
+// Binary Sparse Coding kernels: Gram tables, stand-alone log-joint, M-step sufficient statistics,
+// data estimator.  Reference: evo/models/bsc.py, evo/models/_models.py.
+#include "common.cuh"
+#include "evaluators.cuh"
+
+namespace evo {
+
+// ------------------------------------------------------------------------------------------
+// G = W'W  (H,H) f64.  W is (D,H) row-major.  32x32 output tile per CTA, 16x16 threads x 2x2.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gram_kernel(const double *__restrict__ W, double *__restrict__ G, int D, int H) {
+  __shared__ double sa[16][33], sb[16][33];
+  int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  if (c0 > r0) return;  // lower triangle of tiles, mirrored on store
+  double acc[2][2] = {{0, 0}, {0, 0}};
+  for (int d0 = 0; d0 < D; d0 += 16) {
+    for (int i = threadIdx.x; i < 16 * 32; i += 256) {
+      int dd = i >> 5, c = i & 31;
+      int d = d0 + dd;
+      sa[dd][c] = (d < D && r0 + c < H) ? W[(int64_t)d * H + r0 + c] : 0.0;
+      sb[dd][c] = (d < D && c0 + c < H) ? W[(int64_t)d * H + c0 + c] : 0.0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int dd = 0; dd < 16; ++dd) {
+      double a0 = sa[dd][ty], a1 = sa[dd][ty + 16], b0 = sb[dd][tx], b1 = sb[dd][tx + 16];
+      acc[0][0] += a0 * b0; acc[0][1] += a0 * b1; acc[1][0] += a1 * b0; acc[1][1] += a1 * b1;
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      int r = r0 + ty + 16 * i, c = c0 + tx + 16 * j;
+      if (r < H && c < H) {
+        G[(int64_t)r * H + c] = acc[i][j];
+        G[(int64_t)c * H + r] = acc[i][j];
+      }
+    }
+}
+
+// ynorm2[n] = |y_n|^2 in f64, one warp per row
+__global__ void ynorm_kernel(const float *__restrict__ Y, double *__restrict__ out, int64_t N, int D) {
+  int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  int lane = threadIdx.x & 31;
+  int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t n = warp; n < N; n += nwarps) {
+    double s = 0.0;
+    for (int d = lane; d < D; d += 32) { double v = (double)Y[n * D + d]; s += v * v; }
+    s = warp_sum(s);
+    if (lane == 0) out[n] = s;
+  }
+}
+
+// B = Y W : (N,D) f32 x (D,H) f64 -> (N,H) f64.  64x64 tile per CTA, 256 threads x 4x4, f64 FMA.
+__global__ void __launch_bounds__(256) wty_kernel(const float *__restrict__ Y, const double *__restrict__ W,
+                                                  double *__restrict__ B, int64_t N, int D, int H) {
+  __shared__ double sy[16][65];   // [k][row]
+  __shared__ double sw[16][65];   // [k][col]
+  int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  int64_t ntr = (N + 63) / 64;
+  int ntc = (H + 63) / 64;
+  for (int64_t tile = blockIdx.x; tile < ntr * ntc; tile += gridDim.x) {
+    int64_t r0 = (tile / ntc) * 64;
+    int c0 = (int)(tile % ntc) * 64;
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+    for (int d0 = 0; d0 < D; d0 += 16) {
+      __syncthreads();
+      for (int i = threadIdx.x; i < 64 * 16; i += 256) {
+        int rr = i >> 4, kk = i & 15;  // Y row-major: consecutive threads along d
+        int64_t r = r0 + rr;
+        int d = d0 + kk;
+        sy[kk][rr] = (r < N && d < D) ? (double)Y[r * D + d] : 0.0;
+      }
+      for (int i = threadIdx.x; i < 16 * 64; i += 256) {
+        int kk = i >> 6, cc = i & 63;
+        int d = d0 + kk;
+        sw[kk][cc] = (d < D && c0 + cc < H) ? W[(int64_t)d * H + c0 + cc] : 0.0;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < 16; ++kk) {
+        double a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = sy[kk][ty + 16 * i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = sw[kk][tx + 16 * j];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int64_t r = r0 + ty + 16 * i;
+        int c = c0 + tx + 16 * j;
+        if (r < N && c < H) B[r * H + c] = acc[i][j];
+      }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// stand-alone lpj (BSC.log_pseudo_joint bsc.py:79-97 + lpj_reset_check _models.py:567-596)
+// ------------------------------------------------------------------------------------------
+template <class Eval, int T>
+__global__ void __launch_bounds__(T) lpj_kernel(Eval ev, const uint32_t *__restrict__ states, int shared_states,
+                                                int64_t N, int Sp, int Hw, double *__restrict__ out, int64_t ld,
+                                                unsigned long long *counters) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int red_i[8];
+  unsigned long long c_nan = 0, c_small = 0, c_inf = 0;
+  for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
+    __syncthreads();
+    ev.template setup<T>(n, smem_raw);
+    __syncthreads();
+    unsigned fl = 0;
+    const uint32_t *st = shared_states ? states : states + n * (int64_t)Sp * Hw;
+    ev.template eval_batch<T>(st, Sp, out + n * ld, fl);
+    fl = group_or<T>(fl, red_i);
+    if (threadIdx.x == 0 && fl) { if (fl & 1) ++c_nan; else if (fl & 2) ++c_small; else ++c_inf; }
+  }
+  if (threadIdx.x == 0 && counters) {
+    if (c_nan) atomicAdd(counters + 0, c_nan);
+    if (c_small) atomicAdd(counters + 1, c_small);
+    if (c_inf) atomicAdd(counters + 2, c_inf);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// posterior weights of one datapoint into shared memory: q[k] = exp(lpj_k - max) / sum over all
+// S + S_perm columns (bsc.py:176-177,219).  Returns nothing; q has S + S_perm entries.
+// ------------------------------------------------------------------------------------------
+template <int T>
+__device__ void posterior(const double *__restrict__ row, int cols, double *q, double *red_d) {
+  double mx = -DBL_MAX;
+  for (int i = threadIdx.x; i < cols; i += T) { double v = row[i]; q[i] = v; mx = fmax(mx, v); }
+  mx = group_max<T>(mx, red_d);
+  double se = 0.0;
+  for (int i = threadIdx.x; i < cols; i += T) { double e = exp(q[i] - mx); q[i] = e; se += e; }
+  se = group_sum<T>(se, red_d);
+  double inv = 1.0 / se;
+  for (int i = threadIdx.x; i < cols; i += T) q[i] *= inv;
+  __syncthreads();
+}
+
+constexpr double Q_SKIP = 1e-18;  // posterior mass below f64 resolution of the sums it would enter
+
+// ------------------------------------------------------------------------------------------
+// BSC M-step statistics (bsc.py:193-223).  One CTA per datapoint (persistent loop):
+//   es_h = sum_k q_k s_kh                (smem, f64)
+//   pies += es ; Wp[h,:] += es_h y_n ; Wq[h,h'] += sum_k q_k s_kh s_kh' (h' <= h) ;
+//   sigma += sum_k q_k |y - W s_k|^2 = sum_k q_k (lpj_k - pil_bar |s_k|) / pre1   (same theta)
+// ------------------------------------------------------------------------------------------
+template <int T>
+__global__ void __launch_bounds__(T) bsc_suffstats_kernel(const uint32_t *__restrict__ states,
+                                                          const double *__restrict__ lpj,
+                                                          const float *__restrict__ Ym, int64_t N, int D, int H, int Hw,
+                                                          int S, int S_perm, double pre1, double pil_bar,
+                                                          double *__restrict__ stats, float *__restrict__ Es_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ double red_d[8];
+  __shared__ int red_i[8];
+  __shared__ int n_act;
+  double *es = reinterpret_cast<double *>(smem_raw);          // [H]
+  double *q = es + H;                                          // [S + S_perm]
+  float *y = reinterpret_cast<float *>(q + S + S_perm);        // [D]
+  int *act = reinterpret_cast<int *>(y + D);                   // [H]
+  double *Wp = stats, *Wq = stats + (int64_t)H * D, *pies = Wq + (int64_t)H * H, *sig = pies + H;
+  double sig_acc = 0.0;
+  const int cols = S + S_perm;
+  for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
+    __syncthreads();
+    for (int h = threadIdx.x; h < H; h += T) es[h] = 0.0;
+    for (int d = threadIdx.x; d < D; d += T) y[d] = Ym[n * D + d];
+    posterior<T>(lpj + n * cols, cols, q, red_d);
+    const uint32_t *st = states + n * (int64_t)S * Hw;
+    // per state: es, Wq, sigma
+    double sg = 0.0;
+    for (int k = threadIdx.x; k < S; k += T) {
+      double qk = q[S_perm + k];
+      const uint32_t *sk = st + (int64_t)k * Hw;
+      int a = 0;
+      bool live = qk > Q_SKIP;
+      for (int w1 = 0; w1 < Hw; ++w1) {
+        uint32_t m1 = sk[w1];
+        a += __popc(m1);
+        if (!live) continue;
+        while (m1) {
+          int b1 = __ffs(m1) - 1;
+          m1 &= m1 - 1;
+          int h = (w1 << 5) + b1;
+          atomicAdd(&es[h], qk);
+          double *row = Wq + (int64_t)h * H;
+          for (int w2 = 0; w2 <= w1; ++w2) {
+            uint32_t m2 = sk[w2];
+            if (w2 == w1) m2 &= (b1 == 31) ? 0xFFFFFFFFu : ((2u << b1) - 1u);  // h' <= h
+            while (m2) {
+              int b2 = __ffs(m2) - 1;
+              m2 &= m2 - 1;
+              atomicAdd(row + (w2 << 5) + b2, qk);
+            }
+          }
+        }
+      }
+      sg += qk * (lpj[n * cols + S_perm + k] - pil_bar * (double)a) / pre1;
+    }
+    if (S_perm > 0 && threadIdx.x == 0) sg += q[0] * lpj[n * cols] / pre1;  // all-zero state: |y|^2
+    sig_acc += sg;
+    __syncthreads();
+    // active latents
+    if (threadIdx.x == 0) n_act = 0;
+    __syncthreads();
+    for (int base = 0; base < H; base += T) {
+      int h = base + threadIdx.x;
+      bool f = h < H && es[h] != 0.0;
+      int tot;
+      int off = group_scan_flag<T>(f, tot, red_i);
+      if (f) act[n_act + off] = h;
+      __syncthreads();
+      if (threadIdx.x == 0) n_act += tot;
+      __syncthreads();
+    }
+    int na = n_act;
+    for (int i = threadIdx.x; i < na; i += T) atomicAdd(pies + act[i], es[act[i]]);
+    if (Es_out)
+      for (int h = threadIdx.x; h < H; h += T) Es_out[n * H + h] = (float)es[h];
+    for (int i = 0; i < na; ++i) {
+      int h = act[i];
+      double e = es[h];
+      double *row = Wp + (int64_t)h * D;
+      for (int d = threadIdx.x; d < D; d += T) atomicAdd(row + d, e * (double)y[d]);
+    }
+  }
+  sig_acc = group_sum<T>(sig_acc, red_d);
+  if (threadIdx.x == 0) atomicAdd(sig, sig_acc);
+}
+
+// y_rec[n, ~keep] = W[~keep] <s>_n  (Model.reconstruct _models.py:614-665 + BSC.modelmean bsc.py:279-287)
+template <int T>
+__global__ void __launch_bounds__(T) bsc_reconstruct_kernel(const uint32_t *__restrict__ states,
+                                                            const double *__restrict__ lpj, const double *__restrict__ W,
+                                                            const float *__restrict__ Y, const uint8_t *__restrict__ keep,
+                                                            const uint8_t *__restrict__ infer, int64_t N, int D, int H,
+                                                            int Hw, int S, int S_perm, float *__restrict__ Yrec) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ double red_d[8];
+  __shared__ int red_i[8];
+  double *es = reinterpret_cast<double *>(smem_raw);  // [H]
+  double *q = es + H;                                  // [S + S_perm]
+  const int cols = S + S_perm;
+  for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
+    __syncthreads();
+    int any = 0;
+    if (infer) {
+      for (int d = threadIdx.x; d < D; d += T) any |= infer[n * D + d];
+      any = (int)group_or<T>((unsigned)any, red_i);
+    } else {
+      any = 1;
+    }
+    if (!any) {  // no usable entry: the reference leaves the row as the copy of y
+      for (int d = threadIdx.x; d < D; d += T) Yrec[n * D + d] = Y[n * D + d];
+      continue;
+    }
+    for (int h = threadIdx.x; h < H; h += T) es[h] = 0.0;
+    posterior<T>(lpj + n * cols, cols, q, red_d);
+    const uint32_t *st = states + n * (int64_t)S * Hw;
+    for (int k = threadIdx.x; k < S; k += T) {
+      double qk = q[S_perm + k];
+      if (!(qk > Q_SKIP)) continue;
+      const uint32_t *sk = st + (int64_t)k * Hw;
+      for (int w = 0; w < Hw; ++w) {
+        uint32_t m = sk[w];
+        while (m) { int b = __ffs(m) - 1; m &= m - 1; atomicAdd(&es[(w << 5) + b], qk); }
+      }
+    }
+    __syncthreads();
+    for (int d = threadIdx.x; d < D; d += T) {
+      float out = Y[n * D + d];
+      if (!keep || !keep[n * D + d]) {
+        double acc = 0.0;
+        const double *Wr = W + (int64_t)d * H;
+        for (int h = 0; h < H; ++h) { double e = es[h]; if (e != 0.0) acc += e * Wr[h]; }
+        out = (float)acc;
+      }
+      Yrec[n * D + d] = out;
+    }
+  }
+}
+
+// sum_n logsumexp_k lpj[n][k]   (_models.py:544-547): one warp per row
+__global__ void free_energy_kernel(const double *__restrict__ lpj, int64_t N, int cols, int64_t ld, double *out) {
+  int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  int lane = threadIdx.x & 31;
+  int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  double acc = 0.0;
+  for (int64_t n = warp; n < N; n += nwarps) {
+    const double *row = lpj + n * ld;
+    double mx = -DBL_MAX;
+    for (int i = lane; i < cols; i += 32) mx = fmax(mx, row[i]);
+    mx = warp_max(mx);
+    double se = 0.0;
+    for (int i = lane; i < cols; i += 32) se += exp(row[i] - mx);
+    se = warp_sum(se);
+    acc += mx + log(se);
+  }
+  if (lane == 0 && acc != 0.0) atomicAdd(out, acc);
+}
+
+}  // namespace evo
+
+using namespace evo;
+
+static int grid_for(const void *kernel, int T, size_t smem, int64_t N) {
+  int per_sm = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, T, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+  int64_t g = (int64_t)sm_count() * per_sm;
+  if (g > N) g = N;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+extern "C" int evo_bsc_prepare(const double *W, const float *Y, int64_t N, int D, int H, double *G, double *B,
+                               double *ynorm2, void *stream) {
+  EVO_REQUIRE(N >= 0 && D > 0 && H > 0, "bad sizes");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (G) {
+    dim3 grid((H + 31) / 32, (H + 31) / 32);
+    gram_kernel<<<grid, 256, 0, st>>>(W, G, D, H);
+    EVO_LAUNCH_CHECK("gram");
+  }
+  if (N == 0) return EVO_OK;
+  if (ynorm2) {
+    int blocks = (int)((N * 32 + 255) / 256 < (int64_t)sm_count() * 8 ? (N * 32 + 255) / 256 : (int64_t)sm_count() * 8);
+    ynorm_kernel<<<blocks, 256, 0, st>>>(Y, ynorm2, N, D);
+    EVO_LAUNCH_CHECK("ynorm");
+  }
+  if (B) {
+    int64_t tiles = ((N + 63) / 64) * ((H + 63) / 64);
+    int blocks = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
+    wty_kernel<<<blocks, 256, 0, st>>>(Y, W, B, N, D, H);
+    EVO_LAUNCH_CHECK("wty");
+  }
+  return EVO_OK;
+}
+
+template <class Eval>
+static int launch_lpj(Eval ev, const uint32_t *states, int shared_states, int64_t N, int Sp, int Hw, double *out,
+                      int64_t ld, unsigned long long *counters, cudaStream_t st) {
+  size_t smem = ev.smem_bytes();
+  if (Sp <= 32) {
+    auto k = lpj_kernel<Eval, 32>;
+    if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid_for((const void *)k, 32, smem, N), 32, smem, st>>>(ev, states, shared_states, N, Sp, Hw, out, ld, counters);
+  } else {
+    auto k = lpj_kernel<Eval, 128>;
+    if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid_for((const void *)k, 128, smem, N), 128, smem, st>>>(ev, states, shared_states, N, Sp, Hw, out, ld, counters);
+  }
+  EVO_LAUNCH_CHECK("lpj");
+  return EVO_OK;
+}
+
+extern "C" int evo_bsc_lpj(int eval, const uint32_t *states, int shared_states, int64_t N, int Sp, int D, int H,
+                           const double *W, const float *Y, const uint8_t *mask, const double *G, const double *B,
+                           const double *ynorm2, double pre1, double pil_bar, double *lpj_out, int64_t ld_lpj,
+                           unsigned long long *reset_counters, void *stream) {
+  EVO_REQUIRE(N >= 0 && Sp > 0 && D > 0 && H > 0 && ld_lpj >= Sp, "bad sizes");
+  if (N == 0) return EVO_OK;
+  int Hw = words_for(H);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (eval == EVO_EVAL_BSC_GRAM) {
+    EVO_REQUIRE(G && B && ynorm2, "gram evaluator needs G, B, ynorm2");
+    EVO_REQUIRE(mask == nullptr, "gram evaluator needs complete data");
+    BscGramEval ev{G, B, ynorm2, pre1, pil_bar, H, Hw, nullptr, 0.0};
+    return launch_lpj(ev, states, shared_states, N, Sp, Hw, lpj_out, ld_lpj, reset_counters, st);
+  } else if (eval == EVO_EVAL_BSC_DIRECT) {
+    EVO_REQUIRE(W && Y, "direct evaluator needs W, Y");
+    BscDirectEval ev{W, Y, mask, pre1, pil_bar, D, H, Hw, nullptr, nullptr, 0.0};
+    return launch_lpj(ev, states, shared_states, N, Sp, Hw, lpj_out, ld_lpj, reset_counters, st);
+  }
+  set_error("evo_bsc_lpj: unknown evaluator %d", eval);
+  return EVO_ERR_ARG;
+}
+
+extern "C" int evo_free_energy(const double *lpj, int64_t N, int cols, int64_t ld, double *out, void *stream) {
+  EVO_REQUIRE(N >= 0 && cols > 0 && ld >= cols, "bad sizes");
+  if (N == 0) return EVO_OK;
+  int blocks = (int)((N * 32 + 255) / 256 < (int64_t)sm_count() * 8 ? (N * 32 + 255) / 256 : (int64_t)sm_count() * 8);
+  free_energy_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(lpj, N, cols, ld, out);
+  EVO_LAUNCH_CHECK("free_energy");
+  return EVO_OK;
+}
+
+extern "C" int evo_bsc_suffstats(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H,
+                                 int S, int S_perm, int allzero, double pre1, double pil_bar, double *stats,
+                                 float *Es_out, void *stream) {
+  (void)allzero;
+  EVO_REQUIRE(N >= 0 && D > 0 && H > 0 && S > 0, "bad sizes");
+  if (N == 0) return EVO_OK;
+  int Hw = words_for(H);
+  size_t smem = sizeof(double) * ((size_t)H + S + S_perm) + sizeof(float) * (size_t)D + sizeof(int) * (size_t)H;
+  constexpr int T = 128;
+  auto k = bsc_suffstats_kernel<T>;
+  if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k<<<grid_for((const void *)k, T, smem, N), T, smem, (cudaStream_t)stream>>>(states, lpj, Ym, N, D, H, Hw, S, S_perm,
+                                                                              pre1, pil_bar, stats, Es_out);
+  EVO_LAUNCH_CHECK("bsc_suffstats");
+  return EVO_OK;
+}
+
+extern "C" int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double *W, const float *Y,
+                                   const uint8_t *recon_keep, const uint8_t *infer_mask, int64_t N, int D, int H, int S,
+                                   int S_perm, float *Yrec, void *stream) {
+  EVO_REQUIRE(N >= 0 && D > 0 && H > 0 && S > 0, "bad sizes");
+  if (N == 0) return EVO_OK;
+  int Hw = words_for(H);
+  size_t smem = sizeof(double) * ((size_t)H + S + S_perm);
+  constexpr int T = 128;
+  auto k = bsc_reconstruct_kernel<T>;
+  if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k<<<grid_for((const void *)k, T, smem, N), T, smem, (cudaStream_t)stream>>>(states, lpj, W, Y, recon_keep, infer_mask,
+                                                                              N, D, H, Hw, S, S_perm, Yrec);
+  EVO_LAUNCH_CHECK("bsc_reconstruct");
+  return EVO_OK;
+}

@@ -1,0 +1,446 @@
+// Fused truncated-variational E-step for one datapoint per thread group (T threads = one CTA):
+//   lpj of K^n under the current parameters       (_models.py:507-513)
+//   evolutionary generations: select -> mutate -> packed-bit hash de-duplication -> lpj of the
+//   genuinely new states                            (evo/variational/eas.py:153-313)
+//   top-K replacement (j-th best new <-> j-th worst old slot)   (evo/variational/utils.py:231-337)
+//   free-energy tail sum_n logsumexp_k lpj_nk        (_models.py:544-547)
+// The K^n block, the children of all generations, the hash table and the lpj values live in
+// shared memory; HBM sees one read of K^n (+ the evaluator's per-datapoint table row), one write
+// of the lpj row and writes of the substituted states only.
+#pragma once
+#include "common.cuh"
+#include "evaluators.cuh"
+
+namespace evo {
+
+struct EstepDev {
+  int64_t N, n_offset;
+  int D, H, Hw, S, S_perm, Mprime;
+  int n_parents, n_children, n_generations, selection, mutation, background;
+  double p_bf, sparseness;
+  uint64_t seed;
+  uint32_t iteration;
+  uint32_t *states;
+  double *lpj;
+  const uint32_t *inj_children;
+  const int32_t *inj_count;
+  int inj_cmax;
+  double *acc;
+  // derived
+  int Cg;    // children capacity per generation
+  int Ctot;  // Cg * n_generations
+  int HT;    // hash table slots (power of two)
+  int PK;    // capacity of pool / key arrays = max(S, Cg)
+};
+
+constexpr int TAG_EMPTY = -1;
+constexpr int TAG_CHILD = 1 << 24;
+
+struct EstepSmem {
+  uint32_t *st_uniq;   // [(S + Ctot)][Hw]
+  uint32_t *st_child;  // [Cg][Hw]
+  double *lpj_uniq;    // [S + Ctot]
+  double *keys;        // [PK]
+  double *red_d;       // [8]
+  int *table;          // [HT]
+  int *pool;           // [PK]
+  int *slot;           // [Cg]   hash slot / flip positions
+  int *parents;        // [n_parents]
+  int *red_i;          // [8]
+  int *sh;             // [8] shared scalars
+  unsigned char *redisc;  // [S + Ctot]
+  unsigned char *taken;   // [S + Ctot]
+  unsigned char *status;  // [Cg]
+  unsigned char *eval_smem;
+};
+
+__host__ __device__ inline size_t align8(size_t x) { return (x + 7) & ~(size_t)7; }
+
+__host__ __device__ inline size_t estep_carve(const EstepDev &a, unsigned char *base, EstepSmem *s) {
+  size_t off = 0;
+  size_t U = (size_t)a.S + a.Ctot;
+#define CARVE(field, type, count)                                  \
+  do {                                                             \
+    if (s) s->field = reinterpret_cast<type *>(base + off);       \
+    off = align8(off + sizeof(type) * (size_t)(count));           \
+  } while (0)
+  CARVE(lpj_uniq, double, U);
+  CARVE(keys, double, a.PK);
+  CARVE(red_d, double, 8);
+  CARVE(st_uniq, uint32_t, U * a.Hw);
+  CARVE(st_child, uint32_t, (size_t)a.Cg * a.Hw);
+  CARVE(table, int, a.HT);
+  CARVE(pool, int, a.PK);
+  CARVE(slot, int, a.Cg > 0 ? a.Cg : 1);
+  CARVE(parents, int, a.n_parents > 0 ? a.n_parents : 1);
+  CARVE(red_i, int, 8);
+  CARVE(sh, int, 8);
+  CARVE(redisc, unsigned char, U);
+  CARVE(taken, unsigned char, U);
+  CARVE(status, unsigned char, a.Cg > 0 ? a.Cg : 1);
+#undef CARVE
+  if (s) s->eval_smem = base + off;
+  return off;
+}
+
+// ---- hash table over packed states --------------------------------------------------------
+__device__ __forceinline__ const uint32_t *tag_state(const EstepDev &a, const EstepSmem &s, int tag) {
+  return tag >= TAG_CHILD ? s.st_child + (size_t)(tag - TAG_CHILD) * a.Hw : s.st_uniq + (size_t)tag * a.Hw;
+}
+// read-only probe: index of the uniq entry equal to st, or -1
+__device__ __forceinline__ int table_find(const EstepDev &a, const EstepSmem &s, const uint32_t *st) {
+  uint32_t mask = (uint32_t)a.HT - 1u;
+  uint32_t p = (uint32_t)hash_state(st, a.Hw) & mask;
+  for (int it = 0; it < a.HT; ++it) {
+    int tag = s.table[p];
+    if (tag == TAG_EMPTY) return -1;
+    if (same_state(tag_state(a, s, tag), st, a.Hw)) return tag;
+    p = (p + 1) & mask;
+  }
+  return -1;
+}
+// concurrent insert; equal states converge on one slot holding the smallest tag.  Returns the slot.
+__device__ __forceinline__ int table_insert(const EstepDev &a, const EstepSmem &s, const uint32_t *st, int tag) {
+  uint32_t mask = (uint32_t)a.HT - 1u;
+  uint32_t p = (uint32_t)hash_state(st, a.Hw) & mask;
+  for (int it = 0; it < a.HT; ++it) {
+    int cur = s.table[p];
+    if (cur == TAG_EMPTY) {
+      cur = atomicCAS(&s.table[p], TAG_EMPTY, tag);
+      if (cur == TAG_EMPTY) return (int)p;
+    }
+    if (same_state(tag_state(a, s, cur), st, a.Hw)) {
+      atomicMin(&s.table[p], tag);
+      return (int)p;
+    }
+    p = (p + 1) & mask;
+  }
+  return -1;  // table full: cannot happen, HT >= 2 * (S + Ctot)
+}
+
+// ---- mutation helpers -----------------------------------------------------------------------
+__device__ __forceinline__ void flip_bit(uint32_t *st, int pos) { st[pos >> 5] ^= 1u << (pos & 31); }
+
+// sparseflip (eas.py:46-100): independent flips, p1 on on-bits, p0 on off-bits, over the first Hm
+// latents.  Sampled by thinning a Bernoulli(pmax) process visited with geometric jumps -- same
+// distribution, O(#candidates) draws instead of O(H).
+__device__ inline void sparseflip_state(uint32_t *st, int Hm, double sparseness, double p_bf, const RngCtx &rng,
+                                        uint32_t purpose, uint32_t g, uint32_t c) {
+  int a = 0;
+  for (int i = 0; i < Hm; i += 32) {
+    uint32_t w = st[i >> 5];
+    if (Hm - i < 32) w &= (1u << (Hm - i)) - 1u;
+    a += __popc(w);
+  }
+  double H = (double)Hm, s = (double)a, tiny = 1e-100;
+  double alpha = (H - s) * (H * p_bf - (sparseness - s)) / ((sparseness - s + H * p_bf) * s + tiny);
+  double p0 = H * p_bf / (H + (alpha - 1.0) * s + tiny);
+  double p1 = alpha * p0;
+  p0 = fmin(fmax(p0, 0.0), 1.0);
+  p1 = fmin(fmax(p1, 0.0), 1.0);
+  if (!(p0 == p0)) p0 = 0.0;
+  if (!(p1 == p1)) p1 = 0.0;
+  double pmax = fmax(p0, p1);
+  if (pmax <= 0.0) return;
+  double inv_log = (pmax < 1.0) ? 1.0 / log1p(-pmax) : 0.0;
+  uint32_t draw_idx = c * 4096u;
+  long pos = -1;
+  for (;;) {
+    uint4 r = rng.draw(purpose, g, draw_idx++);
+    double u = u01(r.x, r.y);
+    long gap = (pmax < 1.0) ? (long)floor(log(u) * inv_log) : 0;
+    pos += 1 + gap;
+    if (pos >= Hm) break;
+    bool on = (st[pos >> 5] >> (pos & 31)) & 1u;
+    double pb = on ? p1 : p0;
+    double v = u01(r.z, r.w);
+    if (v * pmax < pb) flip_bit(st, (int)pos);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+template <class Eval, int T>
+__global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  EstepSmem s;
+  estep_carve(a, smem_raw, &s);
+  const int tid = threadIdx.x;
+  const int Hw = a.Hw, S = a.S;
+  const int Hm = a.background ? a.H - 1 : a.H;
+  double acc_F = 0.0, acc_U = 0.0, acc_sub = 0.0, acc_eval = 0.0;
+  unsigned long long cnt_nan = 0, cnt_small = 0, cnt_inf = 0;
+
+  for (int64_t n = blockIdx.x; n < a.N; n += gridDim.x) {
+    RngCtx rng(a.seed, a.n_offset + n, a.iteration);
+    gsync<T>();  // previous datapoint fully done with shared memory
+    // ---- load K^n, evaluator tables ---------------------------------------------------------
+    {
+      const uint32_t *src = a.states + n * (int64_t)S * Hw;
+      for (int i = tid; i < S * Hw; i += T) s.st_uniq[i] = src[i];
+      for (int i = tid; i < a.HT; i += T) s.table[i] = TAG_EMPTY;
+      for (int i = tid; i < S + a.Ctot; i += T) { s.redisc[i] = 0; s.taken[i] = 0; }
+      ev.template setup<T>(n, s.eval_smem);
+    }
+    gsync<T>();
+    // ---- lpj of the permanent state and of K^n ------------------------------------------------
+    double lpj_perm = 0.0;
+    {
+      unsigned fl = 0;
+      if (a.S_perm > 0) {
+        unsigned f0 = 0;
+        lpj_perm = ev.eval_zero(f0);
+        if (tid == 0 && f0) { if (f0 & 1) ++cnt_nan; else if (f0 & 2) ++cnt_small; else ++cnt_inf; }
+      }
+      ev.template eval_batch<T>(s.st_uniq, S, s.lpj_uniq, fl);
+      fl = group_or<T>(fl, s.red_i);
+      if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
+      for (int i = tid; i < S; i += T) table_insert(a, s, s.st_uniq + (size_t)i * Hw, i);
+    }
+    gsync<T>();
+
+    int U = 0;        // accepted new unique states so far
+    int pool_n = S;   // generation 0 selects from K^n
+    for (int i = tid; i < S; i += T) s.pool[i] = i;
+    gsync<T>();
+
+    for (int g = 0; g < a.n_generations; ++g) {
+      int nc = 0;
+      if (a.inj_children) {
+        // ---- injected candidates (parity runs) -------------------------------------------------
+        nc = a.inj_count[n * (int64_t)a.n_generations + g];
+        if (nc > a.Cg) nc = a.Cg;
+        const uint32_t *src = a.inj_children + ((n * (int64_t)a.n_generations + g) * a.inj_cmax) * (int64_t)Hw;
+        for (int i = tid; i < nc * Hw; i += T) s.st_child[i] = src[i];
+      } else {
+        // ---- parent selection (eas.py:138-150) -------------------------------------------------
+        int take = pool_n < a.n_parents ? pool_n : a.n_parents;
+        {
+          double mn = DBL_MAX;
+          if (a.selection == EVO_SEL_FIT) {
+            for (int i = tid; i < pool_n; i += T) mn = fmin(mn, s.lpj_uniq[s.pool[i]]);
+            mn = -group_max<T>(-mn, s.red_d);
+          }
+          double shift = 2.0 * fmin(mn, 0.0);
+          for (int i = tid; i < pool_n; i += T) {
+            uint4 r = rng.draw(RNG_SELECT, g, (uint32_t)i);
+            double u = u01(r.x, r.y);
+            double key;
+            if (a.selection == EVO_SEL_FIT) {
+              double w = s.lpj_uniq[s.pool[i]] - shift;
+              key = (w > 0.0) ? log(u) / w : -DBL_MAX;  // Efraimidis-Spirakis weighted sampling w/o replacement
+            } else {
+              key = u;
+            }
+            s.keys[i] = key;
+          }
+          gsync<T>();
+          for (int p = 0; p < take; ++p) {
+            KeyIdx best; best.key = 0; best.idx = -1;
+            for (int i = tid; i < pool_n; i += T) {
+              double k = s.keys[i];
+              if (k != k) continue;  // NaN marks taken
+              KeyIdx c; c.key = k; c.idx = i;
+              best = better(best, c);
+            }
+            best = group_argmax<T>(best, s.red_d, s.red_i);
+            if (tid == 0) {
+              s.parents[p] = best.idx >= 0 ? s.pool[best.idx] : s.pool[0];
+              if (best.idx >= 0) s.keys[best.idx] = nan("");
+            }
+            gsync<T>();
+          }
+        }
+        // ---- mutation (eas.py:10-135) -----------------------------------------------------------
+        const int mut = a.mutation;
+        if (mut == EVO_MUT_RANDFLIP || mut == EVO_MUT_SPARSEFLIP) {
+          const int C = a.n_children;
+          nc = take * C;
+          if (mut == EVO_MUT_RANDFLIP) {
+            // C distinct uniformly drawn positions per parent; child j flips position j
+            for (int p = tid; p < take; p += T) {
+              uint32_t di = (uint32_t)p * 64u * (uint32_t)(C + 1);
+              for (int j = 0; j < C; ++j) {
+                int pos;
+                bool dup;
+                do {
+                  uint4 r = rng.draw(RNG_MUTATE, g, di++);
+                  pos = (int)urange(r.x, (uint32_t)Hm);
+                  dup = false;
+                  for (int q = 0; q < j; ++q) dup |= (s.slot[p * C + q] == pos);
+                  if (dup && C >= Hm) { dup = false; }  // cannot be distinct: give up (degenerate input)
+                } while (dup);
+                s.slot[p * C + j] = pos;
+              }
+            }
+            gsync<T>();
+          }
+          for (int c = tid; c < nc; c += T) {
+            int p = c / C;
+            const uint32_t *src = s.st_uniq + (size_t)s.parents[p] * Hw;
+            uint32_t *dst = s.st_child + (size_t)c * Hw;
+            for (int w = 0; w < Hw; ++w) dst[w] = src[w];
+            if (a.background) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
+            if (mut == EVO_MUT_RANDFLIP) flip_bit(dst, s.slot[c]);
+            else sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_MUTATE, g, (uint32_t)c);
+            if (a.background) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
+          }
+        } else {
+          // one-point crossover of every unordered parent pair, two children per pair
+          int npairs = take * (take - 1) / 2;
+          nc = 2 * npairs;
+          for (int q = tid; q < npairs; q += T) {
+            int i = 0, rem = q;
+            while (rem >= take - 1 - i) { rem -= take - 1 - i; ++i; }
+            int j = i + 1 + rem;
+            uint4 r = rng.draw(RNG_CROSS, g, (uint32_t)q);
+            int cp = 1 + (Hm > 1 ? (int)urange(r.x, (uint32_t)(Hm - 1)) : 0);  // cp in {1..Hm-1}
+            const uint32_t *pa = s.st_uniq + (size_t)s.parents[i] * Hw;
+            const uint32_t *pb = s.st_uniq + (size_t)s.parents[j] * Hw;
+            uint32_t *c0 = s.st_child + (size_t)(2 * q) * Hw, *c1 = c0 + Hw;
+            for (int w = 0; w < Hw; ++w) {
+              int lo = w << 5;
+              uint32_t head = cp >= lo + 32 ? 0xFFFFFFFFu : (cp <= lo ? 0u : ((1u << (cp - lo)) - 1u));
+              c0[w] = (pa[w] & head) | (pb[w] & ~head);
+              c1[w] = (pb[w] & head) | (pa[w] & ~head);
+            }
+            for (int k = 0; k < 2; ++k) {
+              uint32_t *dst = k ? c1 : c0;
+              uint32_t cidx = (uint32_t)(2 * q + k);
+              if (a.background) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
+              if (mut == EVO_MUT_CROSS_RANDFLIP) {
+                uint4 r2 = rng.draw(RNG_FLIP2, g, cidx);
+                flip_bit(dst, (int)urange(r2.x, (uint32_t)Hm));
+              } else if (mut == EVO_MUT_CROSS_SPARSEFLIP) {
+                sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_FLIP2, g, cidx);
+              }
+              if (a.background) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
+            }
+          }
+        }
+      }
+      gsync<T>();
+
+      // ---- de-duplicate against (permanent, K^n, earlier new) and among the children ----------
+      for (int c = tid; c < nc; c += T) {
+        const uint32_t *st = s.st_child + (size_t)c * Hw;
+        unsigned char stt = 1;  // candidate
+        if (a.S_perm > 0 && popc_state(st, Hw) == 0) stt = 0;
+        else {
+          int hit = table_find(a, s, st);
+          if (hit >= 0) { s.redisc[hit] = 1; stt = 0; }
+        }
+        s.status[c] = stt;
+      }
+      gsync<T>();
+      for (int c = tid; c < nc; c += T)
+        if (s.status[c]) s.slot[c] = table_insert(a, s, s.st_child + (size_t)c * Hw, TAG_CHILD + c);
+      gsync<T>();
+      // first occurrence of each new state wins; compact winners (child order) behind st_uniq
+      int u_g = 0;
+      for (int base = 0; base < nc; base += T) {
+        int c = base + tid;
+        bool win = false;
+        int sl = -1;
+        if (c < nc && s.status[c]) { sl = s.slot[c]; win = (sl >= 0 && s.table[sl] == TAG_CHILD + c); }
+        int tot;
+        int off = group_scan_flag<T>(win, tot, s.red_i);
+        if (win) {
+          int idx = S + U + u_g + off;
+          const uint32_t *src = s.st_child + (size_t)c * Hw;
+          uint32_t *dst = s.st_uniq + (size_t)idx * Hw;
+          for (int w = 0; w < Hw; ++w) dst[w] = src[w];
+          s.status[c] = 2;
+          s.table[sl] = idx;  // from now on a uniq entry (losers of this state compare against a child tag and fail)
+        }
+        u_g += tot;
+        gsync<T>();
+      }
+
+      // ---- lpj of the genuinely new states ------------------------------------------------------
+      {
+        unsigned fl = 0;
+        if (u_g > 0) {
+          ev.template eval_batch<T>(s.st_uniq + (size_t)(S + U) * Hw, u_g, s.lpj_uniq + S + U, fl);
+          fl = group_or<T>(fl, s.red_i);
+          if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
+        }
+      }
+      gsync<T>();
+      // ---- next pool: this round's new states, then the re-discovered old ones -----------------
+      int pn = 0;
+      for (int i = tid; i < u_g && i < a.PK; i += T) s.pool[i] = S + U + i;
+      pn = u_g < a.PK ? u_g : a.PK;
+      for (int base = 0; base < S + U; base += T) {
+        int i = base + tid;
+        bool f = (i < S + U) && s.redisc[i];
+        int tot;
+        int off = group_scan_flag<T>(f, tot, s.red_i);
+        if (f) {
+          if (pn + off < a.PK) s.pool[pn + off] = i;
+          s.redisc[i] = 0;
+        }
+        pn += tot;
+        if (pn > a.PK) pn = a.PK;
+        gsync<T>();
+      }
+      U += u_g;
+      pool_n = pn;
+      if (pool_n == 0) break;  // "No new and unique states" (eas.py:306-308)
+    }
+
+    // ---- vary_Kn: j-th best new replaces j-th worst old while it is better ----------------------
+    int n_sub = 0;
+    {
+      int Mp = U < a.Mprime ? U : a.Mprime;
+      for (int j = 0; j < Mp; ++j) {
+        KeyIdx bn; bn.key = 0; bn.idx = -1;
+        for (int i = tid; i < U; i += T)
+          if (!s.taken[S + i]) { KeyIdx c; c.key = s.lpj_uniq[S + i]; c.idx = i; bn = better(bn, c); }
+        bn = group_argmax<T>(bn, s.red_d, s.red_i);
+        KeyIdx wo; wo.key = 0; wo.idx = -1;
+        for (int i = tid; i < S; i += T)
+          if (!s.taken[i]) { KeyIdx c; c.key = -s.lpj_uniq[i]; c.idx = i; wo = better(wo, c); }
+        wo = group_argmax<T>(wo, s.red_d, s.red_i);
+        if (bn.idx < 0 || wo.idx < 0 || !(bn.key > -wo.key)) break;
+        // replace slot wo.idx by new state bn.idx
+        const uint32_t *src = s.st_uniq + (size_t)(S + bn.idx) * Hw;
+        uint32_t *dst = s.st_uniq + (size_t)wo.idx * Hw;
+        uint32_t *gdst = a.states + (n * (int64_t)S + wo.idx) * Hw;
+        gsync<T>();
+        for (int w = tid; w < Hw; w += T) { uint32_t v = src[w]; dst[w] = v; gdst[w] = v; }
+        if (tid == 0) { s.lpj_uniq[wo.idx] = bn.key; s.taken[wo.idx] = 1; s.taken[S + bn.idx] = 1; }
+        ++n_sub;
+        gsync<T>();
+      }
+    }
+    // ---- write lpj row, free-energy contribution ------------------------------------------------
+    {
+      double *row = a.lpj + n * (int64_t)(S + a.S_perm);
+      double mx = -DBL_MAX;
+      for (int i = tid; i < S; i += T) { double v = s.lpj_uniq[i]; row[a.S_perm + i] = v; mx = fmax(mx, v); }
+      if (a.S_perm > 0) { if (tid == 0) row[0] = lpj_perm; mx = fmax(mx, lpj_perm); }
+      mx = group_max<T>(mx, s.red_d);
+      double se = 0.0;
+      for (int i = tid; i < S; i += T) se += exp(s.lpj_uniq[i] - mx);
+      if (a.S_perm > 0 && tid == 0) se += exp(lpj_perm - mx);
+      se = group_sum<T>(se, s.red_d);
+      if (tid == 0) {
+        acc_F += mx + log(se);
+        acc_U += (double)U;
+        acc_sub += (double)n_sub;
+        acc_eval += (double)(S + U);
+      }
+    }
+  }
+  if (tid == 0 && a.acc) {
+    atomicAdd(a.acc + 0, acc_F);
+    atomicAdd(a.acc + 1, acc_U);
+    atomicAdd(a.acc + 2, acc_sub);
+    if (cnt_nan) atomicAdd(a.acc + 3, (double)cnt_nan);
+    if (cnt_small) atomicAdd(a.acc + 4, (double)cnt_small);
+    if (cnt_inf) atomicAdd(a.acc + 5, (double)cnt_inf);
+    atomicAdd(a.acc + 6, acc_eval);
+  }
+}
+
+}  // namespace evo

@@ -1,0 +1,134 @@
+// Log-pseudo-joint evaluators.  Each evaluator is a small POD passed by value to the kernels with
+//   smem_bytes()                      dynamic shared memory it needs per datapoint group
+//   setup<T>(n, smem)                 cooperative per-datapoint load (caller syncs afterwards)
+//   eval_batch<T>(st, cnt, out, fl)   cooperative evaluation of cnt packed states -> out[0..cnt)
+//   eval_zero()                       lpj of the all-zero state (permanent state), per thread
+#pragma once
+#include "common.cuh"
+
+namespace evo {
+
+// ------------------------------------------------------------------------------------------
+// BSC, sparse quadratic form (complete data):
+//   |y - W s|^2 = |y|^2 - 2 sum_{h in s} b_h + sum_{h,h' in s} G_hh',  b = W'y, G = W'W
+// combined in f64 (the three terms cancel catastrophically on well-fitting states).
+// Replaces BSC.log_pseudo_joint (evo/models/bsc.py:79-97) for complete data.
+// ------------------------------------------------------------------------------------------
+struct BscGramEval {
+  const double *G;       // [H][H]
+  const double *B;       // [N][H]
+  const double *ynorm2;  // [N]
+  double pre1, pil_bar;
+  int H, Hw;
+  // per datapoint (set in setup)
+  double *b;  // smem [H]
+  double yn2;
+
+  __host__ __device__ size_t smem_bytes() const { return (size_t)H * sizeof(double); }
+  __host__ int threads_hint(int work) const { return work <= 32 ? 32 : (work <= 64 ? 64 : 128); }
+
+  template <int T>
+  __device__ void setup(int64_t n, unsigned char *smem) {
+    b = reinterpret_cast<double *>(smem);
+    const double *src = B + n * (int64_t)H;
+    for (int i = threadIdx.x; i < H; i += T) b[i] = __ldg(src + i);
+    yn2 = __ldg(ynorm2 + n);
+  }
+
+  __device__ __forceinline__ double eval_one(const uint32_t *st) const {
+    double sb = 0.0, sg = 0.0;
+    int a = 0;
+    for (int w1 = 0; w1 < Hw; ++w1) {
+      uint32_t m1 = st[w1];
+      while (m1) {
+        int b1 = __ffs(m1) - 1;
+        m1 &= m1 - 1;
+        int h = (w1 << 5) + b1;
+        ++a;
+        sb += b[h];
+        const double *Gr = G + (int64_t)h * H;
+        double t = 0.0;
+        for (int w2 = 0; w2 <= w1; ++w2) {
+          uint32_t m2 = st[w2];
+          if (w2 == w1) m2 &= (1u << b1) - 1u;
+          while (m2) {
+            int b2 = __ffs(m2) - 1;
+            m2 &= m2 - 1;
+            t += __ldg(Gr + (w2 << 5) + b2);
+          }
+        }
+        sg += __ldg(Gr + h) + 2.0 * t;
+      }
+    }
+    double resid = yn2 - 2.0 * sb + sg;
+    return pre1 * resid + pil_bar * (double)a;
+  }
+
+  template <int T>
+  __device__ void eval_batch(const uint32_t *st, int cnt, double *out, unsigned &flags) const {
+    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one(st + (size_t)i * Hw), flags);
+  }
+  __device__ double eval_zero(unsigned &flags) const { return lpj_sanitise(pre1 * yn2, flags); }
+};
+
+// ------------------------------------------------------------------------------------------
+// BSC, explicit masked residual -- the reference's own formula (bsc.py:88-95), f64 throughout.
+// Used for incomplete data (the Gram of the observed rows differs per datapoint) and as the
+// on-device cross-check of the Gram form.
+// ------------------------------------------------------------------------------------------
+struct BscDirectEval {
+  const double *W;      // [D][H]
+  const float *Y;       // [N][D]
+  const uint8_t *mask;  // [N][D] or NULL
+  double pre1, pil_bar;
+  int D, H, Hw;
+  double *y;       // smem [D]  (0 where masked)
+  uint8_t *m;      // smem [D]
+  double yn2;
+
+  __host__ __device__ size_t smem_bytes() const { return (size_t)D * sizeof(double) + (((size_t)D + 7) & ~(size_t)7); }
+  __host__ int threads_hint(int work) const { return work <= 32 ? 32 : (work <= 64 ? 64 : 128); }
+
+  template <int T>
+  __device__ void setup(int64_t n, unsigned char *smem) {
+    y = reinterpret_cast<double *>(smem);
+    m = smem + (size_t)D * sizeof(double);
+    for (int d = threadIdx.x; d < D; d += T) {
+      uint8_t ok = mask ? mask[n * (int64_t)D + d] : (uint8_t)1;
+      m[d] = ok;
+      y[d] = ok ? (double)Y[n * (int64_t)D + d] : 0.0;
+    }
+  }
+
+  __device__ __forceinline__ double eval_one(const uint32_t *st) const {
+    double resid = 0.0;
+    for (int d = 0; d < D; ++d) {
+      if (!m[d]) continue;
+      const double *Wr = W + (int64_t)d * H;
+      double mean = 0.0;
+      for (int w = 0; w < Hw; ++w) {
+        uint32_t mm = st[w];
+        while (mm) {
+          int bpos = __ffs(mm) - 1;
+          mm &= mm - 1;
+          mean += __ldg(Wr + (w << 5) + bpos);
+        }
+      }
+      double r = mean - y[d];
+      resid += r * r;
+    }
+    return pre1 * resid + pil_bar * (double)popc_state(st, Hw);
+  }
+
+  template <int T>
+  __device__ void eval_batch(const uint32_t *st, int cnt, double *out, unsigned &flags) const {
+    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one(st + (size_t)i * Hw), flags);
+  }
+  __device__ double eval_zero(unsigned &flags) const {
+    double s = 0.0;
+    for (int d = 0; d < D; ++d) s += y[d] * y[d];
+    return lpj_sanitise(pre1 * s, flags);
+  }
+};
+
+}  // namespace evo

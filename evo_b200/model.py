@@ -1,0 +1,180 @@
+"""`Model` -- EM skeleton with the reference's interface (evo/models/_models.py:17-665), driving the
+CUDA kernels of libevo_b200.so.  Subclasses: `BSC` (bsc.py), `SSSC` (sssc.py).
+
+Per EM iteration and rank: a few kernel launches on the current stream, ONE all-reduce of the packed
+sufficient statistics (+ free-energy / diagnostic scalars in its tail), one small replicated solve.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from . import comm as _comm
+from . import variational as V
+
+ACC_LEN = 8  # [sum logsumexp, #new unique, #substituted, reset nan, reset small, reset inf, #lpj evaluated, spare]
+
+
+def _dev(x, device, dtype):
+    """numpy / torch (any device) -> contiguous tensor on `device`."""
+    if isinstance(x, torch.Tensor):
+        return x.to(device=device, dtype=dtype).contiguous()
+    return torch.as_tensor(np.ascontiguousarray(x)).to(device=device, dtype=dtype).contiguous()
+
+
+class DeviceData:
+    """Device-resident shard of the dataset (`my_data` of the reference):
+    Y float32 [N][D] (0 where missing), inference mask / reconstruction mask as uint8 or None."""
+
+    def __init__(self, my_data, device, comm):
+        y = my_data["y"]
+        self.N, self.D = int(y.shape[0]), int(y.shape[1])
+        x_infr = my_data.get("x_infr") if hasattr(my_data, "get") else my_data["x_infr"]
+        if x_infr is None:
+            x_infr = np.ones((self.N, self.D), dtype=bool)
+        xi = _dev(x_infr, device, torch.uint8)
+        self.incomplete = not bool(xi.all().item())
+        self.mask = xi if self.incomplete else None
+        Y = _dev(y, device, torch.float32)
+        if self.incomplete:
+            Y = torch.where(xi.bool(), Y, torch.zeros_like(Y))  # NaN placeholders never reach a kernel
+        self.Y = Y.contiguous()
+        x = my_data["x"] if "x" in my_data else None
+        self.keep = _dev(x, device, torch.uint8) if x is not None else None
+        self.n_obs = int(xi.sum().item()) if self.incomplete else self.N * self.D
+        # constants reduced once (the reference re-reduces them 3-4x per iteration)
+        tot = comm.allreduce(np.array([float(self.N), float(self.n_obs)]))
+        tot = np.atleast_1d(tot)
+        self.N_total, self.n_obs_total = int(round(tot[0])), int(round(tot[1]))
+        self.Yrec = None
+        self.cache = {}
+
+
+class Model:
+    """Abstract EM model.  Same constructor and methods as the reference's `Model`
+    (_models.py:17-56); `comm` is an `evo_b200.comm.Comm` (or anything with its surface)."""
+
+    def __init__(self, D, H, S, to_learn=("W", "pi", "sigma"), comm=None, device=None):
+        self.comm = comm if comm is not None else _comm.world()
+        self.to_learn = list(to_learn)
+        self.D, self.H, self.S = int(D), int(H), int(S)
+        tol = 1e-5
+        self.noise_policy = {
+            "W": (-np.inf, +np.inf, False, None),
+            "pi": (tol, 1.0 - tol, False, None),
+            "sigma": (tol, +np.inf, False, None),
+        }
+        self.B_max = 0.0
+        self.B_max_shft = np.inf
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.lib = _lib.load()  # raises if the CUDA library has not been built
+        self._data = {}
+        self.last_counts = {}
+
+    # ---- plumbing ---------------------------------------------------------------------------
+    def device_data(self, my_data):
+        key = id(my_data["y"])
+        dd = self._data.get(key)
+        if dd is None or dd.N != my_data["y"].shape[0]:
+            dd = DeviceData(my_data, self.device, self.comm)
+            self._data = {key: dd}  # one resident dataset per model
+        return dd
+
+    def _call(self, name, *args):
+        with torch.cuda.device(self.device):
+            _lib.check(getattr(self.lib, name)(*args, _lib.stream()), name)
+
+    # ---- parameter sanity (_models.py:102-159) -------------------------------------------------
+    def check_params(self, model_params):
+        """Clamp to the noise policy.  Every rank holds bit-identical parameters (same reduced
+        statistics, same deterministic solve), so the reference's per-iteration Bcast is dropped."""
+        for param, (lo, hi, absify, lo_diag) in self.noise_policy.items():
+            if param not in model_params:
+                continue
+            v = model_params[param]
+            if np.isscalar(v) or (isinstance(v, np.ndarray) and v.ndim == 0):
+                v = float(v)
+                assert np.isfinite(v), "scalar %s not finite" % param
+                if v < lo:
+                    v = lo
+                if v >= hi:
+                    v = hi
+                model_params[param] = v
+            elif isinstance(v, torch.Tensor):
+                if np.isfinite(lo) or np.isfinite(hi):
+                    v.clamp_(min=lo if np.isfinite(lo) else None, max=hi if np.isfinite(hi) else None)
+                if lo_diag is not None:
+                    d = torch.diagonal(v)
+                    d.clamp_(min=lo_diag)
+            else:
+                v = np.asarray(v)
+                assert np.isfinite(v).all(), "%s not finite" % param
+                if np.isfinite(lo):
+                    v[v < lo] = lo
+                if np.isfinite(hi):
+                    v[v >= hi] = hi
+                if lo_diag is not None:
+                    idx = np.arange(v.shape[0])
+                    dg = v[idx, idx]
+                    dg[dg < lo_diag] = lo_diag
+                    v[idx, idx] = dg
+                model_params[param] = v
+        return model_params
+
+    # ---- EM step (_models.py:162-203) -----------------------------------------------------------
+    def step(self, model_params, my_suff_stat, my_data, do_reconstruction=False):
+        model_params = self.check_params(model_params)
+        F, S_nunique, S_sub = self.E_step(model_params, my_suff_stat, my_data)
+        if do_reconstruction:
+            self.reconstruct(my_data, my_suff_stat, model_params)
+        new_params = self.M_step(model_params, my_suff_stat, my_data) if len(self.to_learn) > 0 else model_params
+        return F, S_nunique, S_sub, new_params
+
+    # ---- fused E-step launcher --------------------------------------------------------------------
+    def _estep_launch(self, my_suff_stat, dd, acc, fill):
+        """Fill an `evo_estep_args`, let the subclass add its evaluator tables (`fill(args)`), launch."""
+        a = _lib.EstepArgs()
+        ss = my_suff_stat
+        perm = ss["permanent"]
+        a.N, a.n_offset = dd.N, int(ss.get("n_offset", 0) or 0)
+        a.D, a.H, a.S, a.S_perm = self.D, self.H, int(ss["ss_dev"].shape[1]), int(ss["S_perm"])
+        a.Mprime = int(ss["Mprime"])
+        a.n_parents, a.n_children, a.n_generations = int(ss["n_parents"]), int(ss["n_children"]), int(ss["n_generations"])
+        a.selection = _lib.SEL[ss["parent_selection"].name]
+        a.mutation = _lib.MUT[ss["mutation_algorithm"].name]
+        a.background = int(bool(perm["background"]))
+        a.bitflip_prob = float(ss["bitflip_prob"]) if ss["bitflip_prob"] is not None else 0.0
+        a.seed, a.iteration = int(ss.get("seed", 0x5EED)), int(ss.get("iteration", 0)) + 1
+        a.states, a.lpj = ss["ss_dev"].data_ptr(), ss["lpj_dev"].data_ptr()
+        inj = ss.get("inject")
+        keep = None
+        if inj is not None:
+            ch, cnt = inj
+            if not isinstance(ch, torch.Tensor) or ch.dtype != torch.int32:
+                ch, cnt = V.pack_injection(ch, cnt, self.device)
+            keep = (ch, cnt)
+            assert ch.shape[0] == dd.N and ch.shape[1] == a.n_generations
+            a.inj_children, a.inj_count, a.inj_cmax = ch.data_ptr(), cnt.data_ptr(), int(ch.shape[2])
+        a.acc = acc.data_ptr()
+        hold = fill(a)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.evo_estep(C.byref(a), _lib.stream()), "evo_estep")
+        ss["iteration"] = a.iteration
+        return keep, hold
+
+    # ---- free energy (_models.py:334-451) -------------------------------------------------------
+    def _sum_logsumexp(self, lpj):
+        out = torch.zeros(1, dtype=torch.float64, device=self.device)
+        self._call("evo_free_energy", _lib.ptr(lpj), lpj.shape[0], lpj.shape[1], lpj.stride(0), _lib.ptr(out))
+        return out
+
+    # ---- data generation (_models.py:73-99) -- cold path, host NumPy like the reference ---------
+    def generate_data(self, model_params, my_N):
+        assert "pies" in model_params or "pi" in model_params
+        W = np.asarray(model_params["W"].cpu() if isinstance(model_params["W"], torch.Tensor) else model_params["W"])
+        D, H_gen = W.shape
+        pies = model_params["pies"] if "pies" in model_params else model_params["pi"]
+        p = np.random.random(size=(my_N, H_gen))
+        s = p <= pies
+        return self.generate_from_hidden(model_params, {"s": s})

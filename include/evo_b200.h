@@ -1,0 +1,142 @@
+/* evo_b200 -- C-ABI of the B200-native E-step / M-step hot path of tvlearn/evo.
+ *
+ * The reference (pure Python, /root/reference) has no FFI; the entry points below are what its
+ * model classes would bind for this path.  Each one names the reference function it replaces
+ * (file:line relative to the reference root).  INTEGRATION.md shows the ctypes binding.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative code on error; the message is available
+ *     from evo_last_error() (thread-local).
+ *   - all pointers are DEVICE pointers unless the name says host; the caller owns every buffer.
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no hidden syncs.
+ *   - K-state sets are bit-packed: uint32 [N][S][Hw], Hw = ceil(H/32), latent h lives in word
+ *     h/32 bit h%32, pad bits are zero.  The reference stores them as (N,S,H) bool
+ *     (evo/variational/utils.py:94-150).
+ *   - lpj is float64 [N][S + S_perm], permanent states first (utils.py:94, _models.py:507-512).
+ *   - Y is float32 [N][D]; masks are uint8 [N][D] (1 = usable), NULL = complete data.
+ *   - W is float64 [D][H] row-major, exactly the reference's model_params["W"].
+ */
+#ifndef EVO_B200_H
+#define EVO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EVO_OK 0
+#define EVO_ERR_ARG (-1)
+#define EVO_ERR_CUDA (-2)
+#define EVO_ERR_UNSUPPORTED (-3)
+
+/* parent selection (evo/variational/eas.py:138-150) */
+#define EVO_SEL_FIT 0
+#define EVO_SEL_RAND 1
+/* mutation operators (eas.py:10-135) */
+#define EVO_MUT_RANDFLIP 0
+#define EVO_MUT_SPARSEFLIP 1
+#define EVO_MUT_CROSS 2
+#define EVO_MUT_CROSS_RANDFLIP 3
+#define EVO_MUT_CROSS_SPARSEFLIP 4
+
+/* log-joint evaluators */
+#define EVO_EVAL_BSC_GRAM 0   /* sparse quadratic form s'Gs - 2 s'b (complete data)          */
+#define EVO_EVAL_BSC_DIRECT 1 /* explicit masked residual (missing data / reference formula) */
+#define EVO_EVAL_ES3C 2       /* per-state Woodbury / Cholesky                                */
+
+const char *evo_last_error(void);
+int evo_version(void);
+/* number of SMs of the current device (grid sizing) */
+int evo_device_sm_count(void);
+
+/* ---- K-state container (evo/variational/utils.py:19-152) ------------------------------- */
+/* (rows,H) bool bytes -> (rows,Hw) packed words, and back */
+int evo_states_pack(const uint8_t *bools, uint32_t *packed, int64_t rows, int H, void *stream);
+int evo_states_unpack(const uint32_t *packed, uint8_t *bools, int64_t rows, int H, void *stream);
+/* Initial K^n: S distinct Bernoulli(p) states per datapoint, never equal to a permanent state
+ * (utils.py:100-138).  Philox stream keyed by (seed, n_offset + n). */
+int evo_states_init(uint32_t *states, int64_t N, int S, int H, int S_perm, int background, double p,
+                    uint64_t seed, int64_t n_offset, void *stream);
+
+/* ---- BSC log-pseudo-joint (evo/models/bsc.py:60-125, _models.py:567-596) ------------------ */
+/* State-independent tables for the Gram form: G = W'W (H,H) f64, B = Y W (N,H) f64,
+ * ynorm2[n] = |y_n|^2 f64.  Pass ynorm2 == NULL to skip it (Y is constant over EM iterations). */
+int evo_bsc_prepare(const double *W, const float *Y, int64_t N, int D, int H, double *G, double *B,
+                    double *ynorm2, void *stream);
+/* lpj[n][k] = pre1 * |y_n - W s_nk|^2_obs + pil_bar |s_nk|, sanitised as lpj_reset_check.
+ * eval = EVO_EVAL_BSC_GRAM uses (G,B,ynorm2); EVO_EVAL_BSC_DIRECT uses (W,Y,mask).
+ * states: [N][Sp][Hw] or, with shared_states != 0, one [Sp][Hw] table used for every datapoint
+ * (the reference's free_energy(full=True) state table, _models.py:385-431).
+ * lpj_out has row stride ld_lpj doubles; reset_counters = 3 uint64 (nan, small, inf) or NULL. */
+int evo_bsc_lpj(int eval, const uint32_t *states, int shared_states, int64_t N, int Sp, int D, int H,
+                const double *W, const float *Y, const uint8_t *mask, const double *G, const double *B,
+                const double *ynorm2, double pre1, double pil_bar, double *lpj_out, int64_t ld_lpj,
+                unsigned long long *reset_counters, void *stream);
+
+/* ---- fused E-step (Model.E_step _models.py:454-565 = lpj of K^n + evolve_states eas.py:153-313
+ *      + vary_Kn utils.py:231-337 + free-energy tail _models.py:544-547) ---------------------- */
+typedef struct evo_estep_args {
+  /* sizes */
+  int64_t N;         /* datapoints on this rank */
+  int64_t n_offset;  /* global index of row 0 (RNG keying: results do not depend on #ranks) */
+  int32_t D, H, S, S_perm, Mprime;
+  /* evolutionary hyper-parameters (container keys, utils.py:210-226) */
+  int32_t n_parents, n_children, n_generations, selection, mutation, background;
+  double bitflip_prob; /* p_bf */
+  double sparseness;   /* theta["piH"] */
+  /* RNG */
+  uint64_t seed;
+  uint32_t iteration;
+  int32_t eval; /* EVO_EVAL_* */
+  /* K sets, in place */
+  uint32_t *states; /* [N][S][Hw] */
+  double *lpj;      /* [N][S+S_perm] */
+  /* injected candidates (parity tests): children[n][g][c] packed, count[n][g]; NULL = RNG mode */
+  const uint32_t *inj_children; /* [N][G][inj_cmax][Hw] */
+  const int32_t *inj_count;     /* [N][G] */
+  int32_t inj_cmax;
+  int32_t _pad0;
+  /* model tables */
+  const double *W;       /* [D][H]           (direct, es3c) */
+  const float *Y;        /* [N][D]           (direct, es3c) */
+  const uint8_t *mask;   /* [N][D] or NULL   (direct, es3c) */
+  const double *G;       /* [H][H]           (gram) */
+  const double *B;       /* [N][H]           (gram) */
+  const double *ynorm2;  /* [N]              (gram) */
+  double pre1, pil_bar;  /* BSC scalars (bsc.py:111-113) */
+  /* ES3C tables (sssc.py:329-366): pil_bar_h (H), mus (H), Psi (H,H), sigma2 */
+  const double *pil_bar_h, *mus, *Psi;
+  double sigma2;
+  /* outputs: acc[0] += sum_n logsumexp_k lpj_nk, acc[1] += #new unique, acc[2] += #substituted,
+   * acc[3..5] += lpj_reset_check counters (nan, small, inf), acc[6] += #log-joints evaluated */
+  double *acc;
+} evo_estep_args;
+int evo_estep(const evo_estep_args *args, void *stream);
+
+/* vary_Kn alone (utils.py:231-337) for one batch of datapoints: new candidates [N][U][Hw] with
+ * lpj_new [N][U], n_new[n] valid rows each; updates states/lpj in place; out_counts[n] =
+ * (#new unique, #substituted). */
+int evo_select_topk(uint32_t *states, double *lpj, int64_t N, int S, int S_perm, int H, int Mprime,
+                    const uint32_t *new_states, const double *lpj_new, const int32_t *n_new, int U,
+                    int32_t *out_counts, void *stream);
+
+/* sum_n logsumexp_k lpj[n][0..cols) accumulated into *out (f64) (_models.py:544-547) */
+int evo_free_energy(const double *lpj, int64_t N, int cols, int64_t ld, double *out, void *stream);
+
+/* ---- BSC M-step statistics (bsc.py:176-223) and estimator (_models.py:614-665) ------------ */
+/* stats layout (f64): [Wp H*D | Wq H*H | pies H | sigma_sum 1]; accumulated (+=), caller zeroes.
+ * Ym = y or y_reconstructed (f32 [N][D]).  Only the lower triangle (h' <= h) of Wq is written. */
+int evo_bsc_suffstats(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D,
+                      int H, int S, int S_perm, int allzero, double pre1, double pil_bar,
+                      double *stats, float *Es_out, void *stream);
+/* y_rec[n][d] = sum_h <s_h>_n W[d][h] where recon_mask[n][d] == 0 (x false); other entries copy y;
+ * rows whose infer_mask is all zero are left untouched (_models.py:646-648). */
+int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double *W, const float *Y,
+                        const uint8_t *recon_keep, const uint8_t *infer_mask, int64_t N, int D, int H,
+                        int S, int S_perm, float *Yrec, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EVO_B200_H */

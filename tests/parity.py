@@ -1,0 +1,148 @@
+"""Shared parity harness (test infrastructure): runs the CUDA BSC path on a golden fixture with the
+recorded candidate sets injected, and compares with (a) the reference outputs stored in the fixture
+and (b) the NumPy oracle replaying the same candidates.  Used by tests/ and __graft_entry__.smoke()."""
+import copy
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def relerr(a, b):
+    a, b = np.asarray(a, dtype=float), np.asarray(b, dtype=float)
+    return float(np.max(np.abs(a - b) / (1e-300 + np.maximum(np.abs(b), 1e-12 * (1 + np.abs(b).max())))) if a.size else 0.0)
+
+
+def maxrel(a, b):
+    """max |a-b| / max|b| -- scale-relative error for parameter arrays."""
+    a, b = np.asarray(a, dtype=float), np.asarray(b, dtype=float)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)) if a.size else 0.0
+
+
+def load_case(path):
+    z = np.load(path, allow_pickle=False)
+    c = {k: z[k] for k in z.files}
+    H, N, S = int(c["H"]), int(c["N"]), int(c["S"])
+    c["ss0_bool"] = np.unpackbits(c["ss0"], axis=-1)[..., :H].astype(bool)
+    c["ss_final_bool"] = np.unpackbits(c["ss_final"], axis=-1)[..., :H].astype(bool)
+    c["children_bool"] = np.unpackbits(c["children"], axis=-1)[..., :H].astype(bool)
+    return c
+
+
+def permanent_of(c):
+    return {"background": False, "allzero": bool(c["allzero"]), "singletons": False} if bool(c["allzero"]) else None
+
+
+class OracleReplay:
+    """Feeds the fixture's recorded children to the oracle's evolve_states."""
+
+    def __init__(self, cont, children, counts):
+        self.cont, self.children, self.counts = cont, children, counts
+        self.it, self.n, self.g = 0, -1, 0
+        cont["parent_selection"] = self.select
+        cont["mutation_algorithm"] = self.mutate
+
+    def select(self, cands, n_parents, lpj):
+        if np.shares_memory(cands, self.cont["ss"]):
+            self.n += 1
+            self.g = 0
+        else:
+            self.g += 1
+        return cands[:n_parents]
+
+    def mutate(self, parents, n_children, sparseness, p_bf):
+        k = int(self.counts[self.it, self.n, self.g])
+        return self.children[self.it, self.n, self.g, :k].copy()
+
+    def next_iteration(self):
+        self.it += 1
+        self.n = -1
+
+
+def run_oracle_case(c, iters):
+    from oracle import bsc as OB
+    from oracle import variational as OV
+
+    D, H, N, S = int(c["D"]), int(c["H"]), int(c["N"]), int(c["S"])
+    perm = permanent_of(c)
+    cont = OV.init_states(1, S, H, str(c["selection"]), str(c["mutation"]), int(c["P"]), int(c["C"]), int(c["G"]),
+                          bitflip_prob=1.0 / H, permanent=copy.deepcopy(perm))
+    cont["ss"] = c["ss0_bool"].copy()
+    cont["lpj"] = np.empty((N, cont["ss"].shape[1] + cont["S_perm"]))
+    rep = OracleReplay(cont, c["children_bool"], c["child_count"])
+    data = {"y": c["Y"].copy(), "x_infr": c["X"].copy()}
+    missing = float(c["missing"]) > 0
+    if missing:
+        data["x"] = c["X"].copy()
+    th = {"W": c["W0"].copy(), "pi": float(c["pi0"]), "sigma": float(c["sigma0"])}
+    out = []
+    for it in range(iters):
+        F, a, b, th = OB.step(th, cont, data, D, H, cont["ss"].shape[1], do_reconstruction=missing,
+                              reference_quirks=False)
+        out.append((F, a, b, {k: np.array(th[k]) for k in ("W", "pi", "sigma")}))
+        rep.next_iteration()
+    return out, cont, data
+
+
+def run_gpu_case(c, iters, inject=True):
+    import torch
+
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import init_states
+
+    D, H, N, S = int(c["D"]), int(c["H"]), int(c["N"]), int(c["S"])
+    perm = permanent_of(c)
+    model = BSC(D, H, S)
+    cont = init_states(N, S, H, str(c["selection"]), str(c["mutation"]), int(c["P"]), int(c["C"]), int(c["G"]),
+                       bitflip_prob=1.0 / H, permanent=copy.deepcopy(perm))
+    cont["ss"] = c["ss0_bool"]
+    data = {"y": c["Y"].copy(), "x_infr": c["X"].copy()}
+    missing = float(c["missing"]) > 0
+    if missing:
+        data["x"] = c["X"].copy()
+    th = {"W": c["W0"].copy(), "pi": float(c["pi0"]), "sigma": float(c["sigma0"])}
+    out = []
+    for it in range(iters):
+        if inject:
+            cont["inject"] = (c["children_bool"][it], c["child_count"][it])
+        F, a, b, th = model.step(th, cont, data, do_reconstruction=missing)
+        out.append((F, a, b, {k: np.array(th[k]) for k in ("W", "pi", "sigma")}))
+    torch.cuda.synchronize()
+    return out, cont, data
+
+
+def run_bsc_parity_case(path, iters=None):
+    """GPU vs fixture (reference outputs) vs oracle; returns error summary."""
+    c = load_case(path)
+    total = int(c["iters"])
+    iters = total if iters is None else min(iters, total)
+    gpu, gcont, gdata = run_gpu_case(c, iters)
+    ora, ocont, odata = run_oracle_case(c, iters)
+    res = {"F_err": 0.0, "W_err": 0.0, "pi_err": 0.0, "sigma_err": 0.0, "count_err": 0.0,
+           "F_err_ref": 0.0, "W_err_ref": 0.0}
+    for it in range(iters):
+        Fg, ag, bg, tg = gpu[it]
+        Fo, ao, bo, to = ora[it]
+        res["F_err"] = max(res["F_err"], abs(Fg - Fo) / abs(Fo))
+        res["W_err"] = max(res["W_err"], maxrel(tg["W"], to["W"]))
+        res["pi_err"] = max(res["pi_err"], abs(tg["pi"] - to["pi"]) / abs(to["pi"]))
+        res["sigma_err"] = max(res["sigma_err"], abs(tg["sigma"] - to["sigma"]) / abs(to["sigma"]))
+        res["count_err"] = max(res["count_err"], abs(ag - ao), abs(bg - bo))
+        res["F_err_ref"] = max(res["F_err_ref"], abs(Fg - c["F"][it]) / abs(c["F"][it]))
+        res["W_err_ref"] = max(res["W_err_ref"], maxrel(tg["W"], c["W"][it]))
+    gss = gcont["ss"]
+    res["ss_equal"] = bool(np.array_equal(gss, ocont["ss"]))
+    res["lpj_err"] = maxrel(gcont["lpj"], ocont["lpj"])
+    if iters == total:
+        res["ss_equal_ref"] = bool(np.array_equal(gss, c["ss_final_bool"]))
+        res["lpj_err_ref"] = maxrel(gcont["lpj"], c["lpj_final"])
+        if float(c["missing"]) > 0:
+            res["yrec_err_ref"] = maxrel(gdata["y_reconstructed"], c["y_reconstructed"])
+    res["iters"] = iters
+    return res

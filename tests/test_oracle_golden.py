@@ -1,0 +1,84 @@
+"""CPU tests: the NumPy oracle against the fixtures recorded from the unmodified reference
+(tests/golden/make_golden.py).  No GPU, no /root/reference needed."""
+import os
+import warnings
+
+import numpy as np
+import pytest
+
+import parity as P
+from oracle import bsc as OB
+from oracle import variational as OV
+
+warnings.simplefilter("ignore")
+
+
+@pytest.mark.parametrize("name", ["bsc_bars_replay", "bsc_exact", "bsc_allzero_sparseflip", "bsc_cross", "bsc_missing"])
+def test_oracle_replay_reproduces_reference_trajectory(name):
+    c = P.load_case(os.path.join(P.GOLDEN, name + ".npz"))
+    iters = int(c["iters"])
+    out, cont, data = P.run_oracle_case(c, iters)
+    for it in range(iters):
+        F, a, b, th = out[it]
+        assert abs(F - c["F"][it]) <= 1e-11 * abs(c["F"][it])
+        assert abs(a - c["S_nunique"][it]) < 1e-12 and abs(b - c["S_sub"][it]) < 1e-12
+        assert P.maxrel(th["W"], c["W"][it]) < 1e-8
+        assert abs(th["pi"] - c["pi"][it]) <= 1e-10 * c["pi"][it]
+        assert abs(th["sigma"] - c["sigma"][it]) <= 1e-10 * c["sigma"][it]
+    assert np.array_equal(cont["ss"], c["ss_final_bool"])
+    assert P.maxrel(cont["lpj"], c["lpj_final"]) < 1e-11
+    if float(c["missing"]) > 0:
+        assert P.maxrel(data["y_reconstructed"], c["y_reconstructed"]) < 1e-12
+
+
+def test_oracle_lpj_fixture():
+    z = np.load(os.path.join(P.GOLDEN, "bsc_lpj.npz"))
+    W, Y, X, states = z["W"], z["Y"], z["X"], z["states"]
+    th = OB.precompute({"W": W, "pi": float(z["pi"]), "sigma": float(z["sigma"])}, W.shape[0], W.shape[1], Y.shape[0],
+                       int(X.sum()))
+    assert abs(th["pre1"] - z["pre1"]) < 1e-15 and abs(th["pil_bar"] - z["pil_bar"]) < 1e-15
+    assert abs(th["ljc"] - z["ljc"]) < 1e-12 * abs(z["ljc"])
+    for n in range(Y.shape[0]):
+        got = OB.lpj_states(states[n], W, Y[n], X[n], th["pre1"], th["pil_bar"])
+        assert P.maxrel(got, z["lpj"][n]) < 1e-13
+        assert abs(OB.lpj_allzero(Y[n], X[n], th["pre1"])[0] - z["lpj_allzero"][n]) <= 1e-13 * abs(z["lpj_allzero"][n])
+    assert np.array_equal(OB.lpj_reset_check(z["reset_in"].copy()), z["reset_out"])
+
+
+def test_oracle_vary_kn_cases():
+    z = np.load(os.path.join(P.GOLDEN, "vary_kn_cases.npz"))
+    ncases = 1 + max(int(k.split("_")[0][1:]) for k in z.files)
+    assert ncases == 300
+    for i in range(ncases):
+        g = lambda k: z["c%d_%s" % (i, k)]
+        H, S, S_perm, Mp = int(g("H")), int(g("S")), int(g("S_perm")), int(g("Mprime"))
+        states, lpj_old, lpj = g("states").copy(), g("lpj_old").copy(), np.zeros(S)
+        ret = OV.vary_Kn(lpj_old, g("lpj_new").copy(), lpj, states, g("new").copy(), H, S, S_perm,
+                         np.zeros((S_perm, H), bool), Mp)
+        if g("new").shape[0] == 0:
+            continue
+        assert tuple(ret) == tuple(int(v) for v in g("ret"))
+        assert np.array_equal(states, g("out_states")) and np.array_equal(lpj, g("out_lpj"))
+
+
+def test_oracle_full_free_energy():
+    z = np.load(os.path.join(P.GOLDEN, "bsc_full_F.npz"))
+    Y, W = z["Y"], z["W"]
+    L = OB.free_energy_full({"W": W, "pi": float(z["pi"]), "sigma": float(z["sigma"])},
+                            {"y": Y, "x_infr": np.ones_like(Y, dtype=bool)}, W.shape[0], W.shape[1],
+                            OV.all_states(W.shape[1]))
+    assert abs(L - float(z["L"])) <= 1e-12 * abs(float(z["L"]))
+
+
+def test_pack_unpack_oracle():
+    rng = np.random.RandomState(1)
+    for H in (1, 31, 32, 33, 64, 65, 300):
+        a = rng.rand(3, 4, H) < 0.4
+        p = OV.pack_states(a)
+        assert p.shape == (3, 4, (H + 31) // 32)
+        assert np.array_equal(OV.unpack_states(p, H), a)
+        # bit h -> word h // 32, bit h % 32
+        h = H - 1
+        one = np.zeros((1, H), bool)
+        one[0, h] = True
+        assert OV.pack_states(one)[0, h // 32] == np.uint32(1 << (h % 32))
