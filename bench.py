@@ -1,0 +1,419 @@
+#!/usr/bin/env python
+"""Benchmark of the evo hot path (truncated-variational E-step + M-step) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--impl ours|reference]
+
+A "step" is one EM iteration (`model.step`: E-step over every datapoint of the shard, sufficient
+statistics, all-reduce, parameter update) on synthetic data of the shape BASELINE.json names.
+Metric: log-joints evaluated per second (whole job, all ranks); EM iterations/s rides along.
+Weak scaling: every rank owns N datapoints of the workload (no data-path collective; the only
+collective is the all-reduce of the packed sufficient statistics).
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# synthetic inputs and EA hyper-parameters per config
+WORKLOADS = {
+    # name: model, D, H, N (per GPU), K, (selection, mutation, parents, children, generations), active latents
+    "cfg1": dict(model="bsc", D=25, H=10, N=1000, K=20, ea=("fit", "randflip", 10, 1, 1), act=2.0, bars=True),
+    "cfg2": dict(model="bsc", D=256, H=300, N=100000, K=64, ea=("fit", "randflip", 8, 8, 2), act=5.0),
+    "cfg5": dict(model="bsc", D=1024, H=1024, N=1000000, K=128, ea=("fit", "randflip", 16, 8, 2), act=8.0),
+    "cfg3": dict(model="es3c", D=144, H=512, N=250000, K=64, ea=("fit", "randflip", 8, 8, 2), act=4.0),
+    "cfg4": dict(model="es3c", D=144, H=512, N=250000, K=64, ea=("fit", "randflip", 8, 8, 2), act=4.0, missing=0.3),
+}
+DESCR = {
+    "cfg1": "examples/bars-test BSC, 5x5 bars (D=25, H=10), N=1000, K=20",
+    "cfg2": "BSC feature learning, synthetic 16x16 patches (D=256, H=300), N=100k, K=64",
+    "cfg5": "large-scale BSC (D=1024, H=1024), N=1M, K=128",
+    "cfg3": "ES3C image denoising, synthetic 12x12 patches (D=144, H=512), N=250k, K=64",
+    "cfg4": "ES3C image inpainting, 30% missing (D=144, H=512), N=250k, K=64",
+}
+METRIC, UNIT = "log_joints_per_sec", "log-joints/s"
+
+
+def synth_host(w, N, seed):
+    """Synthetic dataset with NumPy's legacy RandomState -- used by the CPU arm and,
+    through the same recipe on the device, by the GPU arm."""
+    rng = np.random.RandomState(seed)
+    D, H = w["D"], w["H"]
+    if w.get("bars"):
+        R = H // 2
+        Wg = np.zeros((R, R, H))
+        for i in range(R):
+            Wg[i, :, i] = 10.0
+            Wg[:, i, R + i] = 10.0
+        Wg = Wg.reshape(R * R, H)
+    else:
+        Wg = rng.normal(size=(D, H))
+    s = rng.random_sample((N, H)) < w["act"] / H
+    if w["model"] == "es3c":
+        z = rng.normal(loc=1.0, size=(N, H))
+        Y = (s * z) @ Wg.T + rng.normal(size=(N, D))
+    else:
+        Y = s.astype(np.float64) @ Wg.T + rng.normal(size=(N, D))
+    Y = Y.astype(np.float32)
+    X = None
+    if w.get("missing"):
+        X = rng.random_sample((N, D)) >= w["missing"]
+    return Y, X
+
+
+def synth_device(w, N, seed, device):
+    import torch
+
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    D, H = w["D"], w["H"]
+    if w.get("bars"):
+        Y, X = synth_host(w, N, seed)
+        return torch.as_tensor(Y, device=device), None
+    Wg = torch.randn((D, H), generator=g, device=device)
+    Y = torch.empty((N, D), dtype=torch.float32, device=device)
+    X = None
+    chunk = 65536
+    for lo in range(0, N, chunk):
+        hi = min(N, lo + chunk)
+        s = (torch.rand((hi - lo, H), generator=g, device=device) < w["act"] / H).float()
+        if w["model"] == "es3c":
+            s = s * (1.0 + torch.randn((hi - lo, H), generator=g, device=device))
+        Y[lo:hi] = s @ Wg.T + torch.randn((hi - lo, D), generator=g, device=device)
+    if w.get("missing"):
+        X = torch.rand((N, D), generator=g, device=device) >= w["missing"]
+    return Y, X
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, "/tmp/evo_clocks_%d.csv" % os.getpid()
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        return out
+
+
+# ---------------------------------------------------------------------------------------------
+# algorithmic HBM bytes per call -- what `roofline.achieved` is made of
+# ---------------------------------------------------------------------------------------------
+def algorithmic_bytes(w, N, U_mean):
+    D, H, K = w["D"], w["H"], w["K"]
+    Hw = (H + 31) // 32
+    return {
+        # (a') + (c): read y_n, read every packed state evaluated, write every lpj
+        "evo_estep": N * (4 * D + (K + U_mean) * (4 * Hw + 4)),
+        # tables of the Gram form: read Y, write B = Y W (f64)
+        "evo_bsc_prepare": N * (4 * D + 8 * H),
+        # (d): read K^n + lpj + y_n, one pass over the outputs
+        "evo_bsc_suffstats": N * (K * (4 * Hw + 4) + 4 * D) + 8 * (H * D + H * H),
+    }
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    from evo_b200 import _lib
+    from evo_b200.comm import Comm
+    from evo_b200.variational import init_states
+
+    w = WORKLOADS[args.workload]
+    N = args.n if args.n else w["N"]
+    comm = Comm()
+    if w["model"] == "bsc":
+        from evo_b200.bsc import BSC
+        model = BSC(w["D"], w["H"], w["K"], comm=comm, device=device)
+    else:
+        from evo_b200.sssc import SSSC
+        model = SSSC(w["D"], w["H"], w["K"], comm=comm, device=device)
+    lib = _lib.load()
+
+    Y, X = synth_device(w, N, 1000 + rank, device)
+    data = {"y": Y, "x_infr": X}
+    if X is not None:
+        data["x"] = X
+    np.random.seed(1)
+    theta = model.check_params(model.standard_init(data))
+    for k in list(theta):
+        if isinstance(theta[k], np.ndarray) and theta[k].ndim >= 1:
+            theta[k] = torch.as_tensor(theta[k], device=device)  # device-resident parameters
+    sel, mut, P, C, G = w["ea"]
+    cont = init_states(N, w["K"], w["H"], sel, mut, P, C, G, device=device, seed=0x5EED, n_offset=rank * N)
+    recon = bool(w.get("missing")) or w["model"] == "es3c"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step(th):
+        F, nu, nsub, th = model.step(th, cont, data, do_reconstruction=recon)
+        return F, nu, nsub, th, model.last_counts["lpj_evaluated"]
+
+    for _ in range(args.warmup):
+        F, nu, nsub, theta, _ = one_step(theta)
+    # ---- timed region: inputs resident in HBM ------------------------------------------------
+    sampler = ClockSampler(local)
+    model.timing = []
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = lib.evo_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    lpj_total, U_sum = 0.0, 0.0
+    for _ in range(args.steps):
+        F, nu, nsub, theta, cnt = one_step(theta)
+        lpj_total += cnt
+        U_sum += nu
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = lib.evo_launch_count() - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    kern = model.timing_summary()
+    model.timing = None
+
+    # ---- end to end: batch arrives from pinned host memory, parameters and result go back ------
+    Yh = torch.empty(Y.shape, dtype=Y.dtype, pin_memory=True)
+    Yh.copy_(Y)
+    hdata = dict(data)
+    hdata["y"] = Yh
+    model._data = {id(Yh): model.device_data(data)}  # same resident shard, now fed from the host buffer
+    th_host = {k: (v.cpu().numpy() if isinstance(v, torch.Tensor) else v) for k, v in theta.items()}
+    h2d = Yh.numel() * Yh.element_size() + sum(v.nbytes for v in th_host.values() if isinstance(v, np.ndarray))
+    d2h = sum(v.nbytes for v in th_host.values() if isinstance(v, np.ndarray)) + 8 * 8
+
+    def e2e_step(th):
+        model.refresh_data(hdata)
+        F, nu, nsub, th = model.step(th, cont, hdata, do_reconstruction=recon)
+        return th, model.last_counts["lpj_evaluated"]
+
+    for _ in range(min(args.warmup, 2)):
+        th_host, _ = e2e_step(th_host)
+    barrier()
+    t0 = time.perf_counter()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
+    e2e_lpj = 0.0
+    for _ in range(args.steps):
+        th_host, cnt = e2e_step(th_host)
+        e2e_lpj += cnt
+    g1.record()
+    barrier()
+    e2e_ms = torch.tensor([max(g0.elapsed_time(g1), (time.perf_counter() - t0) * 1e3)], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_ms.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    U_mean = U_sum / args.steps
+    alg = algorithmic_bytes(w, N, U_mean)
+    peak, peak_src = measured_peaks()
+    tot_t = sum(c * t for c, t in kern.values())
+    dom = max(kern, key=lambda k: kern[k][0] * kern[k][1])
+    roof = None
+    if dom in alg:
+        ach = alg[dom] / (kern[dom][1] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src, "launch_ms": kern[dom][1],
+                "algorithmic_bytes_per_launch": alg[dom]}
+    line = {
+        "metric": METRIC, "value": lpj_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "%s: %s" % (args.workload, DESCR[args.workload]), "N_per_gpu": N,
+                   "ea": "%s/%s parents=%d children=%d generations=%d" % tuple(w["ea"]),
+                   "l2": "inputs larger than L2 (K sets + tables > 126 MB)" if N * w["K"] * 4 * ((w["H"] + 31) // 32) > 126e6
+                   else "working set fits L2 (small reference config)",
+                   "parallelism": "dp%d over N" % world},
+        "em_iters_per_sec": args.steps / (ms * 1e-3),
+        "lpj_per_step": lpj_total / args.steps, "new_unique_per_datapoint": U_mean, "free_energy": F,
+        "e2e": {"value": e2e_lpj / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": int(launches),
+        "kernels": {k: {"launches": c, "mean_ms": t, "share": c * t / tot_t} for k, (c, t) in kern.items()},
+        "roofline": roof, "clocks": clocks,
+    }
+    if not args.no_cpu and w["model"] == "bsc":
+        line["cpu_baseline"] = cpu_port(args.workload, steps=1, warmup=1)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the NumPy oracle (a restatement of the reference's per-datapoint NumPy path, pinned
+# against the unmodified reference -- kind "port") on the host cores, one process per core like
+# the reference's MPI ranks, each on its own bounded sample of the same workload.
+# ---------------------------------------------------------------------------------------------
+CPU_SAMPLE = {"cfg1": 1000, "cfg2": 1000, "cfg5": 64, "cfg3": 64, "cfg4": 64}  # datapoints per core per step
+
+
+def cpu_worker(args):
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    import warnings
+
+    warnings.simplefilter("ignore")
+    from oracle import bsc as OB
+    from oracle import variational as OV
+
+    w = WORKLOADS[args.workload]
+    n = args.n
+    D, H, K = w["D"], w["H"], w["K"]
+    Y, X = synth_host(w, n, 1000 + args.cpu_worker)
+    Y = Y.astype(np.float64)
+    np.random.seed(1 + args.cpu_worker)
+    mean = Y.mean(0)
+    sigma = float(np.sqrt(((Y - mean) ** 2).mean(0).sum() / D))
+    theta = {"W": mean[:, None] + np.random.normal(scale=sigma / 4.0, size=(D, H)), "pi": 1.0 / H, "sigma": sigma}
+    sel, mut, P, C, G = w["ea"]
+    cont = OV.init_states(n, K, H, sel, mut, P, C, G)
+    data = {"y": Y, "x_infr": np.ones_like(Y, dtype=bool)}
+    for _ in range(args.warmup):
+        OB.step(theta, cont, data, D, H, K)
+    t0 = time.perf_counter()
+    lpj = 0.0
+    for _ in range(args.steps):
+        F, nu, nsub, theta = OB.step(theta, cont, data, D, H, K)
+        lpj += n * K + nu * n
+    print(json.dumps({"lpj": lpj, "sec": time.perf_counter() - t0, "F": F}), flush=True)
+
+
+def cpu_port(workload, steps, warmup, n_sub=None, cores=None):
+    cores = cores or len(os.sched_getaffinity(0))
+    n_sub = n_sub or CPU_SAMPLE[workload]
+    env = dict(os.environ, OMP_NUM_THREADS="1", OPENBLAS_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+    cmd = [sys.executable, os.path.abspath(__file__), "--workload", workload, "--n", str(n_sub), "--steps", str(steps),
+           "--warmup", str(warmup)]
+    t0 = time.perf_counter()
+    procs = [subprocess.Popen(cmd + ["--cpu-worker", str(i)], stdout=subprocess.PIPE, env=env) for i in range(cores)]
+    outs = [json.loads(p.communicate()[0].decode().strip().splitlines()[-1]) for p in procs]
+    wall = time.perf_counter() - t0
+    sec = max(o["sec"] for o in outs)
+    lpj = sum(o["lpj"] for o in outs)
+    return {"value": lpj / sec, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d datapoints per core x %d cores, %d timed EM iteration(s) after %d warm-up, NumPy oracle "
+                      "(oracle/bsc.py), 1 BLAS thread per process; whole call %.1f s" % (n_sub, cores, steps, warmup, wall),
+            "ms_per_step": sec / steps * 1e3, "em_iters_per_sec_on_sample": steps / sec}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    w = WORKLOADS[args.workload]
+    if w["model"] != "bsc" and not os.path.exists(os.path.join(ROOT, "oracle", "sssc.py")):
+        print(json.dumps({"impl": "reference", "unavailable": "no CPU oracle for this model yet"}))
+        return
+    total = max(1, args.steps + args.warmup)
+    n_sub = max(16, int(CPU_SAMPLE[args.workload] * 2 / total))
+    cb = cpu_port(args.workload, steps=args.steps, warmup=args.warmup, n_sub=n_sub)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "%s: %s" % (args.workload, DESCR[args.workload]), "N_per_step": n_sub * cb["cores"],
+                   "ea": "%s/%s parents=%d children=%d generations=%d" % tuple(w["ea"]),
+                   "parallelism": "%d host processes over N" % cb["cores"]},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=0, help="datapoints per GPU (default: the workload's N)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-worker", type=int, default=-1, help=argparse.SUPPRESS)
+    args = ap.parse_args()
+    if args.cpu_worker >= 0:
+        return cpu_worker(args)
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

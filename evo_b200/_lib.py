@@ -44,6 +44,7 @@ SIGNATURES = {
     "evo_last_error": (C.c_char_p, []),
     "evo_version": (_i, []),
     "evo_device_sm_count": (_i, []),
+    "evo_launch_count": (C.c_ulonglong, []),
     "evo_states_pack": (_i, [_vp, _vp, _i64, _i, _vp]),
     "evo_states_unpack": (_i, [_vp, _vp, _i64, _i, _vp]),
     "evo_states_init": (_i, [_vp, _i64, _i, _i, _i, _i, _d, _u64, _i64, _vp]),

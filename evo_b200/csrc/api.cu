@@ -20,6 +20,9 @@ int check_cuda(cudaError_t e, const char *what) {
   set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
   return EVO_ERR_CUDA;
 }
+static unsigned long long g_launches = 0;
+void count_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); }
+unsigned long long launches() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 int sm_count() {
   static int cached[64];
   int dev = 0;
@@ -155,6 +158,7 @@ using namespace evo;
 extern "C" const char *evo_last_error(void) { return g_err; }
 extern "C" int evo_version(void) { return 100; }
 extern "C" int evo_device_sm_count(void) { return sm_count(); }
+extern "C" unsigned long long evo_launch_count(void) { return launches(); }
 
 extern "C" int evo_estep(const evo_estep_args *x, void *stream) {
   EVO_REQUIRE(x != nullptr, "null args");

@@ -23,7 +23,12 @@ int sm_count();
     int _rc = ::evo::check_cuda((call), #call);            \
     if (_rc) return _rc;                                   \
   } while (0)
-#define EVO_LAUNCH_CHECK(name) EVO_CUDA(cudaGetLastError())
+void count_launch();
+#define EVO_LAUNCH_CHECK(name)        \
+  do {                                \
+    ::evo::count_launch();            \
+    EVO_CUDA(cudaGetLastError());     \
+  } while (0)
 #define EVO_REQUIRE(cond, msg)                             \
   do {                                                     \
     if (!(cond)) {                                         \

@@ -31,10 +31,11 @@ class DeviceData:
         y = my_data["y"]
         self.N, self.D = int(y.shape[0]), int(y.shape[1])
         x_infr = my_data.get("x_infr") if hasattr(my_data, "get") else my_data["x_infr"]
-        if x_infr is None:
-            x_infr = np.ones((self.N, self.D), dtype=bool)
-        xi = _dev(x_infr, device, torch.uint8)
-        self.incomplete = not bool(xi.all().item())
+        if x_infr is None:  # complete data
+            xi, self.incomplete = None, False
+        else:
+            xi = _dev(x_infr, device, torch.uint8)
+            self.incomplete = not bool(xi.all().item())
         self.mask = xi if self.incomplete else None
         Y = _dev(y, device, torch.float32)
         if self.incomplete:
@@ -81,9 +82,53 @@ class Model:
             self._data = {key: dd}  # one resident dataset per model
         return dd
 
+    def refresh_data(self, my_data):
+        """Copy `my_data["y"]` (host buffer, ideally pinned) into the resident device shard again --
+        the host->device leg of a step whose batch arrives from the host -- and drop what was
+        derived from the old values."""
+        dd = self.device_data(my_data)
+        y = my_data["y"]
+        src = y if isinstance(y, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(y))
+        if src.dtype == dd.Y.dtype:
+            dd.Y.copy_(src, non_blocking=True)
+        else:
+            dd.Y.copy_(src.to(dd.Y.dtype))
+        if dd.incomplete:
+            dd.Y.copy_(torch.where(dd.mask.bool(), dd.Y, torch.zeros_like(dd.Y)))
+        dd.cache.pop("ynorm2", None)
+        return dd
+
     def _call(self, name, *args):
         with torch.cuda.device(self.device):
+            ev = self._tick()
             _lib.check(getattr(self.lib, name)(*args, _lib.stream()), name)
+            self._tock(name, ev)
+
+    # optional per-call CUDA-event timing on the launching stream (bench.py sets `timing = []`)
+    timing = None
+
+    def _tick(self):
+        if self.timing is None:
+            return None
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def _tock(self, name, e0):
+        if e0 is None:
+            return
+        e1 = torch.cuda.Event(enable_timing=True)
+        e1.record()
+        self.timing.append((name, e0, e1))
+
+    def timing_summary(self):
+        """{call: (count, mean ms)} of the recorded calls (synchronises)."""
+        torch.cuda.synchronize(self.device)
+        out = {}
+        for name, e0, e1 in self.timing or []:
+            c, t = out.get(name, (0, 0.0))
+            out[name] = (c + 1, t + e0.elapsed_time(e1))
+        return {k: (c, t / c) for k, (c, t) in out.items()}
 
     # ---- parameter sanity (_models.py:102-159) -------------------------------------------------
     def check_params(self, model_params):
@@ -159,7 +204,9 @@ class Model:
         a.acc = acc.data_ptr()
         hold = fill(a)
         with torch.cuda.device(self.device):
+            ev = self._tick()
             _lib.check(self.lib.evo_estep(C.byref(a), _lib.stream()), "evo_estep")
+            self._tock("evo_estep", ev)
         ss["iteration"] = a.iteration
         return keep, hold
 

@@ -49,6 +49,8 @@ const char *evo_last_error(void);
 int evo_version(void);
 /* number of SMs of the current device (grid sizing) */
 int evo_device_sm_count(void);
+/* kernels launched by this library since load (bench.py reports the count of the timed region) */
+unsigned long long evo_launch_count(void);
 
 /* ---- K-state container (evo/variational/utils.py:19-152) ------------------------------- */
 /* (rows,H) bool bytes -> (rows,Hw) packed words, and back */
