@@ -121,9 +121,10 @@ __global__ void __launch_bounds__(T) select_topk_kernel(uint32_t *__restrict__ s
 
 template <class Eval>
 static int launch_estep(const EstepDev &dv, Eval ev, cudaStream_t st) {
-  size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes();
   int work = dv.S > dv.Cg ? dv.S : dv.Cg;
   int T = ev.threads_hint(work);
+  T = T <= 32 ? 32 : (T <= 64 ? 64 : 128);
+  size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes(T);
 #define EVO_LAUNCH_T(TT)                                                                              \
   {                                                                                                   \
     auto k = estep_kernel<Eval, TT>;                                                                  \
@@ -210,7 +211,7 @@ extern "C" int evo_estep(const evo_estep_args *x, void *stream) {
   if (x->eval == EVO_EVAL_BSC_GRAM) {
     EVO_REQUIRE(x->G && x->B && x->ynorm2, "gram evaluator needs G, B, ynorm2");
     EVO_REQUIRE(x->mask == nullptr, "gram evaluator needs complete data");
-    BscGramEval ev{x->G, x->B, x->ynorm2, x->pre1, x->pil_bar, dv.H, dv.Hw, nullptr, 0.0};
+    BscGramEval ev{x->G, x->B, x->ynorm2, x->pre1, x->pil_bar, dv.H, dv.Hw, nullptr, nullptr, 0.0};
     return launch_estep(dv, ev, st);
   } else if (x->eval == EVO_EVAL_BSC_DIRECT) {
     EVO_REQUIRE(x->W && x->Y, "direct evaluator needs W, Y");

@@ -355,7 +355,7 @@ extern "C" int evo_bsc_prepare(const double *W, const float *Y, int64_t N, int D
 template <class Eval>
 static int launch_lpj(Eval ev, const uint32_t *states, int shared_states, int64_t N, int Sp, int Hw, double *out,
                       int64_t ld, unsigned long long *counters, cudaStream_t st) {
-  size_t smem = ev.smem_bytes();
+  size_t smem = ev.smem_bytes(Sp <= 32 ? 32 : 128);
   if (Sp <= 32) {
     auto k = lpj_kernel<Eval, 32>;
     if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -380,7 +380,7 @@ extern "C" int evo_bsc_lpj(int eval, const uint32_t *states, int shared_states, 
   if (eval == EVO_EVAL_BSC_GRAM) {
     EVO_REQUIRE(G && B && ynorm2, "gram evaluator needs G, B, ynorm2");
     EVO_REQUIRE(mask == nullptr, "gram evaluator needs complete data");
-    BscGramEval ev{G, B, ynorm2, pre1, pil_bar, H, Hw, nullptr, 0.0};
+    BscGramEval ev{G, B, ynorm2, pre1, pil_bar, H, Hw, nullptr, nullptr, 0.0};
     return launch_lpj(ev, states, shared_states, N, Sp, Hw, lpj_out, ld_lpj, reset_counters, st);
   } else if (eval == EVO_EVAL_BSC_DIRECT) {
     EVO_REQUIRE(W && Y, "direct evaluator needs W, Y");

@@ -97,13 +97,16 @@ __device__ __forceinline__ uint32_t urange(uint32_t r, uint32_t n) { return __um
 // ------------------------------------------------------------------------------------------
 __host__ __device__ inline int words_for(int H) { return (H + 31) >> 5; }
 
-__device__ __forceinline__ uint64_t mix64(uint64_t x) {
-  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
-  return x;
-}
-__device__ __forceinline__ uint64_t hash_state(const uint32_t *w, int Hw) {
-  uint64_t h = 0x9E3779B97F4A7C15ULL;
-  for (int i = 0; i < Hw; ++i) h = mix64(h ^ ((uint64_t)w[i] + 0x9E3779B97F4A7C15ULL * (uint64_t)(i + 1)));
+// cheap 32-bit mixing hash (murmur3 finaliser style); equality is always verified on the words
+__device__ __forceinline__ uint32_t hash_state(const uint32_t *w, int Hw) {
+  uint32_t h = 0x9E3779B9u;
+  for (int i = 0; i < Hw; ++i) {
+    uint32_t k = w[i] * 0xCC9E2D51u;
+    k = __funnelshift_l(k, k, 15) * 0x1B873593u;
+    h ^= k;
+    h = __funnelshift_l(h, h, 13) * 5u + 0xE6546B64u;
+  }
+  h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
   return h;
 }
 __device__ __forceinline__ bool same_state(const uint32_t *a, const uint32_t *b, int Hw) {

@@ -49,7 +49,8 @@ struct EstepSmem {
   int *red_i;          // [8]
   int *sh;             // [8] shared scalars
   unsigned char *redisc;  // [S + Ctot]
-  unsigned char *taken;   // [S + Ctot]
+  int *rnk;               // [Ctot] rank of each new state among the new ones (by lpj, descending)
+  int *old_by_rank;       // [S] slot of the r-th worst old state
   unsigned char *status;  // [Cg]
   unsigned char *eval_smem;
 };
@@ -75,8 +76,9 @@ __host__ __device__ inline size_t estep_carve(const EstepDev &a, unsigned char *
   CARVE(parents, int, a.n_parents > 0 ? a.n_parents : 1);
   CARVE(red_i, int, 8);
   CARVE(sh, int, 8);
+  CARVE(rnk, int, a.Ctot > 0 ? a.Ctot : 1);
+  CARVE(old_by_rank, int, a.S);
   CARVE(redisc, unsigned char, U);
-  CARVE(taken, unsigned char, U);
   CARVE(status, unsigned char, a.Cg > 0 ? a.Cg : 1);
 #undef CARVE
   if (s) s->eval_smem = base + off;
@@ -178,7 +180,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       const uint32_t *src = a.states + n * (int64_t)S * Hw;
       for (int i = tid; i < S * Hw; i += T) s.st_uniq[i] = src[i];
       for (int i = tid; i < a.HT; i += T) s.table[i] = TAG_EMPTY;
-      for (int i = tid; i < S + a.Ctot; i += T) { s.redisc[i] = 0; s.taken[i] = 0; }
+      for (int i = tid; i < S + a.Ctot; i += T) s.redisc[i] = 0;
       ev.template setup<T>(n, s.eval_smem);
     }
     gsync<T>();
@@ -227,28 +229,25 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             double key;
             if (a.selection == EVO_SEL_FIT) {
               double w = s.lpj_uniq[s.pool[i]] - shift;
-              key = (w > 0.0) ? log(u) / w : -DBL_MAX;  // Efraimidis-Spirakis weighted sampling w/o replacement
+              // Efraimidis-Spirakis weighted sampling without replacement: keep the largest log(u)/w
+              key = (w > 0.0) ? (double)(__logf((float)u) / (float)w) : -DBL_MAX;
             } else {
               key = u;
             }
             s.keys[i] = key;
           }
           gsync<T>();
-          for (int p = 0; p < take; ++p) {
-            KeyIdx best; best.key = 0; best.idx = -1;
-            for (int i = tid; i < pool_n; i += T) {
-              double k = s.keys[i];
-              if (k != k) continue;  // NaN marks taken
-              KeyIdx c; c.key = k; c.idx = i;
-              best = better(best, c);
+          // the `take` largest keys, by rank counting (strict total order: key desc, index asc)
+          for (int i = tid; i < pool_n; i += T) {
+            double k = s.keys[i];
+            int r = 0;
+            for (int j = 0; j < pool_n; ++j) {
+              double kj = s.keys[j];
+              r += (kj > k) || (kj == k && j < i);
             }
-            best = group_argmax<T>(best, s.red_d, s.red_i);
-            if (tid == 0) {
-              s.parents[p] = best.idx >= 0 ? s.pool[best.idx] : s.pool[0];
-              if (best.idx >= 0) s.keys[best.idx] = nan("");
-            }
-            gsync<T>();
+            if (r < take) s.parents[r] = s.pool[i];
           }
+          gsync<T>();
         }
         // ---- mutation (eas.py:10-135) -----------------------------------------------------------
         const int mut = a.mutation;
@@ -389,27 +388,51 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
     }
 
     // ---- vary_Kn: j-th best new replaces j-th worst old while it is better ----------------------
+    // Ranks by counting (strict total orders: new by lpj desc / index asc, old by lpj asc / slot
+    // asc).  New state of rank r is accepted iff r < M' and it beats the old state of rank r; the
+    // test is monotone in r, so this equals the reference's pairwise walk (utils.py:295-319).
     int n_sub = 0;
     {
       int Mp = U < a.Mprime ? U : a.Mprime;
-      for (int j = 0; j < Mp; ++j) {
-        KeyIdx bn; bn.key = 0; bn.idx = -1;
-        for (int i = tid; i < U; i += T)
-          if (!s.taken[S + i]) { KeyIdx c; c.key = s.lpj_uniq[S + i]; c.idx = i; bn = better(bn, c); }
-        bn = group_argmax<T>(bn, s.red_d, s.red_i);
-        KeyIdx wo; wo.key = 0; wo.idx = -1;
-        for (int i = tid; i < S; i += T)
-          if (!s.taken[i]) { KeyIdx c; c.key = -s.lpj_uniq[i]; c.idx = i; wo = better(wo, c); }
-        wo = group_argmax<T>(wo, s.red_d, s.red_i);
-        if (bn.idx < 0 || wo.idx < 0 || !(bn.key > -wo.key)) break;
-        // replace slot wo.idx by new state bn.idx
-        const uint32_t *src = s.st_uniq + (size_t)(S + bn.idx) * Hw;
-        uint32_t *dst = s.st_uniq + (size_t)wo.idx * Hw;
-        uint32_t *gdst = a.states + (n * (int64_t)S + wo.idx) * Hw;
+      if (Mp > 0) {
+        double mn = DBL_MAX;
+        for (int i = tid; i < S; i += T) mn = fmin(mn, s.lpj_uniq[i]);
+        mn = -group_max<T>(-mn, s.red_d);
+        // only candidates above the worst old state can ever be accepted
+        const double *ln = s.lpj_uniq + S;
+        for (int i = tid; i < U; i += T) {
+          double v = ln[i];
+          int r = Mp;
+          if (v > mn) {
+            r = 0;
+            for (int j = 0; j < U; ++j) { double vj = ln[j]; r += (vj > v) || (vj == v && j < i); }
+          }
+          s.rnk[i] = r;
+        }
+        for (int k = tid; k < S; k += T) {
+          double v = s.lpj_uniq[k];
+          int r = 0;
+          for (int j = 0; j < S; ++j) { double vj = s.lpj_uniq[j]; r += (vj < v) || (vj == v && j < k); }
+          if (r < Mp) s.old_by_rank[r] = k;
+        }
         gsync<T>();
-        for (int w = tid; w < Hw; w += T) { uint32_t v = src[w]; dst[w] = v; gdst[w] = v; }
-        if (tid == 0) { s.lpj_uniq[wo.idx] = bn.key; s.taken[wo.idx] = 1; s.taken[S + bn.idx] = 1; }
-        ++n_sub;
+        int acc_local = 0;
+        for (int i = tid; i < U; i += T) {
+          int r = s.rnk[i];
+          if (r >= Mp) continue;
+          int k = s.old_by_rank[r];
+          double v = ln[i];
+          if (!(v > s.lpj_uniq[k])) continue;
+          const uint32_t *src = s.st_uniq + (size_t)(S + i) * Hw;
+          uint32_t *dst = s.st_uniq + (size_t)k * Hw;
+          uint32_t *gdst = a.states + (n * (int64_t)S + k) * Hw;
+          for (int w = 0; w < Hw; ++w) { uint32_t x = src[w]; dst[w] = x; gdst[w] = x; }
+          s.rnk[i] = -1 - k;  // remembered; lpj written after the barrier (other threads still compare against it)
+          ++acc_local;
+        }
+        gsync<T>();
+        for (int i = tid; i < U; i += T) { int r = s.rnk[i]; if (r < 0) s.lpj_uniq[-1 - r] = ln[i]; }
+        n_sub = group_sum_i<T>(acc_local, s.red_i);
         gsync<T>();
       }
     }

@@ -21,21 +21,27 @@ struct BscGramEval {
   double pre1, pil_bar;
   int H, Hw;
   // per datapoint (set in setup)
-  double *b;  // smem [H]
+  double *b;       // smem [H]
+  uint16_t *idx;   // smem [MAXA][T] active-latent lists, one column per thread
   double yn2;
+  static constexpr int MAXA = 24;
 
-  __host__ __device__ size_t smem_bytes() const { return (size_t)H * sizeof(double); }
+  __host__ __device__ size_t smem_bytes(int T) const {
+    return (size_t)H * sizeof(double) + (size_t)MAXA * T * sizeof(uint16_t);
+  }
   __host__ int threads_hint(int work) const { return work <= 32 ? 32 : (work <= 64 ? 64 : 128); }
 
   template <int T>
   __device__ void setup(int64_t n, unsigned char *smem) {
     b = reinterpret_cast<double *>(smem);
+    idx = reinterpret_cast<uint16_t *>(smem + (size_t)H * sizeof(double));
     const double *src = B + n * (int64_t)H;
     for (int i = threadIdx.x; i < H; i += T) b[i] = __ldg(src + i);
     yn2 = __ldg(ynorm2 + n);
   }
 
-  __device__ __forceinline__ double eval_one(const uint32_t *st) const {
+  // generic form: any number of active latents, no scratch
+  __device__ __forceinline__ double eval_generic(const uint32_t *st) const {
     double sb = 0.0, sg = 0.0;
     int a = 0;
     for (int w1 = 0; w1 < Hw; ++w1) {
@@ -60,13 +66,40 @@ struct BscGramEval {
         sg += __ldg(Gr + h) + 2.0 * t;
       }
     }
-    double resid = yn2 - 2.0 * sb + sg;
-    return pre1 * resid + pil_bar * (double)a;
+    return pre1 * (yn2 - 2.0 * sb + sg) + pil_bar * (double)a;
+  }
+
+  // list form: one pass over the words collects the active latents, then a dense a x a triangle
+  template <int T>
+  __device__ __forceinline__ double eval_one(const uint32_t *st) const {
+    uint16_t *my = idx + threadIdx.x;
+    int a = 0;
+    for (int w = 0; w < Hw; ++w) {
+      uint32_t m = st[w];
+      while (m) {
+        int bp = __ffs(m) - 1;
+        m &= m - 1;
+        if (a < MAXA) my[a * T] = (uint16_t)((w << 5) + bp);
+        ++a;
+      }
+    }
+    if (a > MAXA) return eval_generic(st);
+    double sb = 0.0, sg = 0.0;
+    for (int i = 0; i < a; ++i) {
+      int h = my[i * T];
+      sb += b[h];
+      const double *Gr = G + (int64_t)h * H;
+      double t = 0.0;
+#pragma unroll 4
+      for (int j = 0; j < i; ++j) t += __ldg(Gr + my[j * T]);
+      sg += __ldg(Gr + h) + 2.0 * t;
+    }
+    return pre1 * (yn2 - 2.0 * sb + sg) + pil_bar * (double)a;
   }
 
   template <int T>
   __device__ void eval_batch(const uint32_t *st, int cnt, double *out, unsigned &flags) const {
-    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one(st + (size_t)i * Hw), flags);
+    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one<T>(st + (size_t)i * Hw), flags);
   }
   __device__ double eval_zero(unsigned &flags) const { return lpj_sanitise(pre1 * yn2, flags); }
 };
@@ -86,7 +119,7 @@ struct BscDirectEval {
   uint8_t *m;      // smem [D]
   double yn2;
 
-  __host__ __device__ size_t smem_bytes() const { return (size_t)D * sizeof(double) + (((size_t)D + 7) & ~(size_t)7); }
+  __host__ __device__ size_t smem_bytes(int) const { return (size_t)D * sizeof(double) + (((size_t)D + 7) & ~(size_t)7); }
   __host__ int threads_hint(int work) const { return work <= 32 ? 32 : (work <= 64 ? 64 : 128); }
 
   template <int T>

@@ -50,9 +50,10 @@ def test_lpj_fixture_direct_and_gram():
     # per-datapoint reference signature
     for n in range(N):
         got = m.log_pseudo_joint(th, {"this_states": states[n]}, {"this_y": Y[n], "this_x_infr": X[n]})
-        assert P.maxrel(got, z["lpj"][n]) < 1e-12
+        # the fixture's y is float64; the device stores y as float32 (6e-8 relative input rounding)
+        assert P.maxrel(got, z["lpj"][n]) < 1e-6
         got0 = m.log_pseudo_joint_permanent_states(th, {}, {"this_y": Y[n], "this_x_infr": X[n]})
-        assert abs(got0[0] - z["lpj_allzero"][n]) <= 1e-12 * abs(z["lpj_allzero"][n])
+        assert abs(got0[0] - z["lpj_allzero"][n]) <= 1e-6 * abs(z["lpj_allzero"][n])
     # batched: Gram form on the complete rows equals the direct form
     rows = [n for n in range(N) if X[n].all()]
     data = {"y": Y[rows].astype(np.float32).astype(np.float64), "x_infr": X[rows]}
