@@ -38,6 +38,20 @@ class EstepArgs(C.Structure):
     ]
 
 
+class Es3cStatsArgs(C.Structure):
+    """Mirror of `evo_es3c_stats_args` (include/evo_b200.h)."""
+
+    _fields_ = [
+        ("N", C.c_int64),
+        ("D", C.c_int32), ("H", C.c_int32), ("S", C.c_int32), ("S_perm", C.c_int32), ("learn_psi", C.c_int32),
+        ("_pad", C.c_int32),
+        ("states", C.c_void_p), ("lpj", C.c_void_p), ("Y", C.c_void_p), ("mask", C.c_void_p),
+        ("recon_keep", C.c_void_p), ("G", C.c_void_p), ("B", C.c_void_p), ("ynorm2", C.c_void_p),
+        ("Wt", C.c_void_p), ("Psi", C.c_void_p), ("mus", C.c_void_p),
+        ("sigma2", C.c_double), ("stats", C.c_void_p), ("Yrec", C.c_void_p),
+    ]
+
+
 _vp, _i, _i64, _d, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_uint64
 
 SIGNATURES = {
@@ -54,6 +68,9 @@ SIGNATURES = {
     "evo_select_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "evo_free_energy": (_i, [_vp, _i64, _i, _i64, _vp, _vp]),
     "evo_bsc_suffstats": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp]),
+    "evo_es3c_set_scratch": (_i, [_vp, _i]),
+    "evo_es3c_lpj": (_i, [_vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _vp, _i64, _vp, _vp]),
+    "evo_es3c_suffstats": (_i, [C.POINTER(Es3cStatsArgs), _vp]),
     "evo_bsc_reconstruct": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp]),
 }
 

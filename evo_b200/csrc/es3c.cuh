@@ -1,7 +1,265 @@
-// ES3C (spike-and-slab) evaluator -- see es3c.cu
+// ES3C (spike-and-slab sparse coding, reference class SSSC) -- warp-per-state small dense systems.
+//
+// For a state with support A (a = |A| <= 32) the reference (evo/models/sssc.py:242-326) forms
+//   M = W_A' W_A / s2 + Psi_A^-1,  Lambda = M^-1,  C_det = log|det M| + log|det Psi_A|,
+//   lpj = -1/2 (C_det + r' C^-1 r) + sum_{h in A} pil_bar_h,   r = y_obs - W_A mu_A.
+// Here the same numbers come from N = I + (1/s2) G_AA Psi_A  (M = N Psi_A^-1, so C_det = log|det N|,
+// Lambda = Psi_A N^-1 and r'C^-1 r = |r|^2/s2 - v' Lambda v with v = W_A' r / s2): one LU with partial
+// pivoting per state, no inverse of Psi_A, valid for the indefinite Psi the reference's element-wise
+// update can produce.  G_AA = W_A' W_A over the observed rows: gathered from the shared
+// G = W'W for complete data, accumulated from W' rows under the datapoint's mask otherwise.
 #pragma once
 #include "common.cuh"
 #include "estep.cuh"
+
 namespace evo {
+
+struct Es3cEval {
+  // complete data
+  const double *G;       // [H][H]
+  const double *B;       // [N][H]  Y W
+  const double *ynorm2;  // [N]
+  // incomplete data
+  const double *Wt;      // [H][D]  W'
+  const float *Y;        // [N][D]  (0 where masked)
+  const uint8_t *mask;   // [N][D]
+  // model
+  const double *Psi, *mus, *pil_bar;  // [H][H], [H], [H]
+  double s2i;
+  int D, H, Hw, masked;
+  double *scratch;       // global per-warp workspaces for 16 < a <= 32 (or NULL)
+  int scratch_warps;     // capacity of `scratch` in warps
+  // per datapoint (setup)
+  double *vec;           // smem: b [H] (complete) or y [D] (incomplete)
+  uint8_t *m;            // smem [D] (incomplete)
+  unsigned char *wsm;    // smem per-warp area base
+  double yn2;
+
+  static constexpr int AS = 16, LDS = 17;   // shared-memory path
+  static constexpr int AG = 32, LDGL = 33;  // global-scratch path
+  static constexpr size_t WARP_SMEM = 64 + 3 * AS * LDS * sizeof(double);
+  static constexpr size_t WARP_SCRATCH = 3 * AG * LDGL;  // doubles
+
+  __host__ __device__ size_t head_bytes() const {
+    return masked ? align8((size_t)D * sizeof(double)) + align8((size_t)D) : align8((size_t)H * sizeof(double));
+  }
+  __host__ __device__ size_t smem_bytes(int T) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM; }
+  __host__ int threads_hint(int work) const { return work <= 64 ? 64 : 128; }
+
+  template <int T>
+  __device__ void setup(int64_t n, unsigned char *smem) {
+    vec = reinterpret_cast<double *>(smem);
+    if (masked) {
+      m = smem + align8((size_t)D * sizeof(double));
+      for (int d = threadIdx.x; d < D; d += T) {
+        uint8_t ok = mask[n * (int64_t)D + d];
+        m[d] = ok;
+        vec[d] = ok ? (double)Y[n * (int64_t)D + d] : 0.0;
+      }
+    } else {
+      const double *src = B + n * (int64_t)H;
+      for (int i = threadIdx.x; i < H; i += T) vec[i] = __ldg(src + i);
+      yn2 = __ldg(ynorm2 + n);
+    }
+    wsm = smem + head_bytes();
+  }
+
+  // |y_obs|^2 for incomplete data (needs the loaded y); call after the post-setup barrier
+  __device__ double masked_yn2() const {
+    double s = 0.0;
+    for (int d = (threadIdx.x & 31); d < D; d += 32) s += vec[d] * vec[d];
+    return warp_sum(s);
+  }
+
+  // ---- active-latent list of one state, warp-cooperative; returns a (may exceed 32) -------------
+  __device__ __forceinline__ int active_list(const uint32_t *st, uint16_t *idx) const {
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    for (int w0 = 0; w0 < Hw; w0 += 32) {
+      uint32_t word = (w0 + lane < Hw) ? st[w0 + lane] : 0u;
+      int c = __popc(word);
+      int pre = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += t; }
+      int pos = base + pre - c;
+      while (word) {
+        int bp = __ffs(word) - 1;
+        word &= word - 1;
+        if (pos < 32) idx[pos] = (uint16_t)(((w0 + lane) << 5) + bp);
+        ++pos;
+      }
+      base += __shfl_sync(0xffffffffu, pre, 31);
+    }
+    __syncwarp();
+    return base;
+  }
+
+  // workspaces for a state of size a: three matrices with leading dimension ld
+  __device__ __forceinline__ bool workspace(int a, uint16_t *&idx, double *&A1, double *&A2, double *&A3, int &ld) const {
+    const int warp = threadIdx.x >> 5;
+    unsigned char *base = wsm + (size_t)warp * WARP_SMEM;
+    idx = reinterpret_cast<uint16_t *>(base);
+    if (a <= AS) {
+      A1 = reinterpret_cast<double *>(base + 64);
+      A2 = A1 + AS * LDS;
+      A3 = A2 + AS * LDS;
+      ld = LDS;
+      return true;
+    }
+    int gw = blockIdx.x * (blockDim.x >> 5) + warp;
+    if (a > AG || scratch == nullptr || gw >= scratch_warps) return false;
+    A1 = scratch + (size_t)gw * WARP_SCRATCH;
+    A2 = A1 + AG * LDGL;
+    A3 = A2 + AG * LDGL;
+    ld = LDGL;
+    return true;
+  }
+
+  // Gathers G_AA -> A1, Psi_AA -> A2 and returns this lane's b_i (W_A' y)_i; lane i <-> latent idx[i].
+  __device__ __forceinline__ double gather(int a, const uint16_t *idx, double *A1, double *A2, int ld, double &ynorm) const {
+    const int lane = threadIdx.x & 31;
+    double bi = 0.0;
+    if (!masked) {
+      if (lane < a) {
+        int h = idx[lane];
+        const double *Gr = G + (int64_t)h * H;
+        for (int l = 0; l < a; ++l) A1[lane * ld + l] = __ldg(Gr + idx[l]);
+        bi = vec[h];
+      }
+      ynorm = yn2;
+    } else {
+      for (int i = 0; i < a; ++i) {
+        const double *wi = Wt + (int64_t)idx[i] * D;
+        double pb = 0.0;
+        for (int d = lane; d < D; d += 32) pb += __ldg(wi + d) * vec[d];
+        pb = warp_sum(pb);
+        if (lane == i) bi = pb;
+        for (int j = 0; j <= i; ++j) {
+          const double *wj = Wt + (int64_t)idx[j] * D;
+          double p = 0.0;
+          for (int d = lane; d < D; d += 32)
+            if (m[d]) p += __ldg(wi + d) * __ldg(wj + d);
+          p = warp_sum(p);
+          if (lane == 0) { A1[i * ld + j] = p; A1[j * ld + i] = p; }
+        }
+      }
+      ynorm = yn2;
+    }
+    if (lane < a) {
+      const double *Pr = Psi + (int64_t)idx[lane] * H;
+      for (int l = 0; l < a; ++l) A2[lane * ld + l] = __ldg(Pr + idx[l]);
+    }
+    __syncwarp();
+    return bi;
+  }
+
+  // LU with partial pivoting of the a x a matrix A3 (lane = row), solving A3 x = rhs in place.
+  // Returns log|det| ; x_i is left in `rhs` of lane i.
+  __device__ __forceinline__ double lu_solve(int a, double *A3, int ld, double &rhs) const {
+    const int lane = threadIdx.x & 31;
+    const bool act = lane < a;
+    double logdet = 0.0;
+    for (int k = 0; k < a; ++k) {
+      double mag = (act && lane >= k) ? fabs(A3[lane * ld + k]) : -1.0;
+      int p = lane;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        double om = __shfl_xor_sync(0xffffffffu, mag, o);
+        int op = __shfl_xor_sync(0xffffffffu, p, o);
+        if (om > mag || (om == mag && op < p)) { mag = om; p = op; }
+      }
+      if (p != k) {
+        if (act) { double t = A3[k * ld + lane]; A3[k * ld + lane] = A3[p * ld + lane]; A3[p * ld + lane] = t; }
+        double rk = __shfl_sync(0xffffffffu, rhs, k), rp = __shfl_sync(0xffffffffu, rhs, p);
+        if (lane == k) rhs = rp;
+        if (lane == p) rhs = rk;
+      }
+      __syncwarp();
+      double piv = A3[k * ld + k];
+      logdet += log(fabs(piv));
+      double rhs_k = __shfl_sync(0xffffffffu, rhs, k);
+      if (act && lane > k) {
+        double f = A3[lane * ld + k] / piv;
+        for (int c = k + 1; c < a; ++c) A3[lane * ld + c] -= f * A3[k * ld + c];
+        rhs -= f * rhs_k;
+      }
+      __syncwarp();
+    }
+    for (int k = a - 1; k >= 0; --k) {
+      double xk = __shfl_sync(0xffffffffu, rhs, k) / A3[k * ld + k];
+      if (lane == k) rhs = xk;
+      if (act && lane < k) rhs -= A3[lane * ld + k] * xk;
+    }
+    return logdet;
+  }
+
+  // N = I + s2i A1 A2 -> A3 ; also v_i, |r|^2 and w = Psi_A' v  (v' Lambda v = w . N^-1 v)
+  __device__ __forceinline__ void build(int a, const uint16_t *idx, const double *A1, const double *A2, double *A3, int ld,
+                                        double bi, double ynorm, double &v, double &rn2, double &w, double &mu) const {
+    const int lane = threadIdx.x & 31;
+    const bool act = lane < a;
+    mu = act ? __ldg(mus + idx[lane]) : 0.0;
+    double t = 0.0;
+    for (int l = 0; l < a; ++l) {
+      double ml = __shfl_sync(0xffffffffu, mu, l);
+      if (act) t += A1[lane * ld + l] * ml;
+    }
+    v = act ? s2i * (bi - t) : 0.0;
+    rn2 = ynorm + warp_sum(act ? mu * (t - 2.0 * bi) : 0.0);
+    w = 0.0;
+    for (int l = 0; l < a; ++l) {
+      double vl = __shfl_sync(0xffffffffu, v, l);
+      if (act) w += A2[l * ld + lane] * vl;  // (Psi_A' v)_i: Psi need not be symmetric after the reference's update
+    }
+    if (act) {
+      for (int j = 0; j < a; ++j) {
+        double acc = 0.0;
+        for (int l = 0; l < a; ++l) acc += A1[lane * ld + l] * A2[l * ld + j];
+        A3[lane * ld + j] = (lane == j ? 1.0 : 0.0) + s2i * acc;
+      }
+    }
+    __syncwarp();
+  }
+
+  // lpj of one state, all 32 lanes of the warp cooperate; result valid in every lane
+  __device__ __forceinline__ double warp_lpj(const uint32_t *st) const {
+    const int lane = threadIdx.x & 31;
+    uint16_t *idx;
+    double *A1, *A2, *A3;
+    int ld;
+    workspace(0, idx, A1, A2, A3, ld);
+    int a = active_list(st, idx);
+    if (a == 0) return -0.5 * s2i * yn2;
+    if (!workspace(a, idx, A1, A2, A3, ld)) return nan("");  // more than 32 active latents: rejected
+    double ynorm;
+    double bi = gather(a, idx, A1, A2, ld, ynorm);
+    double v, rn2, w, mu;
+    build(a, idx, A1, A2, A3, ld, bi, ynorm, v, rn2, w, mu);
+    double x = v;
+    double logdet = lu_solve(a, A3, ld, x);
+    const bool act = lane < a;
+    double quad = s2i * rn2 - warp_sum(act ? w * x : 0.0);
+    double prior = warp_sum(act ? __ldg(pil_bar + idx[lane]) : 0.0);
+    __syncwarp();
+    return -0.5 * (logdet + quad) + prior;
+  }
+
+  template <int T>
+  __device__ void eval_batch(const uint32_t *st, int cnt, double *out, unsigned &flags) {
+    if (masked) yn2 = masked_yn2();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = warp; i < cnt; i += T / 32) {
+      double v = warp_lpj(st + (size_t)i * Hw);
+      v = lpj_sanitise(v, flags);
+      if (lane == 0) out[i] = v;
+    }
+  }
+  __device__ double eval_zero(unsigned &flags) {
+    if (masked) yn2 = masked_yn2();
+    return lpj_sanitise(-0.5 * s2i * yn2, flags);
+  }
+};
+
 int es3c_launch_estep(const EstepDev &dv, const evo_estep_args *x, cudaStream_t st);
-}
+
+}  // namespace evo

@@ -164,4 +164,32 @@ struct BscDirectEval {
   }
 };
 
+// ------------------------------------------------------------------------------------------
+// stand-alone lpj (log_pseudo_joint of any evaluator, bsc.py:79-97 / sssc.py:242-326 + lpj_reset_check _models.py:567-596)
+// ------------------------------------------------------------------------------------------
+template <class Eval, int T>
+__global__ void __launch_bounds__(T) lpj_kernel(Eval ev, const uint32_t *__restrict__ states, int shared_states,
+                                                int64_t N, int Sp, int Hw, double *__restrict__ out, int64_t ld,
+                                                unsigned long long *counters) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int red_i[8];
+  unsigned long long c_nan = 0, c_small = 0, c_inf = 0;
+  for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
+    __syncthreads();
+    ev.template setup<T>(n, smem_raw);
+    __syncthreads();
+    unsigned fl = 0;
+    const uint32_t *st = shared_states ? states : states + n * (int64_t)Sp * Hw;
+    ev.template eval_batch<T>(st, Sp, out + n * ld, fl);
+    fl = group_or<T>(fl, red_i);
+    if (threadIdx.x == 0 && fl) { if (fl & 1) ++c_nan; else if (fl & 2) ++c_small; else ++c_inf; }
+  }
+  if (threadIdx.x == 0 && counters) {
+    if (c_nan) atomicAdd(counters + 0, c_nan);
+    if (c_small) atomicAdd(counters + 1, c_small);
+    if (c_inf) atomicAdd(counters + 2, c_inf);
+  }
+}
+
+
 }  // namespace evo

@@ -138,6 +138,42 @@ int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double 
                         const uint8_t *recon_keep, const uint8_t *infer_mask, int64_t N, int D, int H,
                         int S, int S_perm, float *Yrec, void *stream);
 
+/* ---- ES3C (class SSSC) ------------------------------------------------------------------------
+ * The E-step is evo_estep with eval = EVO_EVAL_ES3C: complete data uses (G, B, ynorm2) from
+ * evo_bsc_prepare, incomplete data uses Wt = W' [H][D] passed in `W`, plus pil_bar_h, mus, Psi, sigma2
+ * (sssc.py:242-366).  States with more than 32 active latents are rejected (lowest lpj).
+ * `es3c_scratch` (f64, es3c_scratch_warps * 3168 doubles) serves states with 17..32 active latents. */
+int evo_es3c_set_scratch(double *scratch, int warps);
+/* SSSC.log_pseudo_joint (sssc.py:242-326) for states [N][Sp][Hw] (or one shared [Sp][Hw] table) */
+int evo_es3c_lpj(const uint32_t *states, int shared_states, int64_t N, int Sp, int D, int H, const double *Wt,
+                 const float *Y, const uint8_t *mask, const double *G, const double *B, const double *ynorm2,
+                 const double *Psi, const double *mus, const double *pil_bar_h, double sigma2, double *lpj_out,
+                 int64_t ld_lpj, unsigned long long *reset_counters, void *stream);
+
+/* Sufficient statistics + data estimator of SSSC.EM_step (sssc.py:553-646) over the post-selection
+ * K sets.  stats (f64, accumulated, caller zeroes), H2 = H*H:
+ *   [sum_s H | sum_sz H | sum_ss H2 | sum_szsz H2 | sum_s_sz H2 | sum_szsz_outer H2 | WpT H*D | trace 1]
+ * sum_s_sz only if learn_psi; sum_szsz_outer for complete data, trace = sum_n |W_obs <sz>_n|^2 for
+ * incomplete data (the reference's D x D accumulator is only ever traced, sssc.py:752).
+ * Yrec (may be NULL): y_rec[n][d] = recon_keep[n][d] ? y : (W <sz>_n)_d  (sssc.py:614-627); with
+ * incomplete data WpT accumulates y_rec (sssc.py:630-634). */
+typedef struct evo_es3c_stats_args {
+  int64_t N;
+  int32_t D, H, S, S_perm, learn_psi, _pad;
+  const uint32_t *states; /* [N][S][Hw] */
+  const double *lpj;      /* [N][S+S_perm] */
+  const float *Y;         /* [N][D] (0 where masked) */
+  const uint8_t *mask;    /* [N][D] or NULL */
+  const uint8_t *recon_keep; /* [N][D] or NULL (= reconstruct every entry) */
+  const double *G, *B, *ynorm2; /* complete data */
+  const double *Wt;       /* [H][D] */
+  const double *Psi, *mus;
+  double sigma2;
+  double *stats;
+  float *Yrec;            /* [N][D] or NULL */
+} evo_es3c_stats_args;
+int evo_es3c_suffstats(const evo_es3c_stats_args *args, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

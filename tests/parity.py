@@ -146,3 +146,90 @@ def run_bsc_parity_case(path, iters=None):
             res["yrec_err_ref"] = maxrel(gdata["y_reconstructed"], c["y_reconstructed"])
     res["iters"] = iters
     return res
+
+
+# ---------------------------------------------------------------------------------------------
+# ES3C (SSSC)
+# ---------------------------------------------------------------------------------------------
+PKEYS = ("W", "pies", "mus", "Psi", "sigma2")
+
+
+def _sssc_theta0(c):
+    return {k: np.array(c[k + "0"]) for k in PKEYS}
+
+
+def run_oracle_sssc_case(c, iters):
+    from oracle import sssc as OS
+    from oracle import variational as OV
+
+    D, H, N, S = int(c["D"]), int(c["H"]), int(c["N"]), int(c["S"])
+    perm = permanent_of(c)
+    cont = OV.init_states(1, S, H, str(c["selection"]), str(c["mutation"]), int(c["P"]), int(c["C"]), int(c["G"]),
+                          bitflip_prob=1.0 / H, permanent=copy.deepcopy(perm))
+    cont["ss"] = c["ss0_bool"].copy()
+    cont["lpj"] = np.empty((N, S + cont["S_perm"]))
+    rep = OracleReplay(cont, c["children_bool"], c["child_count"])
+    data = {"y": c["Y"].copy(), "x_infr": c["X"].copy(), "x": c["Xrec"].copy()}
+    th = _sssc_theta0(c)
+    to_learn = tuple(str(c["to_learn"]).split(","))
+    out = []
+    for it in range(iters):
+        F, a, b, th = OS.em_step(th, cont, data, D, H, S, to_learn=to_learn, do_reconstruction=True,
+                                 reference_quirks=False)
+        out.append((F, a, b, {k: np.array(th[k]) for k in PKEYS}))
+        rep.next_iteration()
+    return out, cont, data
+
+
+def run_gpu_sssc_case(c, iters):
+    import torch
+
+    from evo_b200.sssc import SSSC
+    from evo_b200.variational import init_states
+
+    D, H, N, S = int(c["D"]), int(c["H"]), int(c["N"]), int(c["S"])
+    perm = permanent_of(c)
+    to_learn = tuple(str(c["to_learn"]).split(","))
+    model = SSSC(D, H, S, to_learn=to_learn)
+    cont = init_states(N, S, H, str(c["selection"]), str(c["mutation"]), int(c["P"]), int(c["C"]), int(c["G"]),
+                       bitflip_prob=1.0 / H, permanent=copy.deepcopy(perm))
+    cont["ss"] = c["ss0_bool"]
+    data = {"y": c["Y"].copy(), "x_infr": c["X"].copy(), "x": c["Xrec"].copy()}
+    th = _sssc_theta0(c)
+    out = []
+    for it in range(iters):
+        cont["inject"] = (c["children_bool"][it], c["child_count"][it])
+        F, a, b, th = model.step(th, cont, data, do_reconstruction=True)
+        out.append((F, a, b, {k: np.array(th[k]) for k in PKEYS}))
+    torch.cuda.synchronize()
+    return out, cont, data
+
+
+def run_sssc_parity_case(path, iters=None):
+    c = load_case(path)
+    total = int(c["iters"])
+    iters = total if iters is None else min(iters, total)
+    gpu, gcont, gdata = run_gpu_sssc_case(c, iters)
+    ora, ocont, odata = run_oracle_sssc_case(c, iters)
+    res = {"F_err": 0.0, "F_err_ref": 0.0, "count_err": 0.0}
+    for k in PKEYS:
+        res[k + "_err"] = 0.0
+        res[k + "_err_ref"] = 0.0
+    for it in range(iters):
+        Fg, ag, bg, tg = gpu[it]
+        Fo, ao, bo, to = ora[it]
+        res["F_err"] = max(res["F_err"], abs(Fg - Fo) / abs(Fo))
+        res["F_err_ref"] = max(res["F_err_ref"], abs(Fg - c["F"][it]) / abs(c["F"][it]))
+        res["count_err"] = max(res["count_err"], abs(ag - ao), abs(bg - bo))
+        for k in PKEYS:
+            res[k + "_err"] = max(res[k + "_err"], maxrel(tg[k], to[k]))
+            res[k + "_err_ref"] = max(res[k + "_err_ref"], maxrel(tg[k], c[k][it]))
+    gss = gcont["ss"]
+    res["ss_equal"] = bool(np.array_equal(gss, ocont["ss"]))
+    res["lpj_err"] = maxrel(gcont["lpj"], ocont["lpj"])
+    res["yrec_err"] = maxrel(gdata["y_reconstructed"], odata["y_reconstructed"])
+    if iters == total:
+        res["ss_equal_ref"] = bool(np.array_equal(gss, c["ss_final_bool"]))
+        res["lpj_err_ref"] = maxrel(gcont["lpj"], c["lpj_final"])
+    res["iters"] = iters
+    return res

@@ -82,3 +82,33 @@ def test_pack_unpack_oracle():
         one = np.zeros((1, H), bool)
         one[0, h] = True
         assert OV.pack_states(one)[0, h // 32] == np.uint32(1 << (h % 32))
+
+
+# ---- ES3C (SSSC) oracle vs reference fixtures ------------------------------------------------------
+@pytest.mark.parametrize("name", ["sssc_exact", "sssc_replay", "sssc_missing", "sssc_allzero_h40"])
+def test_sssc_oracle_replay_reproduces_reference(name):
+    c = P.load_case(os.path.join(P.GOLDEN, name + ".npz"))
+    iters = int(c["iters"])
+    out, cont, data = P.run_oracle_sssc_case(c, iters)
+    for it in range(iters):
+        F, a, b, th = out[it]
+        assert abs(F - c["F"][it]) <= 1e-10 * abs(c["F"][it])
+        assert abs(a - c["S_nunique"][it]) < 1e-12 and abs(b - c["S_sub"][it]) < 1e-12
+        for k in P.PKEYS:
+            assert P.maxrel(th[k], c[k][it]) < 1e-7, k
+    assert np.array_equal(cont["ss"], c["ss_final_bool"])
+    assert P.maxrel(cont["lpj"], c["lpj_final"]) < 1e-9
+    assert P.maxrel(data["y_reconstructed"], c["y_reconstructed"]) < 1e-9
+
+
+def test_sssc_oracle_lpj_fixture():
+    from oracle import sssc as OS
+
+    z = np.load(os.path.join(P.GOLDEN, "sssc_lpj.npz"))
+    Y, X, states = z["Y"], z["X"], z["states"]
+    th = OS.precompute({k: np.array(z[k]) for k in P.PKEYS}, Y.shape[1], Y.shape[0], int(X.sum()))
+    assert abs(th["ljc"] - z["ljc"]) <= 1e-12 * abs(z["ljc"])
+    for n in range(Y.shape[0]):
+        got = OS.lpj_states(states[n], th, Y[n], X[n])[0]
+        assert P.maxrel(got, z["lpj"][n]) < 1e-11
+        assert abs(OS.lpj_allzero(Y[n], X[n], th["sigma2_inv"])[0] - z["lpj_allzero"][n]) <= 1e-13 * abs(z["lpj_allzero"][n])
