@@ -153,11 +153,13 @@ def algorithmic_bytes(w, N, U_mean):
     Hw = (H + 31) // 32
     return {
         # (a') + (c): read y_n, read every packed state evaluated, write every lpj
-        "evo_estep": N * (4 * D + (K + U_mean) * (4 * Hw + 4)),
+        "evo_estep": N * (4 * D + ((D + 7) // 8 if w.get("missing") else 0) + (K + U_mean) * (4 * Hw + 4)),
         # tables of the Gram form: read Y, write B = Y W (f64)
         "evo_bsc_prepare": N * (4 * D + 8 * H),
         # (d): read K^n + lpj + y_n, one pass over the outputs
         "evo_bsc_suffstats": N * (K * (4 * Hw + 4) + 4 * D) + 8 * (H * D + H * H),
+        # ES3C (d): as above + mask bits + y_rec write, one pass over the four H x H + H x D outputs
+        "evo_es3c_suffstats": N * (K * (4 * Hw + 4) + 4 * D + (D + 7) // 8 + 4 * D) + 8 * (H * D + 4 * H * H),
     }
 
 
@@ -308,7 +310,7 @@ def run_ours(args):
         "kernels": {k: {"launches": c, "mean_ms": t, "share": c * t / tot_t} for k, (c, t) in kern.items()},
         "roofline": roof, "clocks": clocks,
     }
-    if not args.no_cpu and w["model"] == "bsc":
+    if not args.no_cpu:
         line["cpu_baseline"] = cpu_port(args.workload, steps=1, warmup=1)
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -329,6 +331,7 @@ def cpu_worker(args):
 
     warnings.simplefilter("ignore")
     from oracle import bsc as OB
+    from oracle import sssc as OS
     from oracle import variational as OV
 
     w = WORKLOADS[args.workload]
@@ -337,18 +340,30 @@ def cpu_worker(args):
     Y, X = synth_host(w, n, 1000 + args.cpu_worker)
     Y = Y.astype(np.float64)
     np.random.seed(1 + args.cpu_worker)
-    mean = Y.mean(0)
-    sigma = float(np.sqrt(((Y - mean) ** 2).mean(0).sum() / D))
-    theta = {"W": mean[:, None] + np.random.normal(scale=sigma / 4.0, size=(D, H)), "pi": 1.0 / H, "sigma": sigma}
+    obs = np.ones_like(Y, dtype=bool) if X is None else X
+    mean = (Y * obs).sum(0) / np.maximum(obs.sum(0), 1)
+    sigma = float(np.sqrt((((Y - mean) * obs) ** 2).sum() / obs.sum()))
+    W0 = mean[:, None] + np.random.normal(scale=sigma / 4.0, size=(D, H))
     sel, mut, P, C, G = w["ea"]
     cont = OV.init_states(n, K, H, sel, mut, P, C, G)
-    data = {"y": Y, "x_infr": np.ones_like(Y, dtype=bool)}
+    if w["model"] == "bsc":
+        theta = {"W": W0, "pi": 1.0 / H, "sigma": sigma}
+        data = {"y": Y, "x_infr": obs}
+        step = lambda th: OB.step(th, cont, data, D, H, K)
+    else:
+        learn = ("W", "pies", "sigma2") if X is not None else ("W", "pies", "mus", "sigma2", "Psi")
+        theta = {"W": W0, "pies": np.random.uniform(0.1, 0.5, size=H),
+                 "mus": np.ones(H) if X is not None else np.random.normal(0, 1, H),
+                 "Psi": np.eye(H), "sigma2": np.float64(sigma ** 2)}
+        Yn = np.where(obs, Y, np.nan)
+        data = {"y": Yn, "x_infr": obs, "x": obs if X is not None else np.zeros_like(obs)}
+        step = lambda th: OS.em_step(th, cont, data, D, H, K, to_learn=learn, do_reconstruction=True)
     for _ in range(args.warmup):
-        OB.step(theta, cont, data, D, H, K)
+        step(theta)
     t0 = time.perf_counter()
     lpj = 0.0
     for _ in range(args.steps):
-        F, nu, nsub, theta = OB.step(theta, cont, data, D, H, K)
+        F, nu, nsub, theta = step(theta)
         lpj += n * K + nu * n
     print(json.dumps({"lpj": lpj, "sec": time.perf_counter() - t0, "F": F}), flush=True)
 
@@ -377,9 +392,6 @@ def run_reference(args):
     if rank != 0:
         return
     w = WORKLOADS[args.workload]
-    if w["model"] != "bsc" and not os.path.exists(os.path.join(ROOT, "oracle", "sssc.py")):
-        print(json.dumps({"impl": "reference", "unavailable": "no CPU oracle for this model yet"}))
-        return
     total = max(1, args.steps + args.warmup)
     n_sub = max(16, int(CPU_SAMPLE[args.workload] * 2 / total))
     cb = cpu_port(args.workload, steps=args.steps, warmup=args.warmup, n_sub=n_sub)
