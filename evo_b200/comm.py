@@ -22,9 +22,10 @@ def shard_bounds(N, R, r):
 
 
 class Comm:
-    def __init__(self, group=None):
+    def __init__(self, group=None, single=False):
+        """`single=True` gives a world-size-1 communicator even inside an initialised process group."""
         self.group = group
-        self._on = dist.is_available() and dist.is_initialized()
+        self._on = dist.is_available() and dist.is_initialized() and not single
         self.rank = dist.get_rank(group) if self._on else 0
         self.size = dist.get_world_size(group) if self._on else 1
 
