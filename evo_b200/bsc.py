@@ -112,15 +112,22 @@ class BSC(Model):
         return None
 
     # ---- E-step (_models.py:454-565) -----------------------------------------------------------------
-    def E_step(self, model_params, my_suff_stat, my_data):
+    def _estep_enqueue(self, model_params, my_suff_stat, my_data):
         dd = self.device_data(my_data)
         self.E_step_precompute(model_params, my_suff_stat, my_data)
         self._tables(model_params, dd)
         acc = torch.zeros(ACC_LEN, dtype=torch.float64, device=self.device)
         self._estep_launch(my_suff_stat, dd, acc, lambda a: self._fill_eval(a, model_params, dd))
         dd.cache["acc"] = acc
+        return dd, acc
+
+    def E_step(self, model_params, my_suff_stat, my_data):
+        dd, acc = self._estep_enqueue(model_params, my_suff_stat, my_data)
         red = acc.clone()
         self.comm.allreduce_(red)
+        return self._estep_finish(red, model_params, my_suff_stat, dd)
+
+    def _estep_finish(self, red, model_params, my_suff_stat, dd):
         r = red.cpu().numpy()
         for i, k in enumerate(("reset_lpj_isnan", "reset_lpj_smaller_eps_lpj", "reset_lpj_isinf")):
             dict.__setitem__(my_suff_stat, k, int(r[3 + i]))
@@ -213,8 +220,22 @@ class BSC(Model):
             my_data["y_reconstructed"] = dd.Yrec.double().cpu().numpy()
 
     # ---- M-step (bsc.py:128-277) ------------------------------------------------------------------------
-    def M_step(self, model_params, my_suff_stat, my_data):
-        dd = self.device_data(my_data)
+    def step(self, model_params, my_suff_stat, my_data, do_reconstruction=False):
+        """Model.step (_models.py:162-203) with the E-step scalars riding in the tail of the statistics
+        buffer: ONE all-reduce and one host read per EM iteration."""
+        model_params = self.check_params(model_params)
+        if len(self.to_learn) == 0:
+            return Model.step(self, model_params, my_suff_stat, my_data, do_reconstruction)
+        dd, acc = self._estep_enqueue(model_params, my_suff_stat, my_data)
+        if do_reconstruction:
+            self.reconstruct(my_data, my_suff_stat, model_params)
+        stats = self._stats_enqueue(model_params, my_suff_stat, dd)
+        stats[-ACC_LEN:] = acc
+        self.comm.allreduce_(stats)
+        F, S_nunique, S_sub = self._estep_finish(stats[-ACC_LEN:], model_params, my_suff_stat, dd)
+        return F, S_nunique, S_sub, self._solve_update(model_params, my_suff_stat, dd, stats)
+
+    def _stats_enqueue(self, model_params, my_suff_stat, dd):
         D, H = self.D, self.H
         ss = my_suff_stat
         if dd.incomplete:
@@ -222,11 +243,21 @@ class BSC(Model):
             Ym = dd.Yrec
         else:
             Ym = dd.Y
-        stats = torch.zeros(H * D + H * H + H + 1, dtype=torch.float64, device=self.device)
+        stats = torch.zeros(H * D + H * H + H + 1 + ACC_LEN, dtype=torch.float64, device=self.device)
         self._call("evo_bsc_suffstats", _lib.ptr(ss["ss_dev"]), _lib.ptr(ss["lpj_dev"]), _lib.ptr(Ym), dd.N, D, H,
                    int(ss["ss_dev"].shape[1]), int(ss["S_perm"]), int(bool(ss["permanent"]["allzero"])),
                    float(model_params["pre1"]), float(model_params["pil_bar"]), _lib.ptr(stats), None)
+        return stats
+
+    def M_step(self, model_params, my_suff_stat, my_data):
+        dd = self.device_data(my_data)
+        stats = self._stats_enqueue(model_params, my_suff_stat, dd)
         self.comm.allreduce_(stats)
+        return self._solve_update(model_params, my_suff_stat, dd, stats)
+
+    def _solve_update(self, model_params, my_suff_stat, dd, stats):
+        D, H = self.D, self.H
+        ss = my_suff_stat
         Wp = stats[: H * D].view(H, D)
         Wq = stats[H * D: H * D + H * H].view(H, H)
         Wq = torch.tril(Wq) + torch.tril(Wq, -1).T
@@ -244,7 +275,7 @@ class BSC(Model):
             model_params["pi"] = float((p.sum() / H).item())
             model_params["pies"] = p.cpu().numpy() if as_numpy else p
         if "sigma" in self.to_learn:
-            sig = float(stats[-1].item())
+            sig = float(stats[H * D + H * H + H].item())
             if dd.incomplete:
                 model_params["sigma"] = float(np.sqrt((sig + dd.n_obs_total * sigma_old ** 2) / N / D))
             else:
