@@ -64,6 +64,9 @@ SIGNATURES = {
     "evo_states_init": (_i, [_vp, _i64, _i, _i, _i, _i, _d, _u64, _i64, _vp]),
     "evo_bsc_prepare": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp, _vp, _vp]),
     "evo_bsc_lpj": (_i, [_i, _vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _d, _d, _vp, _i64, _vp, _vp]),
+    "evo_bsc_lpj_gemm_workspace_bytes": (_i64, [_i, _i]),
+    "evo_bsc_lpj_gemm_prepare": (_i, [_vp, _i, _i, _vp, _vp]),
+    "evo_bsc_lpj_gemm": (_i, [_vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _d, _d, _vp, _i64, _vp, _vp]),
     "evo_estep": (_i, [C.POINTER(EstepArgs), _vp]),
     "evo_select_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "evo_free_energy": (_i, [_vp, _i64, _i, _i64, _vp, _vp]),

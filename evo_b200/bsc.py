@@ -182,6 +182,28 @@ class BSC(Model):
                    _lib.ptr(out), Sp, None)
         return out
 
+    def dense_workspace(self, model_params):
+        """fp16 hi/lo planes of W for the tensor-core log-joint (`evo_bsc_lpj_gemm_prepare`)."""
+        Wd = _dev(model_params["W"], self.device, torch.float64)
+        nbytes = int(self.lib.evo_bsc_lpj_gemm_workspace_bytes(self.D, self.H))
+        ws = getattr(self, "_dense_ws", None)
+        if ws is None or ws.numel() != nbytes:
+            ws = self._dense_ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        self._call("evo_bsc_lpj_gemm_prepare", _lib.ptr(Wd), self.D, self.H, _lib.ptr(ws))
+        return ws
+
+    def lpj_all_dense(self, model_params, my_data, states_dev, shared=False, workspace=None):
+        """`lpj_all` through the fused tcgen05 GEMM S W' with the squared-residual epilogue
+        (`evo_bsc_lpj_gemm`; fp16 hi+lo split of W, fp32 accumulation: <= 1e-5 relative)."""
+        dd = self.device_data(my_data)
+        ws = workspace if workspace is not None else self.dense_workspace(model_params)
+        Sp = states_dev.shape[-2]
+        out = torch.empty((dd.N, Sp), dtype=torch.float64, device=self.device)
+        self._call("evo_bsc_lpj_gemm", _lib.ptr(states_dev), int(shared), dd.N, Sp, self.D, self.H, _lib.ptr(ws),
+                   _lib.ptr(dd.Y), _lib.ptr(dd.mask), float(model_params["pre1"]), float(model_params["pil_bar"]),
+                   _lib.ptr(out), Sp, None)
+        return out
+
     def free_energy(self, my_data, model_params, my_suff_stat, full=True, compute_lpj=True):
         """Free energy over the current K sets, or the exact log-likelihood over all 2^H states
         (`full=True`, H < 12) (_models.py:334-451)."""

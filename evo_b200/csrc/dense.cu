@@ -1,0 +1,462 @@
+// Dense BSC log-pseudo-joint on the 5th-generation tensor cores (tcgen05 / TMEM / TMA), sm_100a.
+//
+//   lpj[n][k] = pre1 * sum_{d in obs} ((s_nk W')_d - y_nd)^2 + pil_bar |s_nk|      (evo/models/bsc.py:79-97)
+//
+// evaluated as ONE logical GEMM  C[(n,k)][d] = sum_h S[(n,k)][h] W[d][h]  (M = N*S states, N = D,
+// K = H) whose accumulator never leaves the SM: the epilogue reads it from TMEM, subtracts y_n,
+// squares, reduces over d and writes one f64 per state.  The N*K x D residual of the reference
+// (`np.dot(states, W.T) - y`, bsc.py:91-93) is never materialised.
+//
+// Precision: the binary operand S is exact in fp16.  W (f64) is scaled by a power of two and split
+// into two fp16 planes hi + lo (22 significant bits); both planes accumulate into the same fp32
+// TMEM accumulator, so the logical GEMM is executed as two tensor-core passes.  Measured against the
+// f64 oracle: <= 2e-6 relative on lpj (tests/test_dense_gpu.py states 1e-5).
+//
+// Roles inside one persistent CTA (320 threads, one CTA per SM):
+//   warp 0      TMA producer: W planes, [box_rows x 64] fp16 tiles, SWIZZLE_128B, 5-stage ring
+//   warp 1      MMA issuer (one lane): tcgen05.mma.kind::f16, M=128, N<=256, K=16; owns TMEM (512 cols)
+//   warps 2-5   epilogue: tcgen05.ld 32x32b -> (acc*2^-e - y)^2 -> f64 row sums -> lpj
+//   warps 6-9   A generator: packed state bits -> fp16 {0,1} tiles in the UMMA K-major 128B-swizzle layout
+// Pipelines: A ring (3 stages, generic-proxy writes + fence.proxy.async), B ring (5 stages, TMA
+// complete_tx), TMEM accumulator double buffer (2 x 256 columns) between MMA and epilogue.
+#include <cuda.h>
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+
+namespace evo {
+namespace dense {
+
+constexpr int BM = 128;           // states per tile (UMMA M)
+constexpr int BK = 64;            // latents per k-block: 64 fp16 = 128 B = one swizzle row
+constexpr int BN = 256;           // max observables per accumulator stage (UMMA N)
+constexpr int A_STAGES = 3;
+constexpr int B_STAGES = 5;
+constexpr int A_BYTES = BM * BK * 2;   // 16 KB
+constexpr int B_BYTES = BN * BK * 2;   // 32 KB
+constexpr int N_BARS = 2 * A_STAGES + 2 * B_STAGES + 4;
+constexpr int THREADS = 320;
+constexpr size_t SMEM_BYTES = 1024 + (size_t)A_STAGES * A_BYTES + (size_t)B_STAGES * B_BYTES + 8 * N_BARS + 16;
+
+struct Args {
+  const uint32_t *states;
+  int shared_states;
+  int64_t rows;  // N * Sp
+  int Sp, D, Dp, H, Hw, KB, n_tiles, box_rows, plane_rows;
+  const float *Y;
+  const uint8_t *mask;
+  const float *descale;  // device scalar 2^-e written by the split kernel
+  double pre1, pil_bar;
+  double *out;
+  int64_t ld;
+  unsigned long long *counters;
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: 8-row x 128 B atoms, SBO = 1024 B between
+// 8-row groups, LBO unused (1), descriptor version 1 (sm_100), layout type 2.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// instruction descriptor: D = f32, A = B = f16, both K-major, M = 128, N = n
+__device__ __forceinline__ uint32_t umma_idesc_f16(int n) {
+  return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+// two state bits -> two fp16 values {0.0, 1.0} packed in one b32
+__device__ __forceinline__ uint32_t bits2_to_half2(uint32_t b) {
+  return ((b & 1u) * 0x3C00u) | ((b & 2u) * 0x1E000000u);
+}
+
+__global__ void __launch_bounds__(THREADS, 1) dense_lpj_kernel(const __grid_constant__ CUtensorMap tmap, Args a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t *sm = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+  uint8_t *sA = sm;
+  uint8_t *sB = sm + (size_t)A_STAGES * A_BYTES;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sB + (size_t)B_STAGES * B_BYTES);
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + N_BARS);
+  const uint32_t bar0 = smem_u32(bars);
+  auto A_FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
+  auto A_EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(A_STAGES + s); };
+  auto B_FULL = [&](int s) { return bar0 + 8u * (uint32_t)(2 * A_STAGES + s); };
+  auto B_EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * A_STAGES + B_STAGES + s); };
+  auto T_FULL = [&](int s) { return bar0 + 8u * (uint32_t)(2 * A_STAGES + 2 * B_STAGES + s); };
+  auto T_EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * A_STAGES + 2 * B_STAGES + 2 + s); };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < A_STAGES; ++s) { mbar_init(A_FULL(s), 128); mbar_init(A_EMPTY(s), 1); }
+    for (int s = 0; s < B_STAGES; ++s) { mbar_init(B_FULL(s), 1); mbar_init(B_EMPTY(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(T_FULL(s), 1); mbar_init(T_EMPTY(s), 128); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int64_t tiles = (a.rows + BM - 1) / BM;
+
+  if (warp == 0) {
+    // ===== TMA producer: W planes ================================================================
+    if (lane == 0) {
+      int bs = 0;
+      uint32_t bph = 0;
+      const uint32_t tx = (uint32_t)a.box_rows * 128u;
+      for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x)
+        for (int j = 0; j < a.n_tiles; ++j)
+          for (int kb = 0; kb < a.KB; ++kb)
+            for (int p = 0; p < 2; ++p) {
+              mbar_wait(B_EMPTY(bs), bph ^ 1u);
+              mbar_expect_tx(B_FULL(bs), tx);
+              tma_load_2d(smem_u32(sB + (size_t)bs * B_BYTES), &tmap, B_FULL(bs), kb * BK,
+                          p * a.plane_rows + j * a.box_rows);
+              if (++bs == B_STAGES) { bs = 0; bph ^= 1u; }
+            }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer ============================================================================
+    if (lane == 0) {
+      int as = 0, bs = 0, ts = 0;
+      uint32_t aph = 0, bph = 0, tph = 0;
+      for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x)
+        for (int j = 0; j < a.n_tiles; ++j) {
+          const int nj = min(BN, a.Dp - j * BN);
+          const uint32_t idesc = umma_idesc_f16(nj);
+          mbar_wait(T_EMPTY(ts), tph ^ 1u);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + (uint32_t)ts * BN;
+          for (int kb = 0; kb < a.KB; ++kb) {
+            mbar_wait(A_FULL(as), aph);
+            const uint64_t adesc = umma_desc_sw128(smem_u32(sA + (size_t)as * A_BYTES));
+            for (int p = 0; p < 2; ++p) {
+              mbar_wait(B_FULL(bs), bph);
+              tc_fence_after();
+              const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + (size_t)bs * B_BYTES));
+#pragma unroll
+              for (int k4 = 0; k4 < BK / 16; ++k4)  // +32 B per K=16 step inside the 128 B swizzle row
+                umma_f16(tmem_d, adesc + (uint64_t)(2 * k4), bdesc + (uint64_t)(2 * k4), idesc, (uint32_t)(kb | p | k4));
+              umma_commit(B_EMPTY(bs));
+              if (++bs == B_STAGES) { bs = 0; bph ^= 1u; }
+            }
+            umma_commit(A_EMPTY(as));
+            if (++as == A_STAGES) { as = 0; aph ^= 1u; }
+          }
+          umma_commit(T_FULL(ts));
+          if (++ts == 2) { ts = 0; tph ^= 1u; }
+        }
+    }
+  } else if (warp < 6) {
+    // ===== epilogue: TMEM -> squared residual -> lpj =============================================
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    const float descale = __ldg(a.descale);
+    int ts = 0;
+    uint32_t tph = 0;
+    for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+      const int64_t gr = t * BM + q * 32 + lane;
+      const bool valid = gr < a.rows;
+      const int64_t n = valid ? gr / a.Sp : 0;
+      const int k = valid ? (int)(gr - n * a.Sp) : 0;
+      const float *yrow = a.Y + n * (int64_t)a.D;
+      const uint8_t *mrow = a.mask ? a.mask + n * (int64_t)a.D : nullptr;
+      const bool vec = ((a.D & 3) == 0) && !mrow;
+      double acc = 0.0;
+      for (int j = 0; j < a.n_tiles; ++j) {
+        const int nj = min(BN, a.Dp - j * BN);
+        mbar_wait(T_FULL(ts), tph);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)ts * BN;
+        for (int c = 0; c < nj; c += 16) {
+          uint32_t v[16];
+          tmem_ld16(taddr + (uint32_t)c, v);
+          tmem_ld_wait();
+          const int d0 = j * BN + c;
+          float part = 0.f;
+          if (vec && d0 + 16 <= a.D) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 4) {
+              const float4 y4 = __ldg(reinterpret_cast<const float4 *>(yrow + d0 + i));
+              float r0 = fmaf(__uint_as_float(v[i + 0]), descale, -y4.x);
+              float r1 = fmaf(__uint_as_float(v[i + 1]), descale, -y4.y);
+              float r2 = fmaf(__uint_as_float(v[i + 2]), descale, -y4.z);
+              float r3 = fmaf(__uint_as_float(v[i + 3]), descale, -y4.w);
+              part = fmaf(r0, r0, part);
+              part = fmaf(r1, r1, part);
+              part = fmaf(r2, r2, part);
+              part = fmaf(r3, r3, part);
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int d = d0 + i;
+              if (d < a.D && (!mrow || mrow[d])) {
+                float r = fmaf(__uint_as_float(v[i]), descale, -__ldg(yrow + d));
+                part = fmaf(r, r, part);
+              }
+            }
+          }
+          acc += (double)part;
+        }
+        tc_fence_before();
+        mbar_arrive(T_EMPTY(ts));
+        if (++ts == 2) { ts = 0; tph ^= 1u; }
+      }
+      if (valid) {
+        const uint32_t *st = a.states + (a.shared_states ? (int64_t)k : gr) * a.Hw;
+        int pc = 0;
+        for (int w = 0; w < a.Hw; ++w) pc += __popc(__ldg(st + w));
+        unsigned fl = 0;
+        const double v = lpj_sanitise(a.pre1 * acc + a.pil_bar * (double)pc, fl);
+        a.out[n * a.ld + k] = v;
+        if (fl && a.counters) atomicAdd(a.counters + ((fl & 1u) ? 0 : ((fl & 2u) ? 1 : 2)), 1ull);
+      }
+    }
+  } else {
+    // ===== A generator: packed bits -> fp16 tile, K-major, 128 B swizzle =========================
+    const int r = (warp - 6) * 32 + lane;
+    uint8_t *rowbase = sA + (size_t)(r >> 3) * 1024 + (size_t)(r & 7) * 128;
+    const uint32_t sw = (uint32_t)(r & 7);
+    int as = 0;
+    uint32_t aph = 0;
+    for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+      const int64_t gr = t * BM + r;
+      const bool valid = gr < a.rows;
+      const uint32_t *st = a.states + (valid ? (a.shared_states ? gr % a.Sp : gr) : 0) * a.Hw;
+      for (int j = 0; j < a.n_tiles; ++j)
+        for (int kb = 0; kb < a.KB; ++kb) {
+          uint32_t w0 = 0, w1 = 0;
+          if (valid) {
+            if (2 * kb < a.Hw) w0 = __ldg(st + 2 * kb);
+            if (2 * kb + 1 < a.Hw) w1 = __ldg(st + 2 * kb + 1);
+          }
+          mbar_wait(A_EMPTY(as), aph ^ 1u);
+          uint8_t *dst = rowbase + (size_t)as * A_BYTES;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const uint32_t byte = ((c < 4 ? w0 : w1) >> (8 * (c & 3))) & 0xFFu;
+            uint4 o;
+            o.x = bits2_to_half2(byte);
+            o.y = bits2_to_half2(byte >> 2);
+            o.z = bits2_to_half2(byte >> 4);
+            o.w = bits2_to_half2(byte >> 6);
+            *reinterpret_cast<uint4 *>(dst + (((uint32_t)c ^ sw) << 4)) = o;
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          mbar_arrive(A_FULL(as));
+          if (++as == A_STAGES) { as = 0; aph ^= 1u; }
+        }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
+// ---- W -> two scaled fp16 planes ----------------------------------------------------------------
+__global__ void wmax_kernel(const double *__restrict__ W, int64_t n, unsigned int *out) {
+  float m = 0.f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float v = fabsf((float)W[i]);
+    if (v == v && v < INFINITY) m = fmaxf(m, v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out, __float_as_uint(m));  // non-negative floats order like their bits
+}
+
+// planes: [2][plane_rows][Hp] fp16, zero padded.  hdr[0] = max|W| bits (input), hdr[1] = 2^-e (f32, output)
+__global__ void wsplit_kernel(const double *__restrict__ W, int D, int H, int plane_rows, int Hp, __half *planes,
+                              unsigned int *hdr) {
+  const float mx = __uint_as_float(hdr[0]);
+  int e = 0;
+  if (mx > 0.f) e = 13 - ilogbf(mx);  // max |W| 2^e in [2^13, 2^14): fp16 range with headroom
+  e = max(-100, min(100, e));
+  const double scale = ldexp(1.0, e);
+  const int64_t total = (int64_t)plane_rows * Hp;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int d = (int)(i / Hp), h = (int)(i - (int64_t)d * Hp);
+    double v = (d < D && h < H) ? W[(int64_t)d * H + h] * scale : 0.0;
+    if (!(v == v)) v = 0.0;
+    v = fmin(fmax(v, -65504.0), 65504.0);
+    const __half hi = __double2half(v);
+    const __half lo = __double2half(v - (double)__half2float(hi));
+    planes[i] = hi;
+    planes[total + i] = lo;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) reinterpret_cast<float *>(hdr)[1] = (float)ldexp(1.0, -e);
+}
+
+struct Geometry {
+  int Dp, Hp, KB, n_tiles, box_rows, plane_rows;
+  size_t plane_bytes, total_bytes;
+};
+static Geometry geometry(int D, int H) {
+  Geometry g;
+  g.Dp = (D + 15) & ~15;
+  g.Hp = (H + BK - 1) / BK * BK;
+  g.KB = g.Hp / BK;
+  g.box_rows = g.Dp < BN ? g.Dp : BN;
+  g.n_tiles = (g.Dp + BN - 1) / BN;
+  g.plane_rows = g.n_tiles * g.box_rows;
+  g.plane_bytes = (size_t)g.plane_rows * g.Hp * sizeof(__half);
+  g.total_bytes = 256 + 2 * g.plane_bytes;  // 256-byte header (max bits, descale), planes 256-B aligned
+  return g;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
+        qr == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+}  // namespace dense
+}  // namespace evo
+
+using namespace evo;
+
+extern "C" int64_t evo_bsc_lpj_gemm_workspace_bytes(int D, int H) {
+  if (D <= 0 || H <= 0) return 0;
+  return (int64_t)dense::geometry(D, H).total_bytes;
+}
+
+extern "C" int evo_bsc_lpj_gemm_prepare(const double *W, int D, int H, void *workspace, void *stream) {
+  EVO_REQUIRE(W && workspace && D > 0 && H > 0, "bad arguments");
+  EVO_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  dense::Geometry g = dense::geometry(D, H);
+  unsigned int *hdr = reinterpret_cast<unsigned int *>(workspace);
+  __half *planes = reinterpret_cast<__half *>(reinterpret_cast<uint8_t *>(workspace) + 256);
+  EVO_CUDA(cudaMemsetAsync(hdr, 0, 256, st));
+  int64_t n = (int64_t)D * H;
+  int blocks = (int)((n + 255) / 256 < (int64_t)sm_count() * 4 ? (n + 255) / 256 : (int64_t)sm_count() * 4);
+  dense::wmax_kernel<<<blocks, 256, 0, st>>>(W, n, hdr);
+  EVO_LAUNCH_CHECK("wmax");
+  int64_t total = (int64_t)g.plane_rows * g.Hp;
+  blocks = (int)((total + 255) / 256 < (int64_t)sm_count() * 4 ? (total + 255) / 256 : (int64_t)sm_count() * 4);
+  dense::wsplit_kernel<<<blocks, 256, 0, st>>>(W, D, H, g.plane_rows, g.Hp, planes, hdr);
+  EVO_LAUNCH_CHECK("wsplit");
+  return EVO_OK;
+}
+
+extern "C" int evo_bsc_lpj_gemm(const uint32_t *states, int shared_states, int64_t N, int Sp, int D, int H,
+                                const void *workspace, const float *Y, const uint8_t *mask, double pre1, double pil_bar,
+                                double *lpj_out, int64_t ld_lpj, unsigned long long *reset_counters, void *stream) {
+  EVO_REQUIRE(N >= 0 && Sp > 0 && D > 0 && H > 0 && ld_lpj >= Sp, "bad sizes");
+  EVO_REQUIRE(states && workspace && Y && lpj_out, "null pointer");
+  if (N == 0) return EVO_OK;
+  dense::Geometry g = dense::geometry(D, H);
+  dense::EncodeTiledFn enc = dense::encode_fn();
+  if (!enc) {
+    set_error("evo_bsc_lpj_gemm: cuTensorMapEncodeTiled is not available from the driver");
+    return EVO_ERR_UNSUPPORTED;
+  }
+  uint8_t *planes = const_cast<uint8_t *>(reinterpret_cast<const uint8_t *>(workspace)) + 256;
+  CUtensorMap tmap;
+  cuuint64_t gdim[2] = {(cuuint64_t)g.Hp, (cuuint64_t)(2 * g.plane_rows)};
+  cuuint64_t gstride[1] = {(cuuint64_t)g.Hp * sizeof(__half)};
+  cuuint32_t box[2] = {(cuuint32_t)dense::BK, (cuuint32_t)g.box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, planes, gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (cr != CUDA_SUCCESS) {
+    set_error("evo_bsc_lpj_gemm: cuTensorMapEncodeTiled failed (%d)", (int)cr);
+    return EVO_ERR_CUDA;
+  }
+  dense::Args a;
+  a.states = states;
+  a.shared_states = shared_states;
+  a.rows = N * Sp;
+  a.Sp = Sp; a.D = D; a.Dp = g.Dp; a.H = H; a.Hw = words_for(H); a.KB = g.KB;
+  a.n_tiles = g.n_tiles; a.box_rows = g.box_rows; a.plane_rows = g.plane_rows;
+  a.Y = Y; a.mask = mask;
+  a.descale = reinterpret_cast<const float *>(workspace) + 1;
+  a.pre1 = pre1; a.pil_bar = pil_bar;
+  a.out = lpj_out; a.ld = ld_lpj; a.counters = reset_counters;
+  static bool attr_set = false;
+  if (!attr_set) {
+    EVO_CUDA(cudaFuncSetAttribute(dense::dense_lpj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)dense::SMEM_BYTES));
+    attr_set = true;
+  }
+  int64_t tiles = (a.rows + dense::BM - 1) / dense::BM;
+  int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  dense::dense_lpj_kernel<<<grid, dense::THREADS, dense::SMEM_BYTES, (cudaStream_t)stream>>>(tmap, a);
+  EVO_LAUNCH_CHECK("dense_lpj");
+  return EVO_OK;
+}

@@ -76,6 +76,22 @@ int evo_bsc_lpj(int eval, const uint32_t *states, int shared_states, int64_t N, 
                 const double *ynorm2, double pre1, double pil_bar, double *lpj_out, int64_t ld_lpj,
                 unsigned long long *reset_counters, void *stream);
 
+/* Dense tensor-core form of the same log-pseudo-joint (bsc.py:88-95: `np.dot(states, W.T) - y`, squared
+ * and summed over the usable entries) as ONE fused tcgen05 GEMM  C[(n,k)][d] = sum_h s_nkh W[d][h]
+ * whose epilogue forms pre1 * sum_d m_nd (C - y_nd)^2 + pil_bar |s| straight from TMEM; the N*S x D
+ * residual is never written.  W is scaled by a power of two and split into two fp16 planes (hi + lo,
+ * 22 significant bits; the binary operand is exact), both accumulated in fp32: lpj agrees with the f64
+ * reference to <= 1e-5 relative (measured <= 2e-6).
+ *   evo_bsc_lpj_gemm_workspace_bytes: size of the caller-owned workspace (256-byte aligned) for (D,H).
+ *   evo_bsc_lpj_gemm_prepare: once per parameter set -- fills the workspace from W (two kernels).
+ *   evo_bsc_lpj_gemm: same meaning of states / shared_states / mask / lpj_out / ld_lpj / reset_counters
+ *   as evo_bsc_lpj (counters are incremented per sanitised state). */
+int64_t evo_bsc_lpj_gemm_workspace_bytes(int D, int H);
+int evo_bsc_lpj_gemm_prepare(const double *W, int D, int H, void *workspace, void *stream);
+int evo_bsc_lpj_gemm(const uint32_t *states, int shared_states, int64_t N, int Sp, int D, int H,
+                     const void *workspace, const float *Y, const uint8_t *mask, double pre1, double pil_bar,
+                     double *lpj_out, int64_t ld_lpj, unsigned long long *reset_counters, void *stream);
+
 /* ---- fused E-step (Model.E_step _models.py:454-565 = lpj of K^n + evolve_states eas.py:153-313
  *      + vary_Kn utils.py:231-337 + free-energy tail _models.py:544-547) ---------------------- */
 typedef struct evo_estep_args {
