@@ -163,6 +163,71 @@ def algorithmic_bytes(w, N, U_mean):
     }
 
 
+def run_lpj_compare(args):
+    """north_star (a): the dense tcgen05 log-joint (evo_bsc_lpj_gemm) timed against the sparse
+    Gram/popc kernel (evo_bsc_lpj) on the SAME evolved K sets of a BSC workload, each call alone
+    between CUDA events on the launching stream.  One JSON line; no EM step is timed here."""
+    import torch
+
+    from evo_b200 import _lib
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import init_states
+
+    torch.cuda.set_device(0)
+    device = torch.device("cuda", 0)
+    w = WORKLOADS[args.workload]
+    assert w["model"] == "bsc", "lpj comparison is defined for the BSC workloads"
+    N = args.n if args.n else w["N"]
+    D, H, K = w["D"], w["H"], w["K"]
+    Hw = (H + 31) // 32
+    model = BSC(D, H, K, device=device)
+    Y, X = synth_device(w, N, 1000, device)
+    data = {"y": Y, "x_infr": None}
+    np.random.seed(1)
+    theta = model.check_params(model.standard_init(data))
+    sel, mut, P, C, G = w["ea"]
+    cont = init_states(N, K, H, sel, mut, P, C, G, device=device, seed=0x5EED)
+    for _ in range(max(args.warmup, 3)):  # evolve the K sets so their sparsity is the workload's
+        model.step(theta, cont, data)
+    model.E_step_precompute(theta, cont, data)
+    sd = cont["ss_dev"]
+    dd = model.device_data(data)
+    model.timing = []
+    for _ in range(args.steps + 1):
+        ws = model.dense_workspace(theta)
+        dense = model.lpj_all_dense(theta, data, sd, workspace=ws)
+        sparse = model.lpj_all(theta, data, sd)
+    t = model.timing_summary()
+    model.timing = None
+    rel = float(((dense - sparse).abs() / sparse.abs().clamp_min(1e-300)).max().item())
+    bits = sd.view(torch.int32).cpu().numpy().view(np.uint32)
+    act = float(np.unpackbits(bits[: min(N, 2000)].view(np.uint8)).sum() / (min(N, 2000) * K))
+    j = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    peak_tf, peak_bw = float(j.get("bf16_tflops", 1590.0)), float(j.get("hbm_gbs", 6650.0))
+    src = "measured (MEASURED_PEAKS.json, burst)" if j else "fallback (B200_PROFILING.md)"
+    lpj = N * K
+    d_ms, s_ms = t["evo_bsc_lpj_gemm"][1], t["evo_bsc_lpj"][1]
+    dp_ms, sp_ms = t["evo_bsc_lpj_gemm_prepare"][1], t["evo_bsc_prepare"][1]
+    flop = 2.0 * H * D * lpj
+    sbytes = N * (4 * D + K * (4 * Hw + 4))
+    line = {
+        "mode": "lpj_compare", "config": {"workload": "%s: %s" % (args.workload, DESCR[args.workload]), "N": N},
+        "log_joints": lpj, "active_latents_per_state": act, "max_rel_diff_dense_vs_sparse": rel,
+        "dense": {"kernel": "evo_bsc_lpj_gemm (tcgen05, fp16 hi+lo = 2 tensor passes)", "ms": d_ms, "prepare_ms": dp_ms,
+                  "lpj_per_sec": lpj / (d_ms * 1e-3),
+                  "roofline": {"bound": "tensor", "achieved": flop / (d_ms * 1e-3) / 1e12, "peak": peak_tf, "unit": "TFLOP/s",
+                               "frac": flop / (d_ms * 1e-3) / 1e12 / peak_tf, "executed_frac": 2 * flop / (d_ms * 1e-3) / 1e12 / peak_tf,
+                               "algorithmic_flop_per_launch": flop, "peak_source": src}},
+        "sparse": {"kernel": "evo_bsc_lpj (Gram / popc form, f64)", "ms": s_ms, "prepare_ms": sp_ms,
+                   "lpj_per_sec": lpj / (s_ms * 1e-3),
+                   "roofline": {"bound": "hbm", "achieved": sbytes / (s_ms * 1e-3) / 1e9, "peak": peak_bw, "unit": "GB/s",
+                                "frac": sbytes / (s_ms * 1e-3) / 1e9 / peak_bw, "algorithmic_bytes_per_launch": sbytes,
+                                "peak_source": src}},
+        "faster": "sparse" if s_ms + sp_ms < d_ms + dp_ms else "dense",
+    }
+    print(json.dumps(line), flush=True)
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -418,12 +483,16 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=0, help="datapoints per GPU (default: the workload's N)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--lpj-compare", action="store_true",
+                    help="time the dense tcgen05 log-joint against the sparse Gram kernel (BSC workloads)")
     ap.add_argument("--cpu-worker", type=int, default=-1, help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.cpu_worker >= 0:
         return cpu_worker(args)
     if args.impl == "reference":
         return run_reference(args)
+    if args.lpj_compare:
+        return run_lpj_compare(args)
     return run_ours(args)
 
 

@@ -36,7 +36,9 @@ constexpr int A_BYTES = BM * BK * 2;   // 16 KB
 constexpr int B_BYTES = BN * BK * 2;   // 32 KB
 constexpr int N_BARS = 2 * A_STAGES + 2 * B_STAGES + 4;
 constexpr int THREADS = 320;
-constexpr size_t SMEM_BYTES = 1024 + (size_t)A_STAGES * A_BYTES + (size_t)B_STAGES * B_BYTES + 8 * N_BARS + 16;
+constexpr int Y_STAGE_FLOATS = 1024;  // per epilogue warp: y of its datapoint (D <= 1024)
+constexpr size_t SMEM_BYTES = 1024 + (size_t)A_STAGES * A_BYTES + (size_t)B_STAGES * B_BYTES + 4 * Y_STAGE_FLOATS * 4 +
+                              8 * N_BARS + 16;
 
 struct Args {
   const uint32_t *states;
@@ -130,7 +132,8 @@ __global__ void __launch_bounds__(THREADS, 1) dense_lpj_kernel(const __grid_cons
   uint8_t *sm = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
   uint8_t *sA = sm;
   uint8_t *sB = sm + (size_t)A_STAGES * A_BYTES;
-  uint64_t *bars = reinterpret_cast<uint64_t *>(sB + (size_t)B_STAGES * B_BYTES);
+  uint8_t *sY = sB + (size_t)B_STAGES * B_BYTES;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sY + 4 * Y_STAGE_FLOATS * 4);
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + N_BARS);
   const uint32_t bar0 = smem_u32(bars);
   auto A_FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
@@ -210,8 +213,31 @@ __global__ void __launch_bounds__(THREADS, 1) dense_lpj_kernel(const __grid_cons
     }
   } else if (warp < 6) {
     // ===== epilogue: TMEM -> squared residual -> lpj =============================================
+    // y of the warp's datapoint is staged in shared memory one tile ahead (coalesced loads issued
+    // while the current tile is being reduced), so the reduction never waits on HBM.
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
     const float descale = __ldg(a.descale);
+    float *ys = reinterpret_cast<float *>(sY) + (size_t)q * Y_STAGE_FLOATS;
+    const bool can_stage = (a.Sp % 32 == 0) && (a.D % 4 == 0) && a.D <= Y_STAGE_FLOATS && !a.mask;
+    const int nv = a.D >> 2;  // float4 per row
+    float4 pre[Y_STAGE_FLOATS / 128];
+    auto fetch_y = [&](int64_t tile) {
+      const int64_t row0 = tile * BM + q * 32;
+      if (!can_stage || row0 >= a.rows) return;
+      const float4 *src = reinterpret_cast<const float4 *>(a.Y + (row0 / a.Sp) * (int64_t)a.D);
+#pragma unroll
+      for (int i = 0; i < Y_STAGE_FLOATS / 128; ++i)
+        if (lane + 32 * i < nv) pre[i] = __ldg(src + lane + 32 * i);
+    };
+    auto stash_y = [&]() {
+      if (!can_stage) return;
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < Y_STAGE_FLOATS / 128; ++i)
+        if (lane + 32 * i < nv) reinterpret_cast<float4 *>(ys)[lane + 32 * i] = pre[i];
+      __syncwarp();
+    };
+    fetch_y(blockIdx.x);
     int ts = 0;
     uint32_t tph = 0;
     for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
@@ -222,42 +248,53 @@ __global__ void __launch_bounds__(THREADS, 1) dense_lpj_kernel(const __grid_cons
       const float *yrow = a.Y + n * (int64_t)a.D;
       const uint8_t *mrow = a.mask ? a.mask + n * (int64_t)a.D : nullptr;
       const bool vec = ((a.D & 3) == 0) && !mrow;
+      stash_y();
+      fetch_y(t + gridDim.x);
       double acc = 0.0;
       for (int j = 0; j < a.n_tiles; ++j) {
         const int nj = min(BN, a.Dp - j * BN);
         mbar_wait(T_FULL(ts), tph);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)ts * BN;
-        for (int c = 0; c < nj; c += 16) {
-          uint32_t v[16];
-          tmem_ld16(taddr + (uint32_t)c, v);
-          tmem_ld_wait();
-          const int d0 = j * BN + c;
-          float part = 0.f;
-          if (vec && d0 + 16 <= a.D) {
+        uint32_t v[2][16];
+        tmem_ld16(taddr, v[0]);
+        tmem_ld_wait();
+#pragma unroll 1
+        for (int c = 0; c < nj; c += 32) {
 #pragma unroll
-            for (int i = 0; i < 16; i += 4) {
-              const float4 y4 = __ldg(reinterpret_cast<const float4 *>(yrow + d0 + i));
-              float r0 = fmaf(__uint_as_float(v[i + 0]), descale, -y4.x);
-              float r1 = fmaf(__uint_as_float(v[i + 1]), descale, -y4.y);
-              float r2 = fmaf(__uint_as_float(v[i + 2]), descale, -y4.z);
-              float r3 = fmaf(__uint_as_float(v[i + 3]), descale, -y4.w);
-              part = fmaf(r0, r0, part);
-              part = fmaf(r1, r1, part);
-              part = fmaf(r2, r2, part);
-              part = fmaf(r3, r3, part);
-            }
-          } else {
+          for (int hb = 0; hb < 2; ++hb) {
+            const int cc = c + 16 * hb;
+            if (cc >= nj) break;
+            if (cc + 16 < nj) tmem_ld16(taddr + (uint32_t)(cc + 16), v[hb ^ 1]);  // next chunk in flight
+            const int d0 = j * BN + cc;
+            float part = 0.f;
+            if (vec && d0 + 16 <= a.D) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const int d = d0 + i;
-              if (d < a.D && (!mrow || mrow[d])) {
-                float r = fmaf(__uint_as_float(v[i]), descale, -__ldg(yrow + d));
-                part = fmaf(r, r, part);
+              for (int i = 0; i < 16; i += 4) {
+                const float4 y4 = can_stage ? *reinterpret_cast<const float4 *>(ys + d0 + i)
+                                            : __ldg(reinterpret_cast<const float4 *>(yrow + d0 + i));
+                float r0 = fmaf(__uint_as_float(v[hb][i + 0]), descale, -y4.x);
+                float r1 = fmaf(__uint_as_float(v[hb][i + 1]), descale, -y4.y);
+                float r2 = fmaf(__uint_as_float(v[hb][i + 2]), descale, -y4.z);
+                float r3 = fmaf(__uint_as_float(v[hb][i + 3]), descale, -y4.w);
+                part = fmaf(r0, r0, part);
+                part = fmaf(r1, r1, part);
+                part = fmaf(r2, r2, part);
+                part = fmaf(r3, r3, part);
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const int d = d0 + i;
+                if (d < a.D && (!mrow || mrow[d])) {
+                  float r = fmaf(__uint_as_float(v[hb][i]), descale, -__ldg(yrow + d));
+                  part = fmaf(r, r, part);
+                }
               }
             }
+            acc += (double)part;
+            tmem_ld_wait();
           }
-          acc += (double)part;
         }
         tc_fence_before();
         mbar_arrive(T_EMPTY(ts));
