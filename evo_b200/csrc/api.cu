@@ -119,39 +119,6 @@ __global__ void __launch_bounds__(T) select_topk_kernel(uint32_t *__restrict__ s
   }
 }
 
-template <class Eval>
-static int launch_estep(const EstepDev &dv, Eval ev, cudaStream_t st) {
-  int work = dv.S > dv.Cg ? dv.S : dv.Cg;
-  int T = ev.threads_hint(work);
-  T = T <= 32 ? 32 : (T <= 64 ? 64 : 128);
-  size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes(T);
-#define EVO_LAUNCH_T(TT)                                                                              \
-  {                                                                                                   \
-    auto k = estep_kernel<Eval, TT>;                                                                  \
-    if (smem > 48 * 1024)                                                                             \
-      EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
-    int per_sm = 1;                                                                                   \
-    EVO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, TT, smem));                    \
-    if (per_sm < 1) {                                                                                 \
-      set_error("evo_estep: %zu bytes of shared memory per datapoint exceed the SM", smem);           \
-      return EVO_ERR_UNSUPPORTED;                                                                     \
-    }                                                                                                 \
-    int64_t g = (int64_t)sm_count() * per_sm;                                                         \
-    if (g > dv.N) g = dv.N;                                                                           \
-    k<<<(int)g, TT, smem, st>>>(dv, ev);                                                              \
-  }
-  if (smem > 227 * 1024) {
-    set_error("evo_estep: %zu bytes of shared memory per datapoint exceed 227 KB", smem);
-    return EVO_ERR_UNSUPPORTED;
-  }
-  if (T <= 32) EVO_LAUNCH_T(32)
-  else if (T <= 64) EVO_LAUNCH_T(64)
-  else EVO_LAUNCH_T(128)
-#undef EVO_LAUNCH_T
-  EVO_LAUNCH_CHECK("estep");
-  return EVO_OK;
-}
-
 }  // namespace evo
 
 using namespace evo;
@@ -207,16 +174,19 @@ extern "C" int evo_estep(const evo_estep_args *x, void *stream) {
   while (HT < need) HT <<= 1;
   dv.HT = HT;
   dv.PK = dv.S > Cg ? dv.S : Cg;
+  auto pow2mask = [](int n) { uint32_t m = 1; while ((int)m < n) m <<= 1; return m - 1u; };
+  dv.Hs = dv.Hw | 1;
+  dv.mask_c = pow2mask(dv.Ctot); dv.mask_s = pow2mask(dv.S); dv.mask_p = pow2mask(dv.PK);
   cudaStream_t st = (cudaStream_t)stream;
   if (x->eval == EVO_EVAL_BSC_GRAM) {
     EVO_REQUIRE(x->G && x->B && x->ynorm2, "gram evaluator needs G, B, ynorm2");
     EVO_REQUIRE(x->mask == nullptr, "gram evaluator needs complete data");
     BscGramEval ev{x->G, x->B, x->ynorm2, x->pre1, x->pil_bar, dv.H, dv.Hw, nullptr, nullptr, 0.0};
-    return launch_estep(dv, ev, st);
+    return launch_estep_any(dv, ev, st);
   } else if (x->eval == EVO_EVAL_BSC_DIRECT) {
     EVO_REQUIRE(x->W && x->Y, "direct evaluator needs W, Y");
     BscDirectEval ev{x->W, x->Y, x->mask, x->pre1, x->pil_bar, dv.D, dv.H, dv.Hw, nullptr, nullptr, 0.0};
-    return launch_estep(dv, ev, st);
+    return launch_estep_any(dv, ev, st);
   } else if (x->eval == EVO_EVAL_ES3C) {
     return es3c_launch_estep(dv, x, st);
   }

@@ -7,34 +7,6 @@ namespace evo {
 static double *g_scratch = nullptr;
 static int g_scratch_warps = 0;
 
-template <class Eval>
-static int launch_estep_es3c(const EstepDev &dv, Eval ev, cudaStream_t st) {
-  int work = dv.S > dv.Cg ? dv.S : dv.Cg;
-  int T = ev.threads_hint(work);
-  size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes(T);
-  if (smem > 227 * 1024) {
-    set_error("evo_estep(es3c): %zu bytes of shared memory per datapoint exceed 227 KB", smem);
-    return EVO_ERR_UNSUPPORTED;
-  }
-#define EVO_LAUNCH_T(TT)                                                                              \
-  {                                                                                                   \
-    auto k = estep_kernel<Eval, TT>;                                                                  \
-    if (smem > 48 * 1024)                                                                             \
-      EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
-    int per_sm = 1;                                                                                   \
-    EVO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, TT, smem));                    \
-    if (per_sm < 1) per_sm = 1;                                                                       \
-    int64_t g = (int64_t)sm_count() * per_sm;                                                         \
-    if (g > dv.N) g = dv.N;                                                                           \
-    k<<<(int)g, TT, smem, st>>>(dv, ev);                                                              \
-  }
-  if (T <= 64) EVO_LAUNCH_T(64)
-  else EVO_LAUNCH_T(128)
-#undef EVO_LAUNCH_T
-  EVO_LAUNCH_CHECK("estep_es3c");
-  return EVO_OK;
-}
-
 int es3c_launch_estep(const EstepDev &dv, const evo_estep_args *x, cudaStream_t st) {
   EVO_REQUIRE(x->Psi && x->mus && x->pil_bar_h, "es3c evaluator needs Psi, mus, pil_bar_h");
   EVO_REQUIRE(x->sigma2 > 0.0, "sigma2 must be positive");
@@ -51,7 +23,7 @@ int es3c_launch_estep(const EstepDev &dv, const evo_estep_args *x, cudaStream_t 
     EVO_REQUIRE(x->G && x->B && x->ynorm2, "es3c with complete data needs G, B, ynorm2");
     ev.masked = 0; ev.G = x->G; ev.B = x->B; ev.ynorm2 = x->ynorm2;
   }
-  return launch_estep_es3c(dv, ev, st);
+  return launch_estep_any(dv, ev, st);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -65,14 +37,9 @@ __device__ __forceinline__ void gj_inverse(int a, double *A3, double *R, int ld,
     for (int c = 0; c < a; ++c) R[lane * ld + c] = (lane == c) ? 1.0 : 0.0;
   __syncwarp();
   for (int k = 0; k < a; ++k) {
-    double mag = (act && lane >= k) ? fabs(A3[lane * ld + k]) : -1.0;
-    int p = lane;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      double om = __shfl_xor_sync(0xffffffffu, mag, o);
-      int op = __shfl_xor_sync(0xffffffffu, p, o);
-      if (om > mag || (om == mag && op < p)) { mag = om; p = op; }
-    }
+    unsigned key = 0u;
+    if (act && lane >= k) key = (__float_as_uint(fabsf((float)A3[lane * ld + k])) & ~31u) | (unsigned)(31 - lane);
+    const int p = 31 - (int)(__reduce_max_sync(0xffffffffu, key) & 31u);
     if (p != k) {
       if (act) {
         double t = A3[k * ld + lane]; A3[k * ld + lane] = A3[p * ld + lane]; A3[p * ld + lane] = t;

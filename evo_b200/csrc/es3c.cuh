@@ -44,7 +44,7 @@ struct Es3cEval {
     return masked ? align8((size_t)D * sizeof(double)) + align8((size_t)D) : align8((size_t)H * sizeof(double));
   }
   __host__ __device__ size_t smem_bytes(int T) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM; }
-  __host__ int threads_hint(int work) const { return work <= 64 ? 64 : 128; }
+  __host__ int threads_hint(int work) const { return work < 64 ? 64 : 256; }  // one warp per state: 8 states in flight
 
   template <int T>
   __device__ void setup(int64_t n, unsigned char *smem) {
@@ -158,16 +158,16 @@ struct Es3cEval {
   __device__ __forceinline__ double lu_solve(int a, double *A3, int ld, double &rhs) const {
     const int lane = threadIdx.x & 31;
     const bool act = lane < a;
-    double logdet = 0.0;
+    // log|det| = log|prod piv|: the product is carried as mantissa x 2^esum (one log per state
+    // instead of one per pivot); pivots that are 0 / denormal / non-finite take the direct log.
+    double prod = 1.0, extra = 0.0;
+    int esum = 0;
     for (int k = 0; k < a; ++k) {
-      double mag = (act && lane >= k) ? fabs(A3[lane * ld + k]) : -1.0;
-      int p = lane;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        double om = __shfl_xor_sync(0xffffffffu, mag, o);
-        int op = __shfl_xor_sync(0xffffffffu, p, o);
-        if (om > mag || (om == mag && op < p)) { mag = om; p = op; }
-      }
+      // partial pivoting: largest |A3[i][k]|, i >= k, found by one redux on the f32 magnitude bits with
+      // the (inverted) lane in the 5 low bits -- any near-maximal pivot is as good numerically
+      unsigned key = 0u;
+      if (act && lane >= k) key = (__float_as_uint(fabsf((float)A3[lane * ld + k])) & ~31u) | (unsigned)(31 - lane);
+      const int p = 31 - (int)(__reduce_max_sync(0xffffffffu, key) & 31u);
       if (p != k) {
         if (act) { double t = A3[k * ld + lane]; A3[k * ld + lane] = A3[p * ld + lane]; A3[p * ld + lane] = t; }
         double rk = __shfl_sync(0xffffffffu, rhs, k), rp = __shfl_sync(0xffffffffu, rhs, p);
@@ -176,7 +176,18 @@ struct Es3cEval {
       }
       __syncwarp();
       double piv = A3[k * ld + k];
-      logdet += log(fabs(piv));
+      {
+        const int ex = (__double2hiint(piv) >> 20) & 0x7ff;
+        if (ex == 0 || ex == 0x7ff) {
+          extra += log(fabs(piv));
+        } else {
+          prod *= __hiloint2double((__double2hiint(piv) & 0x800fffff) | 0x3ff00000, __double2loint(piv));
+          esum += ex - 1023;
+          const int e2 = (__double2hiint(prod) >> 20) & 0x7ff;  // prod stays in [1, 4): renormalise
+          prod = __hiloint2double((__double2hiint(prod) & 0x800fffff) | 0x3ff00000, __double2loint(prod));
+          esum += e2 - 1023;
+        }
+      }
       double rhs_k = __shfl_sync(0xffffffffu, rhs, k);
       if (act && lane > k) {
         double f = A3[lane * ld + k] / piv;
@@ -190,7 +201,7 @@ struct Es3cEval {
       if (lane == k) rhs = xk;
       if (act && lane < k) rhs -= A3[lane * ld + k] * xk;
     }
-    return logdet;
+    return log(fabs(prod)) + (double)esum * 0.693147180559945309417232121458 + extra;
   }
 
   // N = I + s2i A1 A2 -> A3 ; also v_i, |r|^2 and w = Psi_A' v  (v' Lambda v = w . N^-1 v)
@@ -245,11 +256,11 @@ struct Es3cEval {
   }
 
   template <int T>
-  __device__ void eval_batch(const uint32_t *st, int cnt, double *out, unsigned &flags) {
+  __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) {
     if (masked) yn2 = masked_yn2();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int i = warp; i < cnt; i += T / 32) {
-      double v = warp_lpj(st + (size_t)i * Hw);
+      double v = warp_lpj(st + (size_t)i * ld);
       v = lpj_sanitise(v, flags);
       if (lane == 0) out[i] = v;
     }

@@ -8,6 +8,8 @@
 // shared memory; HBM sees one read of K^n (+ the evaluator's per-datapoint table row), one write
 // of the lpj row and writes of the substituted states only.
 #pragma once
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "evaluators.cuh"
 
@@ -16,6 +18,8 @@ namespace evo {
 struct EstepDev {
   int64_t N, n_offset;
   int D, H, Hw, S, S_perm, Mprime;
+  int Hs;    // row stride (words) of the packed states in SHARED memory: Hw | 1, odd => one state per
+             // thread walks its words without bank conflicts (global rows stay Hw)
   int n_parents, n_children, n_generations, selection, mutation, background;
   double p_bf, sparseness;
   uint64_t seed;
@@ -31,14 +35,15 @@ struct EstepDev {
   int Ctot;  // Cg * n_generations
   int HT;    // hash table slots (power of two)
   int PK;    // capacity of pool / key arrays = max(S, Cg)
+  uint32_t mask_c, mask_s, mask_p;  // index-code masks (pow2 - 1) for Ctot, S, PK (order_key)
 };
 
 constexpr int TAG_EMPTY = -1;
 constexpr int TAG_CHILD = 1 << 24;
 
 struct EstepSmem {
-  uint32_t *st_uniq;   // [(S + Ctot)][Hw]
-  uint32_t *st_child;  // [Cg][Hw]
+  uint32_t *st_uniq;   // [(S + Ctot)][Hs]
+  uint32_t *st_child;  // [Cg][Hs]
   double *lpj_uniq;    // [S + Ctot]
   double *keys;        // [PK]
   double *red_d;       // [8]
@@ -56,6 +61,7 @@ struct EstepSmem {
 };
 
 __host__ __device__ inline size_t align8(size_t x) { return (x + 7) & ~(size_t)7; }
+__host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
 __host__ __device__ inline size_t estep_carve(const EstepDev &a, unsigned char *base, EstepSmem *s) {
   size_t off = 0;
@@ -63,13 +69,13 @@ __host__ __device__ inline size_t estep_carve(const EstepDev &a, unsigned char *
 #define CARVE(field, type, count)                                  \
   do {                                                             \
     if (s) s->field = reinterpret_cast<type *>(base + off);       \
-    off = align8(off + sizeof(type) * (size_t)(count));           \
+    off = align16(off + sizeof(type) * (size_t)(count));          \
   } while (0)
   CARVE(lpj_uniq, double, U);
-  CARVE(keys, double, a.PK);
+  CARVE(keys, double, U + 2);  // order keys: selection pool [PK] / new [Ctot] then old [S]
   CARVE(red_d, double, 8);
-  CARVE(st_uniq, uint32_t, U * a.Hw);
-  CARVE(st_child, uint32_t, (size_t)a.Cg * a.Hw);
+  CARVE(st_uniq, uint32_t, U * a.Hs);
+  CARVE(st_child, uint32_t, (size_t)a.Cg * a.Hs);
   CARVE(table, int, a.HT);
   CARVE(pool, int, a.PK);
   CARVE(slot, int, a.Cg > 0 ? a.Cg : 1);
@@ -87,7 +93,7 @@ __host__ __device__ inline size_t estep_carve(const EstepDev &a, unsigned char *
 
 // ---- hash table over packed states --------------------------------------------------------
 __device__ __forceinline__ const uint32_t *tag_state(const EstepDev &a, const EstepSmem &s, int tag) {
-  return tag >= TAG_CHILD ? s.st_child + (size_t)(tag - TAG_CHILD) * a.Hw : s.st_uniq + (size_t)tag * a.Hw;
+  return tag >= TAG_CHILD ? s.st_child + (size_t)(tag - TAG_CHILD) * a.Hs : s.st_uniq + (size_t)tag * a.Hs;
 }
 // read-only probe: index of the uniq entry equal to st, or -1
 __device__ __forceinline__ int table_find(const EstepDev &a, const EstepSmem &s, const uint32_t *st) {
@@ -118,6 +124,38 @@ __device__ __forceinline__ int table_insert(const EstepDev &a, const EstepSmem &
     p = (p + 1) & mask;
   }
   return -1;  // table full: cannot happen, HT >= 2 * (S + Ctot)
+}
+
+// ---- rank counting on order keys ------------------------------------------------------------
+// One f64 compare per pair: the low mantissa bits of a key carry the element's index, so keys are
+// pairwise distinct and values that agree in all higher bits (|rel. difference| < 2^-44 for
+// U <= 256) are ordered by index -- the smaller index compares LARGER when `hi` is true (ranking by
+// value descending, index ascending), SMALLER otherwise (value ascending, index ascending).
+__device__ __forceinline__ double order_key(double v, uint32_t idx, uint32_t mask, bool hi) {
+  uint64_t b = (uint64_t)__double_as_longlong(v);
+  const bool neg = (b >> 63) != 0;
+  const uint32_t code = (hi != neg) ? (mask - idx) : idx;
+  return __longlong_as_double((long long)((b & ~(uint64_t)mask) | code));
+}
+__device__ __forceinline__ int count_greater(const double *keys, int n, double k) {
+  int r = 0, j = 0;
+  for (; j + 4 <= n; j += 4) {
+    const double2 x = *reinterpret_cast<const double2 *>(keys + j);
+    const double2 y = *reinterpret_cast<const double2 *>(keys + j + 2);
+    r += (int)(x.x > k) + (int)(x.y > k) + (int)(y.x > k) + (int)(y.y > k);
+  }
+  for (; j < n; ++j) r += (int)(keys[j] > k);
+  return r;
+}
+__device__ __forceinline__ int count_less(const double *keys, int n, double k) {
+  int r = 0, j = 0;
+  for (; j + 4 <= n; j += 4) {
+    const double2 x = *reinterpret_cast<const double2 *>(keys + j);
+    const double2 y = *reinterpret_cast<const double2 *>(keys + j + 2);
+    r += (int)(x.x < k) + (int)(x.y < k) + (int)(y.x < k) + (int)(y.y < k);
+  }
+  for (; j < n; ++j) r += (int)(keys[j] < k);
+  return r;
 }
 
 // ---- mutation helpers -----------------------------------------------------------------------
@@ -167,7 +205,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
   EstepSmem s;
   estep_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
-  const int Hw = a.Hw, S = a.S;
+  const int Hw = a.Hw, Hs = a.Hs, S = a.S;
   const int Hm = a.background ? a.H - 1 : a.H;
   double acc_F = 0.0, acc_U = 0.0, acc_sub = 0.0, acc_eval = 0.0;
   unsigned long long cnt_nan = 0, cnt_small = 0, cnt_inf = 0;
@@ -178,7 +216,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
     // ---- load K^n, evaluator tables ---------------------------------------------------------
     {
       const uint32_t *src = a.states + n * (int64_t)S * Hw;
-      for (int i = tid; i < S * Hw; i += T) s.st_uniq[i] = src[i];
+      for (int i = tid; i < S * Hw; i += T) s.st_uniq[(i / Hw) * Hs + (i % Hw)] = src[i];
       for (int i = tid; i < a.HT; i += T) s.table[i] = TAG_EMPTY;
       for (int i = tid; i < S + a.Ctot; i += T) s.redisc[i] = 0;
       ev.template setup<T>(n, s.eval_smem);
@@ -193,10 +231,10 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         lpj_perm = ev.eval_zero(f0);
         if (tid == 0 && f0) { if (f0 & 1) ++cnt_nan; else if (f0 & 2) ++cnt_small; else ++cnt_inf; }
       }
-      ev.template eval_batch<T>(s.st_uniq, S, s.lpj_uniq, fl);
+      ev.template eval_batch<T>(s.st_uniq, Hs, S, s.lpj_uniq, fl);
       fl = group_or<T>(fl, s.red_i);
       if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
-      for (int i = tid; i < S; i += T) table_insert(a, s, s.st_uniq + (size_t)i * Hw, i);
+      for (int i = tid; i < S; i += T) table_insert(a, s, s.st_uniq + (size_t)i * Hs, i);
     }
     gsync<T>();
 
@@ -212,7 +250,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         nc = a.inj_count[n * (int64_t)a.n_generations + g];
         if (nc > a.Cg) nc = a.Cg;
         const uint32_t *src = a.inj_children + ((n * (int64_t)a.n_generations + g) * a.inj_cmax) * (int64_t)Hw;
-        for (int i = tid; i < nc * Hw; i += T) s.st_child[i] = src[i];
+        for (int i = tid; i < nc * Hw; i += T) s.st_child[(i / Hw) * Hs + (i % Hw)] = src[i];
       } else {
         // ---- parent selection (eas.py:138-150) -------------------------------------------------
         int take = pool_n < a.n_parents ? pool_n : a.n_parents;
@@ -234,17 +272,12 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             } else {
               key = u;
             }
-            s.keys[i] = key;
+            s.keys[i] = order_key(key, (uint32_t)i, a.mask_p, true);
           }
           gsync<T>();
           // the `take` largest keys, by rank counting (strict total order: key desc, index asc)
           for (int i = tid; i < pool_n; i += T) {
-            double k = s.keys[i];
-            int r = 0;
-            for (int j = 0; j < pool_n; ++j) {
-              double kj = s.keys[j];
-              r += (kj > k) || (kj == k && j < i);
-            }
+            int r = count_greater(s.keys, pool_n, s.keys[i]);
             if (r < take) s.parents[r] = s.pool[i];
           }
           gsync<T>();
@@ -275,8 +308,8 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           }
           for (int c = tid; c < nc; c += T) {
             int p = c / C;
-            const uint32_t *src = s.st_uniq + (size_t)s.parents[p] * Hw;
-            uint32_t *dst = s.st_child + (size_t)c * Hw;
+            const uint32_t *src = s.st_uniq + (size_t)s.parents[p] * Hs;
+            uint32_t *dst = s.st_child + (size_t)c * Hs;
             for (int w = 0; w < Hw; ++w) dst[w] = src[w];
             if (a.background) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
             if (mut == EVO_MUT_RANDFLIP) flip_bit(dst, s.slot[c]);
@@ -293,9 +326,9 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             int j = i + 1 + rem;
             uint4 r = rng.draw(RNG_CROSS, g, (uint32_t)q);
             int cp = 1 + (Hm > 1 ? (int)urange(r.x, (uint32_t)(Hm - 1)) : 0);  // cp in {1..Hm-1}
-            const uint32_t *pa = s.st_uniq + (size_t)s.parents[i] * Hw;
-            const uint32_t *pb = s.st_uniq + (size_t)s.parents[j] * Hw;
-            uint32_t *c0 = s.st_child + (size_t)(2 * q) * Hw, *c1 = c0 + Hw;
+            const uint32_t *pa = s.st_uniq + (size_t)s.parents[i] * Hs;
+            const uint32_t *pb = s.st_uniq + (size_t)s.parents[j] * Hs;
+            uint32_t *c0 = s.st_child + (size_t)(2 * q) * Hs, *c1 = c0 + Hs;
             for (int w = 0; w < Hw; ++w) {
               int lo = w << 5;
               uint32_t head = cp >= lo + 32 ? 0xFFFFFFFFu : (cp <= lo ? 0u : ((1u << (cp - lo)) - 1u));
@@ -321,7 +354,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
 
       // ---- de-duplicate against (permanent, K^n, earlier new) and among the children ----------
       for (int c = tid; c < nc; c += T) {
-        const uint32_t *st = s.st_child + (size_t)c * Hw;
+        const uint32_t *st = s.st_child + (size_t)c * Hs;
         unsigned char stt = 1;  // candidate
         if (a.S_perm > 0 && popc_state(st, Hw) == 0) stt = 0;
         else {
@@ -332,7 +365,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       }
       gsync<T>();
       for (int c = tid; c < nc; c += T)
-        if (s.status[c]) s.slot[c] = table_insert(a, s, s.st_child + (size_t)c * Hw, TAG_CHILD + c);
+        if (s.status[c]) s.slot[c] = table_insert(a, s, s.st_child + (size_t)c * Hs, TAG_CHILD + c);
       gsync<T>();
       // first occurrence of each new state wins; compact winners (child order) behind st_uniq
       int u_g = 0;
@@ -345,8 +378,8 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         int off = group_scan_flag<T>(win, tot, s.red_i);
         if (win) {
           int idx = S + U + u_g + off;
-          const uint32_t *src = s.st_child + (size_t)c * Hw;
-          uint32_t *dst = s.st_uniq + (size_t)idx * Hw;
+          const uint32_t *src = s.st_child + (size_t)c * Hs;
+          uint32_t *dst = s.st_uniq + (size_t)idx * Hs;
           for (int w = 0; w < Hw; ++w) dst[w] = src[w];
           s.status[c] = 2;
           s.table[sl] = idx;  // from now on a uniq entry (losers of this state compare against a child tag and fail)
@@ -359,7 +392,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       {
         unsigned fl = 0;
         if (u_g > 0) {
-          ev.template eval_batch<T>(s.st_uniq + (size_t)(S + U) * Hw, u_g, s.lpj_uniq + S + U, fl);
+          ev.template eval_batch<T>(s.st_uniq + (size_t)(S + U) * Hs, Hs, u_g, s.lpj_uniq + S + U, fl);
           fl = group_or<T>(fl, s.red_i);
           if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
         }
@@ -400,19 +433,13 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         mn = -group_max<T>(-mn, s.red_d);
         // only candidates above the worst old state can ever be accepted
         const double *ln = s.lpj_uniq + S;
-        for (int i = tid; i < U; i += T) {
-          double v = ln[i];
-          int r = Mp;
-          if (v > mn) {
-            r = 0;
-            for (int j = 0; j < U; ++j) { double vj = ln[j]; r += (vj > v) || (vj == v && j < i); }
-          }
-          s.rnk[i] = r;
-        }
+        double *kn = s.keys, *ko = s.keys + ((a.Ctot + 1) & ~1);
+        for (int i = tid; i < U; i += T) kn[i] = order_key(ln[i], (uint32_t)i, a.mask_c, true);
+        for (int k = tid; k < S; k += T) ko[k] = order_key(s.lpj_uniq[k], (uint32_t)k, a.mask_s, false);
+        gsync<T>();
+        for (int i = tid; i < U; i += T) s.rnk[i] = (ln[i] > mn) ? count_greater(kn, U, kn[i]) : Mp;
         for (int k = tid; k < S; k += T) {
-          double v = s.lpj_uniq[k];
-          int r = 0;
-          for (int j = 0; j < S; ++j) { double vj = s.lpj_uniq[j]; r += (vj < v) || (vj == v && j < k); }
+          int r = count_less(ko, S, ko[k]);
           if (r < Mp) s.old_by_rank[r] = k;
         }
         gsync<T>();
@@ -423,8 +450,8 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           int k = s.old_by_rank[r];
           double v = ln[i];
           if (!(v > s.lpj_uniq[k])) continue;
-          const uint32_t *src = s.st_uniq + (size_t)(S + i) * Hw;
-          uint32_t *dst = s.st_uniq + (size_t)k * Hw;
+          const uint32_t *src = s.st_uniq + (size_t)(S + i) * Hs;
+          uint32_t *dst = s.st_uniq + (size_t)k * Hs;
           uint32_t *gdst = a.states + (n * (int64_t)S + k) * Hw;
           for (int w = 0; w < Hw; ++w) { uint32_t x = src[w]; dst[w] = x; gdst[w] = x; }
           s.rnk[i] = -1 - k;  // remembered; lpj written after the barrier (other threads still compare against it)
@@ -464,6 +491,44 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
     if (cnt_inf) atomicAdd(a.acc + 5, (double)cnt_inf);
     atomicAdd(a.acc + 6, acc_eval);
   }
+}
+
+// ---- launch: threads per datapoint group -------------------------------------------------------
+// T in {32, 64, 128, 256}: the evaluator's hint for the work per datapoint (max(S, children per
+// generation)); EVO_ESTEP_T overrides it (tuning runs).  Persistent grid = SMs x resident CTAs.
+template <class Eval>
+static int launch_estep_any(const EstepDev &dv, Eval ev, cudaStream_t st) {
+  int work = dv.S > dv.Cg ? dv.S : dv.Cg;
+  int T = ev.threads_hint(work);
+  if (const char *e = getenv("EVO_ESTEP_T")) { int t = atoi(e); if (t > 0) T = t; }
+  T = T <= 32 ? 32 : (T <= 64 ? 64 : (T <= 128 ? 128 : 256));
+  size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes(T);
+  if (smem > 227 * 1024) {
+    set_error("evo_estep: %zu bytes of shared memory per datapoint exceed 227 KB", smem);
+    return EVO_ERR_UNSUPPORTED;
+  }
+#define EVO_LAUNCH_T(TT)                                                                              \
+  {                                                                                                   \
+    auto k = estep_kernel<Eval, TT>;                                                                  \
+    if (smem > 48 * 1024)                                                                             \
+      EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
+    int per_sm = 1;                                                                                   \
+    EVO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, TT, smem));                    \
+    if (per_sm < 1) {                                                                                 \
+      set_error("evo_estep: %zu bytes of shared memory per datapoint exceed the SM", smem);           \
+      return EVO_ERR_UNSUPPORTED;                                                                     \
+    }                                                                                                 \
+    int64_t g = (int64_t)sm_count() * per_sm;                                                         \
+    if (g > dv.N) g = dv.N;                                                                           \
+    k<<<(int)g, TT, smem, st>>>(dv, ev);                                                              \
+  }
+  if (T == 32) EVO_LAUNCH_T(32)
+  else if (T == 64) EVO_LAUNCH_T(64)
+  else if (T == 128) EVO_LAUNCH_T(128)
+  else EVO_LAUNCH_T(256)
+#undef EVO_LAUNCH_T
+  EVO_LAUNCH_CHECK("estep");
+  return EVO_OK;
 }
 
 }  // namespace evo

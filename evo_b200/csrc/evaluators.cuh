@@ -1,7 +1,7 @@
 // Log-pseudo-joint evaluators.  Each evaluator is a small POD passed by value to the kernels with
 //   smem_bytes()                      dynamic shared memory it needs per datapoint group
 //   setup<T>(n, smem)                 cooperative per-datapoint load (caller syncs afterwards)
-//   eval_batch<T>(st, cnt, out, fl)   cooperative evaluation of cnt packed states -> out[0..cnt)
+//   eval_batch<T>(st, ld, cnt, out, fl)   cooperative evaluation of cnt packed states (row stride ld words) -> out[0..cnt)
 //   eval_zero()                       lpj of the all-zero state (permanent state), per thread
 #pragma once
 #include "common.cuh"
@@ -98,8 +98,8 @@ struct BscGramEval {
   }
 
   template <int T>
-  __device__ void eval_batch(const uint32_t *st, int cnt, double *out, unsigned &flags) const {
-    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one<T>(st + (size_t)i * Hw), flags);
+  __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) const {
+    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one<T>(st + (size_t)i * ld), flags);
   }
   __device__ double eval_zero(unsigned &flags) const { return lpj_sanitise(pre1 * yn2, flags); }
 };
@@ -154,8 +154,8 @@ struct BscDirectEval {
   }
 
   template <int T>
-  __device__ void eval_batch(const uint32_t *st, int cnt, double *out, unsigned &flags) const {
-    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one(st + (size_t)i * Hw), flags);
+  __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) const {
+    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one(st + (size_t)i * ld), flags);
   }
   __device__ double eval_zero(unsigned &flags) const {
     double s = 0.0;
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(T) lpj_kernel(Eval ev, const uint32_t *__restr
     __syncthreads();
     unsigned fl = 0;
     const uint32_t *st = shared_states ? states : states + n * (int64_t)Sp * Hw;
-    ev.template eval_batch<T>(st, Sp, out + n * ld, fl);
+    ev.template eval_batch<T>(st, Hw, Sp, out + n * ld, fl);
     fl = group_or<T>(fl, red_i);
     if (threadIdx.x == 0 && fl) { if (fl & 1) ++c_nan; else if (fl & 2) ++c_small; else ++c_inf; }
   }
