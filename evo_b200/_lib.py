@@ -70,7 +70,8 @@ SIGNATURES = {
     "evo_estep": (_i, [C.POINTER(EstepArgs), _vp]),
     "evo_select_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "evo_free_energy": (_i, [_vp, _i64, _i, _i64, _vp, _vp]),
-    "evo_bsc_suffstats": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp]),
+    "evo_bsc_suffstats_workspace_bytes": (_i64, [_i64, _i, _i]),
+    "evo_bsc_suffstats": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _i64, _vp]),
     "evo_es3c_set_scratch": (_i, [_vp, _i]),
     "evo_es3c_lpj": (_i, [_vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _vp, _i64, _vp, _vp]),
     "evo_es3c_suffstats": (_i, [C.POINTER(Es3cStatsArgs), _vp]),

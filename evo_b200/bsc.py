@@ -266,9 +266,14 @@ class BSC(Model):
         else:
             Ym = dd.Y
         stats = torch.zeros(H * D + H * H + H + 1 + ACC_LEN, dtype=torch.float64, device=self.device)
+        ws = dd.cache.get("stats_ws")
+        if ws is None:
+            nb = int(self.lib.evo_bsc_suffstats_workspace_bytes(dd.N, D, H))
+            ws = dd.cache["stats_ws"] = torch.empty(nb, dtype=torch.uint8, device=self.device) if nb > 0 else False
         self._call("evo_bsc_suffstats", _lib.ptr(ss["ss_dev"]), _lib.ptr(ss["lpj_dev"]), _lib.ptr(Ym), dd.N, D, H,
                    int(ss["ss_dev"].shape[1]), int(ss["S_perm"]), int(bool(ss["permanent"]["allzero"])),
-                   float(model_params["pre1"]), float(model_params["pil_bar"]), _lib.ptr(stats), None)
+                   float(model_params["pre1"]), float(model_params["pil_bar"]), _lib.ptr(stats), None,
+                   _lib.ptr(ws) if ws is not False else None, int(ws.numel()) if ws is not False else 0)
         return stats
 
     def M_step(self, model_params, my_suff_stat, my_data):

@@ -133,12 +133,26 @@ constexpr double Q_SKIP = 1e-18;  // posterior mass below f64 resolution of the 
 //   pies += es ; Wp[h,:] += es_h y_n ; Wq[h,h'] += sum_k q_k s_kh s_kh' (h' <= h) ;
 //   sigma += sum_k q_k |y - W s_k|^2 = sum_k q_k (lpj_k - pil_bar |s_k|) / pre1   (same theta)
 // ------------------------------------------------------------------------------------------
+// Sparse <s>_n lists handed from the statistics pass to the Wp pass (bsc_wp_kernel): per datapoint
+// up to WP_LCAP (latent, <s_h>) pairs; entries beyond the capacity are accumulated directly.
+constexpr int WP_LCAP = 64;
+constexpr int WP_CW = 64;  // observables per Wp slice
+constexpr int WP_WARPS = 32;  // warps of the Wp pass; warp w owns the latents [w*hb, (w+1)*hb), hb = ceil(H/32)
+struct WpLists {
+  uint8_t *off;   // [N][WP_WARPS + 1 (+pad to 40)]: the (ascending-h) list of datapoint n restricted to warp w
+                  // is [off[w], off[w+1]); off[WP_WARPS] = number of listed entries
+  uint16_t *h;    // [N][WP_LCAP]
+  double *e;      // [N][WP_LCAP]
+};
+constexpr int WP_OFF = 40;
+
 template <int T>
 __global__ void __launch_bounds__(T) bsc_suffstats_kernel(const uint32_t *__restrict__ states,
                                                           const double *__restrict__ lpj,
                                                           const float *__restrict__ Ym, int64_t N, int D, int H, int Hw,
                                                           int S, int S_perm, double pre1, double pil_bar,
-                                                          double *__restrict__ stats, float *__restrict__ Es_out) {
+                                                          double *__restrict__ stats, float *__restrict__ Es_out,
+                                                          WpLists lists) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ double red_d[8];
   __shared__ int red_i[8];
@@ -150,10 +164,11 @@ __global__ void __launch_bounds__(T) bsc_suffstats_kernel(const uint32_t *__rest
   double *Wp = stats, *Wq = stats + (int64_t)H * D, *pies = Wq + (int64_t)H * H, *sig = pies + H;
   double sig_acc = 0.0;
   const int cols = S + S_perm;
+  for (int h = threadIdx.x; h < H; h += T) es[h] = 0.0;  // kept zero between datapoints (active entries reset below)
   for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
     __syncthreads();
-    for (int h = threadIdx.x; h < H; h += T) es[h] = 0.0;
-    for (int d = threadIdx.x; d < D; d += T) y[d] = Ym[n * D + d];
+    if (!lists.off)
+      for (int d = threadIdx.x; d < D; d += T) y[d] = Ym[n * D + d];
     posterior<T>(lpj + n * cols, cols, q, red_d);
     const uint32_t *st = states + n * (int64_t)S * Hw;
     // per state: es, Wq, sigma
@@ -206,15 +221,131 @@ __global__ void __launch_bounds__(T) bsc_suffstats_kernel(const uint32_t *__rest
     for (int i = threadIdx.x; i < na; i += T) atomicAdd(pies + act[i], es[act[i]]);
     if (Es_out)
       for (int h = threadIdx.x; h < H; h += T) Es_out[n * H + h] = (float)es[h];
-    for (int i = 0; i < na; ++i) {
-      int h = act[i];
-      double e = es[h];
-      double *row = Wp + (int64_t)h * D;
-      for (int d = threadIdx.x; d < D; d += T) atomicAdd(row + d, e * (double)y[d]);
+    if (lists.off) {
+      // hand the sparse <s>_n (ascending h) to the Wp pass; overflow entries are accumulated here
+      const int nl = na < WP_LCAP ? na : WP_LCAP;
+      if (threadIdx.x <= WP_WARPS) {
+        const int hb = (H + WP_WARPS - 1) / WP_WARPS, bound = threadIdx.x * hb;
+        int lo = 0, hi = nl;  // first entry with h >= bound
+        while (lo < hi) { int mid = (lo + hi) >> 1; if (act[mid] < bound) lo = mid + 1; else hi = mid; }
+        lists.off[n * WP_OFF + threadIdx.x] = (uint8_t)lo;
+      }
+      for (int i = threadIdx.x; i < na && i < WP_LCAP; i += T) {
+        lists.h[n * WP_LCAP + i] = (uint16_t)act[i];
+        lists.e[n * WP_LCAP + i] = es[act[i]];
+      }
+      for (int i = WP_LCAP; i < na; ++i) {
+        int h = act[i];
+        double e = es[h];
+        double *row = Wp + (int64_t)h * D;
+        for (int d = threadIdx.x; d < D; d += T) atomicAdd(row + d, e * (double)Ym[n * D + d]);
+      }
+    } else {
+      for (int i = 0; i < na; ++i) {
+        int h = act[i];
+        double e = es[h];
+        double *row = Wp + (int64_t)h * D;
+        for (int d = threadIdx.x; d < D; d += T) atomicAdd(row + d, e * (double)y[d]);
+      }
     }
+    __syncthreads();
+    for (int i = threadIdx.x; i < na; i += T) es[act[i]] = 0.0;
   }
   sig_acc = group_sum<T>(sig_acc, red_d);
   if (threadIdx.x == 0) atomicAdd(sig, sig_acc);
+}
+
+// ------------------------------------------------------------------------------------------
+// Wp[h, :] += sum_n <s_h>_n y_n  (bsc.py:204-206) from the sparse lists of the statistics pass.
+// CTA = (slice of WP_CW observables, contiguous chunk of datapoints).  The H x WP_CW slice of Wp is
+// accumulated in SHARED memory (f64); warp w owns the latents h = w (mod 16), so no two warps ever
+// touch the same cell and no atomics are needed until the single flush at the end.  Lists and the
+// y slice of WP_BATCH datapoints arrive through a cp.async double buffer (one HBM latency per batch,
+// hidden behind the previous batch).
+// ------------------------------------------------------------------------------------------
+constexpr int WP_BATCH = 16, WP_THREADS = 32 * WP_WARPS;
+struct WpBatch {
+  double e[WP_BATCH][WP_LCAP];
+  float y[WP_BATCH][WP_CW];
+  uint16_t h[WP_BATCH][WP_LCAP];
+  uint8_t off[WP_BATCH][WP_OFF];
+};
+__device__ __forceinline__ void cp_async16(void *dst, const void *src, bool pred) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  int sz = pred ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void *dst, const void *src, bool pred) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  int sz = pred ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+
+__global__ void __launch_bounds__(WP_THREADS) bsc_wp_kernel(WpLists lists, const float *__restrict__ Ym, int64_t N, int D,
+                                                            int H, int n_slices, double *__restrict__ Wp) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WpBatch *buf = reinterpret_cast<WpBatch *>(smem_raw);               // [2]
+  double *acc = reinterpret_cast<double *>(smem_raw + 2 * sizeof(WpBatch));  // [H][WP_CW]
+  const int slice = blockIdx.x % n_slices, chunk = blockIdx.x / n_slices, chunks = gridDim.x / n_slices;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t lo = N * chunk / chunks, hi = N * (chunk + 1) / chunks;
+  const int nb = (int)((hi - lo + WP_BATCH - 1) / WP_BATCH);
+  const int col0 = slice * WP_CW;
+  for (int i = threadIdx.x; i < H * WP_CW; i += WP_THREADS) acc[i] = 0.0;
+
+  auto issue = [&](int b) {
+    WpBatch &B = buf[b & 1];
+    const int64_t n0 = lo + (int64_t)b * WP_BATCH;
+    for (int i = threadIdx.x; i < WP_BATCH * WP_LCAP / 2; i += WP_THREADS) {  // e: 16 B = 2 doubles
+      const bool ok = n0 + i / (WP_LCAP / 2) < hi;
+      cp_async16(&B.e[0][0] + 2 * i, ok ? lists.e + n0 * WP_LCAP + 2 * i : lists.e, ok);
+    }
+    for (int i = threadIdx.x; i < WP_BATCH * WP_LCAP / 8; i += WP_THREADS) {  // h: 16 B = 8 uint16
+      const bool ok = n0 + i / (WP_LCAP / 8) < hi;
+      cp_async16(&B.h[0][0] + 8 * i, ok ? lists.h + n0 * WP_LCAP + 8 * i : lists.h, ok);
+    }
+    for (int i = threadIdx.x; i < WP_BATCH * WP_CW; i += WP_THREADS) {        // y slice, 4 B each (any D)
+      const int j = i / WP_CW, c = i % WP_CW;
+      const bool ok = n0 + j < hi && col0 + c < D;
+      cp_async4(&B.y[j][c], ok ? Ym + (n0 + j) * D + col0 + c : Ym, ok);
+    }
+    for (int i = threadIdx.x; i < WP_BATCH * WP_OFF / 4; i += WP_THREADS) {   // offsets (zero-filled past the end)
+      const bool ok = n0 + i / (WP_OFF / 4) < hi;
+      cp_async4(&B.off[0][0] + 4 * i, ok ? lists.off + n0 * WP_OFF + 4 * i : lists.off, ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  if (nb > 0) issue(0);
+  for (int b = 0; b < nb; ++b) {
+    if (b + 1 < nb) {
+      issue(b + 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const WpBatch &B = buf[b & 1];
+#pragma unroll 2
+    for (int j = 0; j < WP_BATCH; ++j) {
+      const int o0 = B.off[j][warp], o1 = B.off[j][warp + 1];
+      if (o0 == o1) continue;
+      const double y0 = (double)B.y[j][lane], y1 = (double)B.y[j][lane + 32];
+      for (int i = o0; i < o1; ++i) {
+        double *row = acc + (size_t)B.h[j][i] * WP_CW;
+        const double ee = B.e[j][i];
+        row[lane] += ee * y0;
+        row[lane + 32] += ee * y1;
+      }
+    }
+    __syncthreads();  // this buffer is refilled by the load issued in the next iteration
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < H * WP_CW; i += WP_THREADS) {
+    const int h = i / WP_CW, c = col0 + (i % WP_CW);
+    const double v = acc[i];
+    if (c < D && v != 0.0) atomicAdd(Wp + (int64_t)h * D + c, v);
+  }
 }
 
 // y_rec[n, ~keep] = W[~keep] <s>_n  (Model.reconstruct _models.py:614-665 + BSC.modelmean bsc.py:279-287)
@@ -373,20 +504,48 @@ extern "C" int evo_free_energy(const double *lpj, int64_t N, int cols, int64_t l
   return EVO_OK;
 }
 
+static size_t wp_smem(int H) { return 2 * sizeof(WpBatch) + (size_t)H * WP_CW * sizeof(double); }
+static bool wp_lists_applicable(int H) { return wp_smem(H) <= 227 * 1024 && H <= 65535; }
+
+extern "C" int64_t evo_bsc_suffstats_workspace_bytes(int64_t N, int D, int H) {
+  (void)D;
+  if (N <= 0 || !wp_lists_applicable(H)) return 0;
+  return (int64_t)(N * (WP_LCAP * (sizeof(double) + sizeof(uint16_t)) + WP_OFF) + 64);
+}
+
 extern "C" int evo_bsc_suffstats(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H,
                                  int S, int S_perm, int allzero, double pre1, double pil_bar, double *stats,
-                                 float *Es_out, void *stream) {
+                                 float *Es_out, void *workspace, int64_t workspace_bytes, void *stream) {
   (void)allzero;
   EVO_REQUIRE(N >= 0 && D > 0 && H > 0 && S > 0, "bad sizes");
   if (N == 0) return EVO_OK;
   int Hw = words_for(H);
+  WpLists lists{nullptr, nullptr, nullptr};
+  if (workspace && wp_lists_applicable(H) && workspace_bytes >= evo_bsc_suffstats_workspace_bytes(N, D, H)) {
+    unsigned char *p = reinterpret_cast<unsigned char *>(workspace);
+    EVO_REQUIRE(((uintptr_t)p & 15) == 0, "workspace must be 16-byte aligned");
+    lists.e = reinterpret_cast<double *>(p);
+    lists.h = reinterpret_cast<uint16_t *>(p + (size_t)N * WP_LCAP * sizeof(double));
+    lists.off = p + (size_t)N * WP_LCAP * (sizeof(double) + sizeof(uint16_t));
+  }
   size_t smem = sizeof(double) * ((size_t)H + S + S_perm) + sizeof(float) * (size_t)D + sizeof(int) * (size_t)H;
   constexpr int T = 128;
   auto k = bsc_suffstats_kernel<T>;
   if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   k<<<grid_for((const void *)k, T, smem, N), T, smem, (cudaStream_t)stream>>>(states, lpj, Ym, N, D, H, Hw, S, S_perm,
-                                                                              pre1, pil_bar, stats, Es_out);
+                                                                              pre1, pil_bar, stats, Es_out, lists);
   EVO_LAUNCH_CHECK("bsc_suffstats");
+  if (lists.off) {
+    int n_slices = (D + WP_CW - 1) / WP_CW;
+    int chunks = sm_count() / n_slices;
+    if (chunks < 1) chunks = 1;
+    if ((int64_t)chunks > N) chunks = (int)N;
+    size_t wsm = wp_smem(H);
+    if (wsm > 48 * 1024)
+      EVO_CUDA(cudaFuncSetAttribute(bsc_wp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
+    bsc_wp_kernel<<<n_slices * chunks, WP_THREADS, wsm, (cudaStream_t)stream>>>(lists, Ym, N, D, H, n_slices, stats);
+    EVO_LAUNCH_CHECK("bsc_wp");
+  }
   return EVO_OK;
 }
 

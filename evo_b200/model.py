@@ -98,6 +98,44 @@ class Model:
         dd.cache.pop("ynorm2", None)
         return dd
 
+    def stage_data(self, my_data):
+        """Start the host->device copy of `my_data["y"]` (pinned host memory) into the SPARE device
+        buffer on a side stream and return at once, so the copy of the next batch runs under the
+        kernels of the current step.  `adopt_staged` makes it the resident shard."""
+        dd = self.device_data(my_data)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        if getattr(dd, "Y_spare", None) is None:
+            dd.Y_spare = torch.empty_like(dd.Y)
+            dd.spare_free = None
+        y = my_data["y"]
+        src = y if isinstance(y, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(y))
+        cs = self._copy_stream
+        if dd.spare_free is not None:
+            cs.wait_event(dd.spare_free)  # kernels of the step that last read the spare buffer are done
+        with torch.cuda.stream(cs):
+            if src.dtype == dd.Y_spare.dtype:
+                dd.Y_spare.copy_(src, non_blocking=True)
+            else:
+                dd.Y_spare.copy_(src.to(dd.Y_spare.dtype))
+            if dd.incomplete:
+                dd.Y_spare.copy_(torch.where(dd.mask.bool(), dd.Y_spare, torch.zeros_like(dd.Y_spare)))
+            dd.staged = torch.cuda.Event()
+            dd.staged.record(cs)
+        return dd
+
+    def adopt_staged(self, my_data):
+        """The staged buffer becomes the resident shard: the compute stream waits for its copy, the
+        previous shard becomes the spare (free once everything enqueued so far has run)."""
+        dd = self.device_data(my_data)
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(dd.staged)
+        dd.spare_free = torch.cuda.Event()
+        dd.spare_free.record(cur)
+        dd.Y, dd.Y_spare = dd.Y_spare, dd.Y
+        dd.cache.pop("ynorm2", None)
+        return dd
+
     def _call(self, name, *args):
         with torch.cuda.device(self.device):
             ev = self._tick()

@@ -144,10 +144,14 @@ int evo_free_energy(const double *lpj, int64_t N, int cols, int64_t ld, double *
 
 /* ---- BSC M-step statistics (bsc.py:176-223) and estimator (_models.py:614-665) ------------ */
 /* stats layout (f64): [Wp H*D | Wq H*H | pies H | sigma_sum 1]; accumulated (+=), caller zeroes.
- * Ym = y or y_reconstructed (f32 [N][D]).  Only the lower triangle (h' <= h) of Wq is written. */
+ * Ym = y or y_reconstructed (f32 [N][D]).  Only the lower triangle (h' <= h) of Wq is written.
+ * workspace (optional, 16-byte aligned, evo_bsc_suffstats_workspace_bytes(N, D, H) bytes; 0 = not
+ * applicable for this H): with it, Wp is accumulated by a second kernel in shared-memory slices from
+ * per-datapoint sparse <s> lists instead of one global atomic per (datapoint, latent, observable). */
+int64_t evo_bsc_suffstats_workspace_bytes(int64_t N, int D, int H);
 int evo_bsc_suffstats(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D,
                       int H, int S, int S_perm, int allzero, double pre1, double pil_bar,
-                      double *stats, float *Es_out, void *stream);
+                      double *stats, float *Es_out, void *workspace, int64_t workspace_bytes, void *stream);
 /* y_rec[n][d] = sum_h <s_h>_n W[d][h] where recon_mask[n][d] == 0 (x false); other entries copy y;
  * rows whose infer_mask is all zero are left untouched (_models.py:646-648). */
 int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double *W, const float *Y,
