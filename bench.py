@@ -257,6 +257,7 @@ def run_ours(args):
     if w["model"] == "bsc":
         from evo_b200.bsc import BSC
         model = BSC(w["D"], w["H"], w["K"], comm=comm, device=device)
+        model.tables = args.tables
     else:
         from evo_b200.sssc import SSSC
         model = SSSC(w["D"], w["H"], w["K"], comm=comm, device=device)
@@ -504,6 +505,8 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=0, help="datapoints per GPU (default: the workload's N)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--tables", default="tc", choices=["tc", "f64"],
+                    help="BSC table B = Y W: tcgen05 split-precision GEMM (default) or the f64 SIMT GEMM")
     ap.add_argument("--lpj-compare", action="store_true",
                     help="time the dense tcgen05 log-joint against the sparse Gram kernel (BSC workloads)")
     ap.add_argument("--cpu-worker", type=int, default=-1, help=argparse.SUPPRESS)

@@ -63,6 +63,9 @@ SIGNATURES = {
     "evo_states_unpack": (_i, [_vp, _vp, _i64, _i, _vp]),
     "evo_states_init": (_i, [_vp, _i64, _i, _i, _i, _i, _d, _u64, _i64, _vp]),
     "evo_bsc_prepare": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp, _vp, _vp]),
+    "evo_bsc_tables_tc_workspace_bytes": (_i64, [_i64, _i, _i]),
+    "evo_bsc_tables_tc_set_data": (_i, [_vp, _i64, _i, _i, _vp, _vp]),
+    "evo_bsc_tables_tc": (_i, [_vp, _i64, _i, _i, _vp, _vp, _vp]),
     "evo_bsc_lpj": (_i, [_i, _vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _d, _d, _vp, _i64, _vp, _vp]),
     "evo_bsc_lpj_gemm_workspace_bytes": (_i64, [_i, _i]),
     "evo_bsc_lpj_gemm_prepare": (_i, [_vp, _i, _i, _vp, _vp]),

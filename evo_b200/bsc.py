@@ -15,6 +15,9 @@ class BSC(Model):
     def __init__(self, D, H, S, to_learn=("W", "pi", "sigma"), comm=None, device=None):
         Model.__init__(self, D, H, S, to_learn, comm, device)
         self.eps_lpj = np.finfo(np.float64).min  # bsc.py:23-24
+        # table B = Y W of the Gram form: "f64" (SIMT GEMM, bit-reproducible parity path) or "tc"
+        # (tcgen05 split-precision GEMM, lpj within 1e-5 of the f64 reference)
+        self.tables = "f64"
 
     # ---- generative model (bsc.py:27-57), cold path ---------------------------------------------
     def generate_from_hidden(self, model_params, my_hdata):
@@ -92,9 +95,22 @@ class BSC(Model):
             c["G"] = torch.empty((H, H), dtype=torch.float64, device=self.device)
             c["B"] = torch.empty((dd.N, H), dtype=torch.float64, device=self.device)
         yn = None
-        if "ynorm2" not in c:
+        fresh = "ynorm2" not in c  # first use of this shard (or its values were replaced)
+        if fresh:
             c["ynorm2"] = torch.empty((dd.N,), dtype=torch.float64, device=self.device)
             yn = c["ynorm2"]
+        if self.tables == "tc":
+            # B = Y W on the tensor cores (fp16 hi+lo split, <= 2e-6 of max|B|); G and |y|^2 stay f64
+            if "tc_ws" not in c:
+                nb = int(self.lib.evo_bsc_tables_tc_workspace_bytes(dd.N, self.D, H))
+                c["tc_ws"] = torch.empty(nb, dtype=torch.uint8, device=self.device)
+                fresh = True
+            self._call("evo_bsc_prepare", _lib.ptr(Wd), _lib.ptr(dd.Y), dd.N, self.D, H, _lib.ptr(c["G"]), None,
+                       _lib.ptr(yn))
+            if fresh:
+                self._call("evo_bsc_tables_tc_set_data", _lib.ptr(dd.Y), dd.N, self.D, H, _lib.ptr(c["tc_ws"]))
+            self._call("evo_bsc_tables_tc", _lib.ptr(Wd), dd.N, self.D, H, _lib.ptr(c["tc_ws"]), _lib.ptr(c["B"]))
+            return
         self._call("evo_bsc_prepare", _lib.ptr(Wd), _lib.ptr(dd.Y), dd.N, self.D, H, _lib.ptr(c["G"]), _lib.ptr(c["B"]),
                    _lib.ptr(yn))
 

@@ -421,6 +421,254 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
+
+// =================================================================================================
+// B = Y W on the tensor cores (table of the Gram form, evo_bsc_prepare's f64 SIMT GEMM at 2 N D H
+// flop is the largest dense contraction of a BSC iteration at D = H = 1024).
+//   C[n][h] = sum_d Y[n][d] W[d][h]:  M = N datapoints (tiles of 128), N = H (tiles of <= 256), K = D.
+// Both operands are scaled by a power of two and split into fp16 hi + lo planes; three tensor passes
+// (hi*hi, hi*lo, lo*hi) accumulate in the same fp32 TMEM tile -- the dropped lo*lo term is 2^-22
+// relative.  Y planes are built once per dataset, W' planes once per parameter set.  Epilogue:
+// TMEM -> f64 -> B[n][h].  Measured against the f64 kernel: <= 1e-6 of max|B| (tests state 2e-6).
+// =================================================================================================
+constexpr int T_STAGES = 2;
+constexpr int T_STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;  // {Y hi, Y lo, W' hi, W' lo} of one k-block: 96 KB
+constexpr int T_THREADS = 192;
+constexpr size_t T_SMEM_BYTES = 1024 + (size_t)T_STAGES * T_STAGE_BYTES + 8 * (2 * T_STAGES + 4) + 16;
+
+struct TArgs {
+  int64_t N;
+  int H, KB, n_tiles, box_rows;
+  int64_t a_plane_rows;  // rows of one Y plane (N rounded up to 128)
+  int b_plane_rows;      // rows of one W' plane (n_tiles * box_rows)
+  int Hp;                // H rounded up to 16
+  const float *descale;  // device scalar 2^-(ey + ew)
+  double *B;
+};
+
+__global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_constant__ CUtensorMap tmapA,
+                                                                  const __grid_constant__ CUtensorMap tmapB, TArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t *sm = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (size_t)T_STAGES * T_STAGE_BYTES);
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * T_STAGES + 4);
+  const uint32_t bar0 = smem_u32(bars);
+  auto FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
+  auto EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(T_STAGES + s); };
+  auto T_FULL = [&](int s) { return bar0 + 8u * (uint32_t)(2 * T_STAGES + s); };
+  auto T_EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * T_STAGES + 2 + s); };
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < T_STAGES; ++s) { mbar_init(FULL(s), 1); mbar_init(EMPTY(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(T_FULL(s), 1); mbar_init(T_EMPTY(s), 128); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int64_t tiles = (a.N + BM - 1) / BM;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer =====
+      int st = 0;
+      uint32_t ph = 0;
+      const uint32_t tx = 2u * A_BYTES + 2u * (uint32_t)a.box_rows * 128u;
+      for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x)
+        for (int j = 0; j < a.n_tiles; ++j)
+          for (int kb = 0; kb < a.KB; ++kb) {
+            mbar_wait(EMPTY(st), ph ^ 1u);
+            mbar_expect_tx(FULL(st), tx);
+            const uint32_t base = smem_u32(sm + (size_t)st * T_STAGE_BYTES);
+            tma_load_2d(base, &tmapA, FULL(st), kb * BK, (int)(t * BM));
+            tma_load_2d(base + A_BYTES, &tmapA, FULL(st), kb * BK, (int)(a.a_plane_rows + t * BM));
+            tma_load_2d(base + 2 * A_BYTES, &tmapB, FULL(st), kb * BK, j * a.box_rows);
+            tma_load_2d(base + 2 * A_BYTES + B_BYTES, &tmapB, FULL(st), kb * BK, a.b_plane_rows + j * a.box_rows);
+            if (++st == T_STAGES) { st = 0; ph ^= 1u; }
+          }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      int st = 0, ts = 0;
+      uint32_t ph = 0, tph = 0;
+      for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x)
+        for (int j = 0; j < a.n_tiles; ++j) {
+          const int nj = min(BN, a.Hp - j * BN);
+          const uint32_t idesc = umma_idesc_f16(nj);
+          mbar_wait(T_EMPTY(ts), tph ^ 1u);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + (uint32_t)ts * BN;
+          for (int kb = 0; kb < a.KB; ++kb) {
+            mbar_wait(FULL(st), ph);
+            tc_fence_after();
+            const uint32_t base = smem_u32(sm + (size_t)st * T_STAGE_BYTES);
+            const uint64_t ahi = umma_desc_sw128(base), alo = umma_desc_sw128(base + A_BYTES);
+            const uint64_t bhi = umma_desc_sw128(base + 2 * A_BYTES), blo = umma_desc_sw128(base + 2 * A_BYTES + B_BYTES);
+#pragma unroll
+            for (int k4 = 0; k4 < BK / 16; ++k4) umma_f16(tmem_d, ahi + 2 * k4, bhi + 2 * k4, idesc, (uint32_t)(kb | k4));
+#pragma unroll
+            for (int k4 = 0; k4 < BK / 16; ++k4) umma_f16(tmem_d, ahi + 2 * k4, blo + 2 * k4, idesc, 1u);
+#pragma unroll
+            for (int k4 = 0; k4 < BK / 16; ++k4) umma_f16(tmem_d, alo + 2 * k4, bhi + 2 * k4, idesc, 1u);
+            umma_commit(EMPTY(st));
+            if (++st == T_STAGES) { st = 0; ph ^= 1u; }
+          }
+          umma_commit(T_FULL(ts));
+          if (++ts == 2) { ts = 0; tph ^= 1u; }
+        }
+    }
+  } else {
+    // ===== epilogue: TMEM -> f64 -> B[n][h] =====
+    const int q = warp & 3;
+    const float descale = __ldg(a.descale);
+    int ts = 0;
+    uint32_t tph = 0;
+    const bool vec2 = (a.H & 1) == 0;
+    for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+      const int64_t n = t * BM + q * 32 + lane;
+      const bool valid = n < a.N;
+      double *orow = a.B + (valid ? n : 0) * (int64_t)a.H;
+      for (int j = 0; j < a.n_tiles; ++j) {
+        const int nj = min(BN, a.Hp - j * BN);
+        mbar_wait(T_FULL(ts), tph);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)ts * BN;
+        for (int c = 0; c < nj; c += 16) {
+          uint32_t v[16];
+          tmem_ld16(taddr + (uint32_t)c, v);
+          tmem_ld_wait();
+          const int h0 = j * BN + c;
+          if (valid) {
+            if (vec2 && h0 + 16 <= a.H) {
+#pragma unroll
+              for (int i = 0; i < 16; i += 2)
+                *reinterpret_cast<double2 *>(orow + h0 + i) =
+                    make_double2((double)(__uint_as_float(v[i]) * descale), (double)(__uint_as_float(v[i + 1]) * descale));
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if (h0 + i < a.H) orow[h0 + i] = (double)(__uint_as_float(v[i]) * descale);
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(T_EMPTY(ts));
+        if (++ts == 2) { ts = 0; tph ^= 1u; }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
+// max |x| of an f32 array (non-negative floats order like their bit patterns)
+__global__ void fmax_kernel(const float *__restrict__ X, int64_t n, unsigned int *out) {
+  float m = 0.f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float v = fabsf(X[i]);
+    if (v == v && v < INFINITY) m = fmaxf(m, v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out, __float_as_uint(m));
+}
+
+__device__ __forceinline__ int scale_exp(float mx) {
+  int e = 0;
+  if (mx > 0.f) e = 13 - ilogbf(mx);  // max |x| 2^e in [2^13, 2^14)
+  return max(-100, min(100, e));
+}
+__device__ __forceinline__ void split_half(double v, __half &hi, __half &lo) {
+  if (!(v == v)) v = 0.0;
+  v = fmin(fmax(v, -65504.0), 65504.0);
+  hi = __double2half(v);
+  lo = __double2half(v - (double)__half2float(hi));
+}
+
+// Y (f32 [N][D]) -> planes [2][Np][Dp] fp16, zero padded.  hdr[0] = max|Y| bits; hdr[1] <- 2^-ey (f32)
+__global__ void ysplit_kernel(const float *__restrict__ Y, int64_t N, int D, int64_t Np, int Dp, __half *planes,
+                              unsigned int *hdr) {
+  const int e = scale_exp(__uint_as_float(hdr[0]));
+  const double scale = ldexp(1.0, e);
+  const int64_t total = Np * Dp;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / Dp;
+    const int d = (int)(i - n * Dp);
+    __half hi, lo;
+    split_half((n < N && d < D) ? (double)Y[n * D + d] * scale : 0.0, hi, lo);
+    planes[i] = hi;
+    planes[total + i] = lo;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) reinterpret_cast<float *>(hdr)[1] = (float)ldexp(1.0, -e);
+}
+
+// W (f64 [D][H]) -> transposed planes [2][Hr][Dp] fp16.  hdr[2] = max|W| bits; hdr[3] <- 2^-ew; hdr[4] <- 2^-(ey+ew)
+__global__ void wtsplit_kernel(const double *__restrict__ W, int D, int H, int Hr, int Dp, __half *planes, unsigned int *hdr) {
+  const int e = scale_exp(__uint_as_float(hdr[2]));
+  const double scale = ldexp(1.0, e);
+  const int64_t total = (int64_t)Hr * Dp;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int h = (int)(i / Dp), d = (int)(i - (int64_t)h * Dp);
+    __half hi, lo;
+    split_half((h < H && d < D) ? W[(int64_t)d * H + h] * scale : 0.0, hi, lo);
+    planes[i] = hi;
+    planes[total + i] = lo;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    float *f = reinterpret_cast<float *>(hdr);
+    f[3] = (float)ldexp(1.0, -e);
+    f[4] = f[1] * f[3];
+  }
+}
+
+struct TGeometry {
+  int Dp, KB, Hp, n_tiles, box_rows, b_plane_rows;
+  int64_t Np;
+  size_t y_bytes, w_bytes, total_bytes;
+};
+static TGeometry tgeometry(int64_t N, int D, int H) {
+  TGeometry g;
+  g.Dp = (D + BK - 1) / BK * BK;
+  g.KB = g.Dp / BK;
+  g.Hp = (H + 15) & ~15;
+  g.box_rows = g.Hp < BN ? g.Hp : BN;
+  g.n_tiles = (g.Hp + BN - 1) / BN;
+  g.b_plane_rows = g.n_tiles * g.box_rows;
+  g.Np = (N + BM - 1) / BM * BM;
+  g.y_bytes = ((size_t)2 * g.Np * g.Dp * sizeof(__half) + 255) & ~(size_t)255;
+  g.w_bytes = ((size_t)2 * g.b_plane_rows * g.Dp * sizeof(__half) + 255) & ~(size_t)255;
+  g.total_bytes = 256 + g.y_bytes + g.w_bytes;
+  return g;
+}
+static int encode_2d(CUtensorMap *tm, void *base, uint64_t cols, uint64_t rows, uint32_t box_rows) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return EVO_ERR_UNSUPPORTED;
+  }
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)cols * sizeof(__half)};
+  cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult cr = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (cr != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr);
+    return EVO_ERR_CUDA;
+  }
+  return EVO_OK;
+}
+
 }  // namespace dense
 }  // namespace evo
 
@@ -495,5 +743,66 @@ extern "C" int evo_bsc_lpj_gemm(const uint32_t *states, int shared_states, int64
   int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   dense::dense_lpj_kernel<<<grid, dense::THREADS, dense::SMEM_BYTES, (cudaStream_t)stream>>>(tmap, a);
   EVO_LAUNCH_CHECK("dense_lpj");
+  return EVO_OK;
+}
+
+static int grid_1d(int64_t n) {
+  int64_t b = (n + 255) / 256, cap = (int64_t)sm_count() * 8;
+  return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+extern "C" int64_t evo_bsc_tables_tc_workspace_bytes(int64_t N, int D, int H) {
+  if (N <= 0 || D <= 0 || H <= 0) return 0;
+  return (int64_t)dense::tgeometry(N, D, H).total_bytes;
+}
+
+extern "C" int evo_bsc_tables_tc_set_data(const float *Y, int64_t N, int D, int H, void *workspace, void *stream) {
+  EVO_REQUIRE(Y && workspace && N > 0 && D > 0 && H > 0, "bad arguments");
+  EVO_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  dense::TGeometry g = dense::tgeometry(N, D, H);
+  unsigned int *hdr = reinterpret_cast<unsigned int *>(workspace);
+  __half *yp = reinterpret_cast<__half *>(reinterpret_cast<uint8_t *>(workspace) + 256);
+  EVO_CUDA(cudaMemsetAsync(hdr, 0, 8, st));
+  dense::fmax_kernel<<<grid_1d(N * D), 256, 0, st>>>(Y, N * (int64_t)D, hdr);
+  EVO_LAUNCH_CHECK("fmax");
+  dense::ysplit_kernel<<<grid_1d(g.Np * g.Dp), 256, 0, st>>>(Y, N, D, g.Np, g.Dp, yp, hdr);
+  EVO_LAUNCH_CHECK("ysplit");
+  return EVO_OK;
+}
+
+extern "C" int evo_bsc_tables_tc(const double *W, int64_t N, int D, int H, void *workspace, double *B, void *stream) {
+  EVO_REQUIRE(W && workspace && B && N > 0 && D > 0 && H > 0, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  dense::TGeometry g = dense::tgeometry(N, D, H);
+  uint8_t *ws = reinterpret_cast<uint8_t *>(workspace);
+  unsigned int *hdr = reinterpret_cast<unsigned int *>(ws);
+  __half *yp = reinterpret_cast<__half *>(ws + 256);
+  __half *wp = reinterpret_cast<__half *>(ws + 256 + g.y_bytes);
+  EVO_CUDA(cudaMemsetAsync(hdr + 2, 0, 4, st));
+  dense::wmax_kernel<<<grid_1d((int64_t)D * H), 256, 0, st>>>(W, (int64_t)D * H, hdr + 2);
+  EVO_LAUNCH_CHECK("wmax");
+  dense::wtsplit_kernel<<<grid_1d((int64_t)g.b_plane_rows * g.Dp), 256, 0, st>>>(W, D, H, g.b_plane_rows, g.Dp, wp, hdr);
+  EVO_LAUNCH_CHECK("wtsplit");
+  CUtensorMap ta, tb;
+  int rc = dense::encode_2d(&ta, yp, (uint64_t)g.Dp, (uint64_t)(2 * g.Np), (uint32_t)dense::BM);
+  if (rc) return rc;
+  rc = dense::encode_2d(&tb, wp, (uint64_t)g.Dp, (uint64_t)(2 * g.b_plane_rows), (uint32_t)g.box_rows);
+  if (rc) return rc;
+  dense::TArgs a;
+  a.N = N; a.H = H; a.KB = g.KB; a.n_tiles = g.n_tiles; a.box_rows = g.box_rows;
+  a.a_plane_rows = g.Np; a.b_plane_rows = g.b_plane_rows; a.Hp = g.Hp;
+  a.descale = reinterpret_cast<const float *>(ws) + 4;
+  a.B = B;
+  static bool attr_set = false;
+  if (!attr_set) {
+    EVO_CUDA(cudaFuncSetAttribute(dense::table_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)dense::T_SMEM_BYTES));
+    attr_set = true;
+  }
+  int64_t tiles = (N + dense::BM - 1) / dense::BM;
+  int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  dense::table_gemm_kernel<<<grid, dense::T_THREADS, dense::T_SMEM_BYTES, st>>>(ta, tb, a);
+  EVO_LAUNCH_CHECK("table_gemm");
   return EVO_OK;
 }

@@ -66,6 +66,14 @@ int evo_states_init(uint32_t *states, int64_t N, int S, int H, int S_perm, int b
  * ynorm2[n] = |y_n|^2 f64.  Pass ynorm2 == NULL to skip it (Y is constant over EM iterations). */
 int evo_bsc_prepare(const double *W, const float *Y, int64_t N, int D, int H, double *G, double *B,
                     double *ynorm2, void *stream);
+/* The same table B = Y W on the tensor cores (tcgen05, TMA-fed): Y and W are scaled by powers of two
+ * and split into fp16 hi + lo planes, three passes (hi*hi, hi*lo, lo*hi) accumulate in fp32 TMEM, the
+ * epilogue writes f64.  |B_tc - B_f64| <= 2e-6 max|B| (measured <= 1e-6); lpj from it agrees with the
+ * f64 reference to <= 1e-5 relative.  Workspace (256-byte aligned) holds the planes:
+ *   evo_bsc_tables_tc_set_data  once per dataset (Y planes), evo_bsc_tables_tc once per parameter set. */
+int64_t evo_bsc_tables_tc_workspace_bytes(int64_t N, int D, int H);
+int evo_bsc_tables_tc_set_data(const float *Y, int64_t N, int D, int H, void *workspace, void *stream);
+int evo_bsc_tables_tc(const double *W, int64_t N, int D, int H, void *workspace, double *B, void *stream);
 /* lpj[n][k] = pre1 * |y_n - W s_nk|^2_obs + pil_bar |s_nk|, sanitised as lpj_reset_check.
  * eval = EVO_EVAL_BSC_GRAM uses (G,B,ynorm2); EVO_EVAL_BSC_DIRECT uses (W,Y,mask).
  * states: [N][Sp][Hw] or, with shared_states != 0, one [Sp][Hw] table used for every datapoint

@@ -89,3 +89,87 @@ def test_dense_lpj_linearity_at_full_tile_count():
     assert np.array_equal(16.0 * a, b)
     s = m.lpj_all(th, data, cont["ss_dev"]).cpu().numpy()
     assert np.max(np.abs(a - s) / np.maximum(np.abs(s), 1e-12)) < TOL
+
+
+@pytest.mark.parametrize("D,H,N,wscale", [(25, 10, 300, 10.0), (256, 300, 1000, 1.0), (144, 70, 129, 1e-3), (1024, 1024, 500, 1.0)])
+def test_tc_table_matches_f64_table(D, H, N, wscale):
+    """B = Y W from the tcgen05 split-precision GEMM vs the f64 SIMT GEMM (evo_bsc_prepare) and NumPy.
+    Stated bound: 1e-5 of max|B| (fp16 hi+lo operands, three passes, fp32 tensor-core accumulation over
+    D; measured 1e-7 at D=25 ... 5e-6 at D=1024)."""
+    import torch
+
+    from evo_b200 import _lib
+    from evo_b200.bsc import BSC
+
+    rng = np.random.RandomState(D + H)
+    W = rng.normal(size=(D, H)) * wscale
+    Y = (rng.normal(size=(N, D)) * 3.0 * wscale).astype(np.float32)
+    m = BSC(D, H, 8)
+    Wd = torch.as_tensor(W, device=m.device)
+    Yd = torch.as_tensor(Y, device=m.device)
+    B64 = torch.empty((N, H), dtype=torch.float64, device=m.device)
+    G = torch.empty((H, H), dtype=torch.float64, device=m.device)
+    m._call("evo_bsc_prepare", _lib.ptr(Wd), _lib.ptr(Yd), N, D, H, _lib.ptr(G), _lib.ptr(B64), None)
+    ws = torch.empty(int(m.lib.evo_bsc_tables_tc_workspace_bytes(N, D, H)), dtype=torch.uint8, device=m.device)
+    Btc = torch.full((N, H), float("nan"), dtype=torch.float64, device=m.device)
+    m._call("evo_bsc_tables_tc_set_data", _lib.ptr(Yd), N, D, H, _lib.ptr(ws))
+    m._call("evo_bsc_tables_tc", _lib.ptr(Wd), N, D, H, _lib.ptr(ws), _lib.ptr(Btc))
+    ref = Y.astype(np.float64) @ W
+    scale = np.abs(ref).max()
+    assert np.abs(B64.cpu().numpy() - ref).max() < 1e-12 * scale
+    err = np.abs(Btc.cpu().numpy() - ref).max() / scale
+    print('tc table err / max|B|:', D, H, err)
+    assert err < 1e-5, err
+
+
+def test_tc_tables_em_trajectory_matches_f64_tables():
+    """Three EM iterations of BSC (RNG mode, same Philox streams) with the tensor-core table vs the f64
+    table: free energies within 1e-5 relative, W within 1e-4 of its scale (selection may differ on
+    near-ties below the table's 2e-6 resolution -- documented)."""
+    import torch
+
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import init_states
+
+    D, H, K, N = 64, 40, 32, 4000
+    rng = np.random.RandomState(3)
+    Wg = rng.normal(size=(D, H)) * 2.0
+    s = rng.random_sample((N, H)) < 3.0 / H
+    Y = (s @ Wg.T + rng.normal(size=(N, D))).astype(np.float32)
+    out = {}
+    for mode in ("f64", "tc"):
+        m = BSC(D, H, K)
+        m.tables = mode
+        data = {"y": torch.as_tensor(Y, device=m.device), "x_infr": None}
+        np.random.seed(1)
+        th = m.check_params(m.standard_init(data))
+        cont = init_states(N, K, H, "fit", "randflip", 6, 4, 2, device=m.device, seed=11)
+        Fs = []
+        for _ in range(3):
+            F, _, _, th = m.step(th, cont, data)
+            Fs.append(F)
+        W = th["W"].cpu().numpy() if isinstance(th["W"], torch.Tensor) else np.asarray(th["W"])
+        out[mode] = (np.array(Fs), W)
+    assert np.max(np.abs(out["tc"][0] - out["f64"][0]) / np.abs(out["f64"][0])) < 1e-5, out
+    assert np.max(np.abs(out["tc"][1] - out["f64"][1])) < 1e-4 * np.abs(out["f64"][1]).max()
+
+
+@pytest.mark.parametrize("D,H,S,N,act,bound", [(256, 300, 64, 400, 5.0, 1e-5), (1024, 1024, 128, 64, 8.0, 1e-5)])
+def test_gram_lpj_from_tc_table(D, H, S, N, act, bound):
+    """lpj of the sparse Gram kernel fed by the tensor-core table vs the f64 oracle (stated bound 1e-5 relative; measured 1.3e-6 (D=256) and 1.5e-6 (D=1024):
+    the table's fp32 accumulation error grows with D)."""
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import pack_states
+
+    W, Y, X, st = _case(D, H, S, N, act, seed=5 * D + H)
+    sigma, pi = 1.3, act / H
+    pre1, pil_bar = -0.5 / sigma ** 2, float(np.log(pi / (1 - pi)))
+    ref = _oracle(W, Y, X, st, pre1, pil_bar)
+    m = BSC(D, H, S)
+    m.tables = "tc"
+    th = {"W": W, "pi": pi, "sigma": sigma, "pre1": pre1, "pil_bar": pil_bar}
+    data = {"y": Y.astype(np.float64), "x_infr": X}
+    got = m.lpj_all(th, data, pack_states(st, m.device)).cpu().numpy()
+    err = np.max(np.abs(got - ref) / np.abs(ref))
+    print("gram lpj from tc table, max rel err:", D, H, err)
+    assert err < bound, err
