@@ -156,6 +156,7 @@ def algorithmic_bytes(w, N, U_mean):
         "evo_estep": N * (4 * D + ((D + 7) // 8 if w.get("missing") else 0) + (K + U_mean) * (4 * Hw + 4)),
         # tables of the Gram form: read Y, write B = Y W (f64)
         "evo_bsc_prepare": N * (4 * D + 8 * H),
+        "evo_bsc_tables_tc": N * (4 * D + 8 * H),
         # (d): read K^n + lpj + y_n, one pass over the outputs
         "evo_bsc_suffstats": N * (K * (4 * Hw + 4) + 4 * D) + 8 * (H * D + H * H),
         # ES3C (d): as above + mask bits + y_rec write, one pass over the four H x H + H x D outputs
@@ -226,6 +227,13 @@ def run_lpj_compare(args):
         "faster": "sparse" if s_ms + sp_ms < d_ms + dp_ms else "dense",
     }
     print(json.dumps(line), flush=True)
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` captures of exactly the
+# default command (profiles/r01e_cfg2_full_ncu_summary.txt); None where no capture at that size exists.
+NCU_TRAFFIC = {("cfg2", 100000): {"evo_estep": 498.436352e6 + 96.002304e6,
+                                  "evo_bsc_suffstats": 316.745216e6 + 52.972288e6 + 171.225088e6 + 7.877376e6,
+                                  "evo_bsc_tables_tc": 104.104704e6 + 186.958336e6}}
 
 
 def measured_peaks():
@@ -378,7 +386,7 @@ def run_ours(args):
     if dom in alg:
         ach = alg[dom] / (kern[dom][1] * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "launch_ms": kern[dom][1],
+                "traffic": NCU_TRAFFIC.get((args.workload, N), {}).get(dom), "peak_source": peak_src, "launch_ms": kern[dom][1],
                 "algorithmic_bytes_per_launch": alg[dom]}
     line = {
         "metric": METRIC, "value": lpj_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -388,6 +396,8 @@ def run_ours(args):
                    "ea": "%s/%s parents=%d children=%d generations=%d" % tuple(w["ea"]),
                    "l2": "inputs larger than L2 (K sets + tables > 126 MB)" if N * w["K"] * 4 * ((w["H"] + 31) // 32) > 126e6
                    else "working set fits L2 (small reference config)",
+                   "tables": ("B = Y W by tcgen05 fp16 hi+lo split GEMM (lpj within 1e-5 of f64)" if args.tables == "tc"
+                              else "f64 SIMT GEMM") if w["model"] == "bsc" else "f64",
                    "parallelism": "dp%d over N" % world},
         "em_iters_per_sec": args.steps / (ms * 1e-3),
         "lpj_per_step": lpj_total / args.steps, "new_unique_per_datapoint": U_mean, "free_energy": F,
