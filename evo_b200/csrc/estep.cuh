@@ -199,14 +199,17 @@ __device__ inline void sparseflip_state(uint32_t *st, int Hm, double sparseness,
 }
 
 // ------------------------------------------------------------------------------------------
-template <class Eval, int T>
+// FAST = the RNG hot path only (randflip mutation, no injected candidates, no background unit): the
+// other operators are compiled out, which shrinks the kernel's instruction footprint.
+template <class Eval, int T, bool FAST = false>
 __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   EstepSmem s;
   estep_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
   const int Hw = a.Hw, Hs = a.Hs, S = a.S;
-  const int Hm = a.background ? a.H - 1 : a.H;
+  const bool bgu = FAST ? false : (a.background != 0);
+  const int Hm = bgu ? a.H - 1 : a.H;
   double acc_F = 0.0, acc_U = 0.0, acc_sub = 0.0, acc_eval = 0.0;
   unsigned long long cnt_nan = 0, cnt_small = 0, cnt_inf = 0;
 
@@ -245,7 +248,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
 
     for (int g = 0; g < a.n_generations; ++g) {
       int nc = 0;
-      if (a.inj_children) {
+      if (!FAST && a.inj_children) {
         // ---- injected candidates (parity runs) -------------------------------------------------
         nc = a.inj_count[n * (int64_t)a.n_generations + g];
         if (nc > a.Cg) nc = a.Cg;
@@ -283,11 +286,11 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           gsync<T>();
         }
         // ---- mutation (eas.py:10-135) -----------------------------------------------------------
-        const int mut = a.mutation;
-        if (mut == EVO_MUT_RANDFLIP || mut == EVO_MUT_SPARSEFLIP) {
+        const int mut = FAST ? (int)EVO_MUT_RANDFLIP : a.mutation;
+        if (FAST || mut == EVO_MUT_RANDFLIP || mut == EVO_MUT_SPARSEFLIP) {
           const int C = a.n_children;
           nc = take * C;
-          if (mut == EVO_MUT_RANDFLIP) {
+          if (FAST || mut == EVO_MUT_RANDFLIP) {
             // C distinct uniformly drawn positions per parent; child j flips position j
             for (int p = tid; p < take; p += T) {
               uint32_t di = (uint32_t)p * 64u * (uint32_t)(C + 1);
@@ -311,10 +314,10 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             const uint32_t *src = s.st_uniq + (size_t)s.parents[p] * Hs;
             uint32_t *dst = s.st_child + (size_t)c * Hs;
             for (int w = 0; w < Hw; ++w) dst[w] = src[w];
-            if (a.background) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
-            if (mut == EVO_MUT_RANDFLIP) flip_bit(dst, s.slot[c]);
+            if (bgu) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
+            if (FAST || mut == EVO_MUT_RANDFLIP) flip_bit(dst, s.slot[c]);
             else sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_MUTATE, g, (uint32_t)c);
-            if (a.background) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
+            if (bgu) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
           }
         } else {
           // one-point crossover of every unordered parent pair, two children per pair
@@ -338,14 +341,14 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             for (int k = 0; k < 2; ++k) {
               uint32_t *dst = k ? c1 : c0;
               uint32_t cidx = (uint32_t)(2 * q + k);
-              if (a.background) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
+              if (bgu) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
               if (mut == EVO_MUT_CROSS_RANDFLIP) {
                 uint4 r2 = rng.draw(RNG_FLIP2, g, cidx);
                 flip_bit(dst, (int)urange(r2.x, (uint32_t)Hm));
               } else if (mut == EVO_MUT_CROSS_SPARSEFLIP) {
                 sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_FLIP2, g, cidx);
               }
-              if (a.background) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
+              if (bgu) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
             }
           }
         }
@@ -500,6 +503,7 @@ template <class Eval>
 static int launch_estep_any(const EstepDev &dv, Eval ev, cudaStream_t st) {
   int work = dv.S > dv.Cg ? dv.S : dv.Cg;
   int T = ev.threads_hint(work);
+  const bool fast = !dv.inj_children && dv.mutation == EVO_MUT_RANDFLIP && !dv.background && !getenv("EVO_ESTEP_GENERIC");
   if (const char *e = getenv("EVO_ESTEP_T")) { int t = atoi(e); if (t > 0) T = t; }
   T = T <= 32 ? 32 : (T <= 64 ? 64 : (T <= 128 ? 128 : 256));
   size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes(T);
@@ -509,7 +513,7 @@ static int launch_estep_any(const EstepDev &dv, Eval ev, cudaStream_t st) {
   }
 #define EVO_LAUNCH_T(TT)                                                                              \
   {                                                                                                   \
-    auto k = estep_kernel<Eval, TT>;                                                                  \
+    auto k = fast ? estep_kernel<Eval, TT, true> : estep_kernel<Eval, TT, false>;                     \
     if (smem > 48 * 1024)                                                                             \
       EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
     int per_sm = 1;                                                                                   \
