@@ -23,6 +23,7 @@ int es3c_launch_estep(const EstepDev &dv, const evo_estep_args *x, cudaStream_t 
     EVO_REQUIRE(x->G && x->B && x->ynorm2, "es3c with complete data needs G, B, ynorm2");
     ev.masked = 0; ev.G = x->G; ev.B = x->B; ev.ynorm2 = x->ynorm2;
   }
+  ev.max_batch = dv.S > dv.Cg ? dv.S : dv.Cg;
   return launch_estep_any(dv, ev, st);
 }
 
@@ -275,6 +276,7 @@ extern "C" int evo_es3c_lpj(const uint32_t *states, int shared_states, int64_t N
     ev.masked = 0; ev.G = G; ev.B = B; ev.ynorm2 = ynorm2;
   }
   constexpr int T = 128;
+  ev.max_batch = Sp <= 16384 ? Sp : 0;
   size_t smem = ev.smem_bytes(T);
   auto k = lpj_kernel<Es3cEval, T>;
   if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

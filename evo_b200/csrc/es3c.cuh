@@ -29,21 +29,26 @@ struct Es3cEval {
   int D, H, Hw, masked;
   double *scratch;       // global per-warp workspaces for 16 < a <= 32 (or NULL)
   int scratch_warps;     // capacity of `scratch` in warps
+  int max_batch;         // largest cnt eval_batch will see (index lists of the small / large systems); 0 = no lists
   // per datapoint (setup)
   double *vec;           // smem: b [H] (complete) or y [D] (incomplete)
   uint8_t *m;            // smem [D] (incomplete)
   unsigned char *wsm;    // smem per-warp area base
+  unsigned char *lsm;    // smem: int counters[2] + uint16 small[max_batch] + uint16 big[max_batch]
   double yn2;
 
   static constexpr int AS = 16, LDS = 17;   // shared-memory path
   static constexpr int AG = 32, LDGL = 33;  // global-scratch path
-  static constexpr size_t WARP_SMEM = 64 + 3 * AS * LDS * sizeof(double);
+  static constexpr int G8 = 8, LD8 = 9;      // packed path: 4 states per warp, 8 lanes each (a <= 8)
+  static constexpr size_t G8_BYTES = 16 + 3 * G8 * LD8 * sizeof(double);
+  static constexpr size_t WARP_SMEM = 4 * G8_BYTES > 64 + 3 * AS * LDS * sizeof(double) ? 4 * G8_BYTES : 64 + 3 * AS * LDS * sizeof(double);
   static constexpr size_t WARP_SCRATCH = 3 * AG * LDGL;  // doubles
 
   __host__ __device__ size_t head_bytes() const {
     return masked ? align8((size_t)D * sizeof(double)) + align8((size_t)D) : align8((size_t)H * sizeof(double));
   }
-  __host__ __device__ size_t smem_bytes(int T) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM; }
+  __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(8 + (size_t)4 * max_batch) : 0; }
+  __host__ __device__ size_t smem_bytes(int T) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM + list_bytes(); }
   __host__ int threads_hint(int work) const { return work < 64 ? 64 : 256; }  // one warp per state: 8 states in flight
 
   template <int T>
@@ -62,6 +67,7 @@ struct Es3cEval {
       yn2 = __ldg(ynorm2 + n);
     }
     wsm = smem + head_bytes();
+    lsm = wsm + (size_t)(T / 32) * WARP_SMEM;
   }
 
   // |y_obs|^2 for incomplete data (needs the loaded y); call after the post-setup barrier
@@ -255,11 +261,179 @@ struct Es3cEval {
     return -0.5 * (logdet + quad) + prior;
   }
 
+  // ---- packed path: one state per 8 lanes (a <= 8), four states per warp -------------------------
+  // Same arithmetic as warp_lpj (gather -> N = I + s2i G_AA Psi_A -> LU with partial pivoting -> quad
+  // form), with every shuffle / redux / sync restricted to the group's 8-lane mask, so the four
+  // groups of a warp run their own trip counts.
+  __device__ __forceinline__ double g8_sum(unsigned gm, double v) const {
+    v += __shfl_xor_sync(gm, v, 4, 8);
+    v += __shfl_xor_sync(gm, v, 2, 8);
+    v += __shfl_xor_sync(gm, v, 1, 8);
+    return v;
+  }
+  __device__ __forceinline__ double group8_lpj(const uint32_t *st) const {
+    const int lane = threadIdx.x & 31, sl = lane & 7, gid = lane >> 3;
+    const unsigned gm = 0xFFu << (8 * gid);
+    unsigned char *base = wsm + (size_t)(threadIdx.x >> 5) * WARP_SMEM + (size_t)gid * G8_BYTES;
+    uint16_t *idx = reinterpret_cast<uint16_t *>(base);
+    double *A1 = reinterpret_cast<double *>(base + 16), *A2 = A1 + G8 * LD8, *A3 = A2 + G8 * LD8;
+    // active latents (the caller guarantees |s| <= 8)
+    int a = 0;
+    for (int w0 = 0; w0 < Hw; w0 += 8) {
+      uint32_t word = (w0 + sl < Hw) ? st[w0 + sl] : 0u;
+      const int c = __popc(word);
+      int pre = c;
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) { int t = __shfl_up_sync(gm, pre, o, 8); if (sl >= o) pre += t; }
+      int pos = a + pre - c;
+      while (word) {
+        int bp = __ffs(word) - 1;
+        word &= word - 1;
+        if (pos < G8) idx[pos] = (uint16_t)(((w0 + sl) << 5) + bp);
+        ++pos;
+      }
+      a += __shfl_sync(gm, pre, 7, 8);
+    }
+    __syncwarp(gm);
+    if (a == 0) return -0.5 * s2i * yn2;
+    const bool act = sl < a;
+    // gather G_AA -> A1, Psi_AA -> A2, b_i
+    double bi = 0.0;
+    if (!masked) {
+      if (act) {
+        const int h = idx[sl];
+        const double *Gr = G + (int64_t)h * H;
+        for (int l = 0; l < a; ++l) A1[sl * LD8 + l] = __ldg(Gr + idx[l]);
+        bi = vec[h];
+      }
+    } else {
+      for (int i = 0; i < a; ++i) {
+        const double *wi = Wt + (int64_t)idx[i] * D;
+        double pb = 0.0;
+        for (int d = sl; d < D; d += 8) pb += __ldg(wi + d) * vec[d];
+        pb = g8_sum(gm, pb);
+        if (sl == i) bi = pb;
+        for (int j = 0; j <= i; ++j) {
+          const double *wj = Wt + (int64_t)idx[j] * D;
+          double p = 0.0;
+          for (int d = sl; d < D; d += 8)
+            if (m[d]) p += __ldg(wi + d) * __ldg(wj + d);
+          p = g8_sum(gm, p);
+          if (sl == 0) { A1[i * LD8 + j] = p; A1[j * LD8 + i] = p; }
+        }
+      }
+    }
+    if (act) {
+      const double *Pr = Psi + (int64_t)idx[sl] * H;
+      for (int l = 0; l < a; ++l) A2[sl * LD8 + l] = __ldg(Pr + idx[l]);
+    }
+    __syncwarp(gm);
+    // v, |r|^2, w = Psi_A' v, N -> A3
+    const double mu = act ? __ldg(mus + idx[sl]) : 0.0;
+    double t = 0.0;
+    for (int l = 0; l < a; ++l) {
+      double ml = __shfl_sync(gm, mu, l, 8);
+      if (act) t += A1[sl * LD8 + l] * ml;
+    }
+    const double v = act ? s2i * (bi - t) : 0.0;
+    const double rn2 = yn2 + g8_sum(gm, act ? mu * (t - 2.0 * bi) : 0.0);
+    double w = 0.0;
+    for (int l = 0; l < a; ++l) {
+      double vl = __shfl_sync(gm, v, l, 8);
+      if (act) w += A2[l * LD8 + sl] * vl;
+    }
+    if (act) {
+      for (int j = 0; j < a; ++j) {
+        double acc = 0.0;
+        for (int l = 0; l < a; ++l) acc += A1[sl * LD8 + l] * A2[l * LD8 + j];
+        A3[sl * LD8 + j] = (sl == j ? 1.0 : 0.0) + s2i * acc;
+      }
+    }
+    __syncwarp(gm);
+    // LU with partial pivoting, rhs = v
+    double rhs = v, prod = 1.0, extra = 0.0;
+    int esum = 0;
+    for (int k = 0; k < a; ++k) {
+      unsigned key = 0u;
+      if (act && sl >= k) key = (__float_as_uint(fabsf((float)A3[sl * LD8 + k])) & ~7u) | (unsigned)(7 - sl);
+      const int p = 7 - (int)(__reduce_max_sync(gm, key) & 7u);
+      if (p != k) {
+        if (act) { double x = A3[k * LD8 + sl]; A3[k * LD8 + sl] = A3[p * LD8 + sl]; A3[p * LD8 + sl] = x; }
+        double rk = __shfl_sync(gm, rhs, k, 8), rp = __shfl_sync(gm, rhs, p, 8);
+        if (sl == k) rhs = rp;
+        if (sl == p) rhs = rk;
+      }
+      __syncwarp(gm);
+      const double piv = A3[k * LD8 + k];
+      {
+        const int ex = (__double2hiint(piv) >> 20) & 0x7ff;
+        if (ex == 0 || ex == 0x7ff) {
+          extra += log(fabs(piv));
+        } else {
+          prod *= __hiloint2double((__double2hiint(piv) & 0x800fffff) | 0x3ff00000, __double2loint(piv));
+          esum += ex - 1023;
+          const int e2 = (__double2hiint(prod) >> 20) & 0x7ff;
+          prod = __hiloint2double((__double2hiint(prod) & 0x800fffff) | 0x3ff00000, __double2loint(prod));
+          esum += e2 - 1023;
+        }
+      }
+      const double rhs_k = __shfl_sync(gm, rhs, k, 8);
+      if (act && sl > k) {
+        const double f = A3[sl * LD8 + k] / piv;
+        for (int c = k + 1; c < a; ++c) A3[sl * LD8 + c] -= f * A3[k * LD8 + c];
+        rhs -= f * rhs_k;
+      }
+      __syncwarp(gm);
+    }
+    for (int k = a - 1; k >= 0; --k) {
+      const double xk = __shfl_sync(gm, rhs, k, 8) / A3[k * LD8 + k];
+      if (sl == k) rhs = xk;
+      if (act && sl < k) rhs -= A3[sl * LD8 + k] * xk;
+    }
+    const double logdet = log(fabs(prod)) + (double)esum * 0.693147180559945309417232121458 + extra;
+    const double quad = s2i * rn2 - g8_sum(gm, act ? w * rhs : 0.0);
+    const double prior = g8_sum(gm, act ? __ldg(pil_bar + idx[sl]) : 0.0);
+    __syncwarp(gm);
+    return -0.5 * (logdet + quad) + prior;
+  }
+
   template <int T>
   __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) {
     if (masked) yn2 = masked_yn2();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = warp; i < cnt; i += T / 32) {
+    if (max_batch <= 0 || cnt > max_batch) {  // no index lists: one warp per state
+      for (int i = warp; i < cnt; i += T / 32) {
+        double v = warp_lpj(st + (size_t)i * ld);
+        v = lpj_sanitise(v, flags);
+        if (lane == 0) out[i] = v;
+      }
+      return;
+    }
+    // split the batch by |s|: systems with a <= 8 are packed four per warp
+    int *cn = reinterpret_cast<int *>(lsm);
+    uint16_t *small = reinterpret_cast<uint16_t *>(lsm + 8), *big = small + max_batch;
+    gsync<T>();
+    if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; }
+    gsync<T>();
+    for (int i = threadIdx.x; i < cnt; i += T) {
+      const int a = popc_state(st + (size_t)i * ld, Hw);
+      if (a <= G8) small[atomicAdd(&cn[0], 1)] = (uint16_t)i;
+      else big[atomicAdd(&cn[1], 1)] = (uint16_t)i;
+    }
+    gsync<T>();
+    const int ns = cn[0], nb = cn[1];
+    for (int q = warp; q * 4 < ns; q += T / 32) {
+      const int j = q * 4 + (lane >> 3);
+      if (j < ns) {  // whole 8-lane groups take or skip this branch together
+        const int i = small[j];
+        double v = group8_lpj(st + (size_t)i * ld);
+        v = lpj_sanitise(v, flags);
+        if ((lane & 7) == 0) out[i] = v;
+      }
+    }
+    __syncwarp();
+    for (int q = warp; q < nb; q += T / 32) {
+      const int i = big[q];
       double v = warp_lpj(st + (size_t)i * ld);
       v = lpj_sanitise(v, flags);
       if (lane == 0) out[i] = v;
