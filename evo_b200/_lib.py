@@ -35,6 +35,7 @@ class EstepArgs(C.Structure):
         ("pil_bar_h", C.c_void_p), ("mus", C.c_void_p), ("Psi", C.c_void_p),
         ("sigma2", C.c_double),
         ("acc", C.c_void_p),
+        ("overflow_list", C.c_void_p),
     ]
 
 

@@ -176,6 +176,9 @@ extern "C" int evo_estep(const evo_estep_args *x, void *stream) {
   dv.PK = dv.S > Cg ? dv.S : Cg;
   auto pow2mask = [](int n) { uint32_t m = 1; while ((int)m < n) m <<= 1; return m - 1u; };
   dv.Hs = dv.Hw | 1;
+  dv.Hr = dv.Hw;
+  dv.ovf_list = x->overflow_list;
+  dv.n_list = nullptr;
   dv.mask_c = pow2mask(dv.Ctot); dv.mask_s = pow2mask(dv.S); dv.mask_p = pow2mask(dv.PK);
   cudaStream_t st = (cudaStream_t)stream;
   if (x->eval == EVO_EVAL_BSC_GRAM) {

@@ -48,7 +48,8 @@ struct Es3cEval {
     return masked ? align8((size_t)D * sizeof(double)) + align8((size_t)D) : align8((size_t)H * sizeof(double));
   }
   __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(8 + (size_t)4 * max_batch) : 0; }
-  __host__ __device__ size_t smem_bytes(int T) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM + list_bytes(); }
+  static constexpr bool kList = false;
+  __host__ __device__ size_t smem_bytes(int T, bool = false) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM + list_bytes(); }
   __host__ int threads_hint(int work) const { return work < 64 ? 64 : 256; }  // one warp per state: 8 states in flight
 
   template <int T>
@@ -397,7 +398,7 @@ struct Es3cEval {
     return -0.5 * (logdet + quad) + prior;
   }
 
-  template <int T>
+  template <int T, bool LIST = false>
   __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) {
     if (masked) yn2 = masked_yn2();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -18,8 +18,11 @@ namespace evo {
 struct EstepDev {
   int64_t N, n_offset;
   int D, H, Hw, S, S_perm, Mprime;
-  int Hs;    // row stride (words) of the packed states in SHARED memory: Hw | 1, odd => one state per
-             // thread walks its words without bank conflicts (global rows stay Hw)
+  int Hs;    // row stride (words) of a state in SHARED memory, odd => one state per thread walks its
+             // words without bank conflicts (global rows stay Hw)
+  int Hr;    // words of one state row in shared memory: Hw (packed bits) or LIST_WORDS (index lists)
+  int32_t *ovf_list;      // LIST kernel: [0] = count, [1..] datapoints it could not represent (or NULL)
+  const int32_t *n_list;  // process only these datapoints ([0] = count, [1..]); NULL = all N
   int n_parents, n_children, n_generations, selection, mutation, background;
   double p_bf, sparseness;
   uint64_t seed;
@@ -91,6 +94,71 @@ __host__ __device__ inline size_t estep_carve(const EstepDev &a, unsigned char *
   return off;
 }
 
+// ---- sparse state rows (LIST representation) --------------------------------------------------
+// A state with at most LIST_CAP active latents is kept in shared memory as 16 uint16: the active
+// indices ascending in e[0..14] (0xFFFF padding) and the count in e[15] -- 32 bytes instead of
+// 4*Hw (132 at H = 1024).  Hashing, comparing and copying treat the row as LIST_WORDS opaque words;
+// only load, bit flip, evaluation and write-back know the layout.  A datapoint whose K^n or children
+// do not fit is handed, untouched, to the packed-bits kernel through `ovf_list`.
+constexpr int LIST_WORDS = 8, LIST_CAP = 15;
+
+// returns false on overflow (the row is then unspecified)
+__device__ __forceinline__ bool list_toggle(uint32_t *row, int pos) {
+  uint16_t *e = reinterpret_cast<uint16_t *>(row);
+  const int cnt = e[15];
+  int i = 0;
+  while (i < cnt && (int)e[i] < pos) ++i;
+  if (i < cnt && (int)e[i] == pos) {
+    for (int j = i; j < cnt - 1; ++j) e[j] = e[j + 1];
+    e[cnt - 1] = 0xFFFFu;
+    e[15] = (uint16_t)(cnt - 1);
+    return true;
+  }
+  if (cnt >= LIST_CAP) return false;
+  for (int j = cnt; j > i; --j) e[j] = e[j - 1];
+  e[i] = (uint16_t)pos;
+  e[15] = (uint16_t)(cnt + 1);
+  return true;
+}
+// packed bits (global, Hg words) -> list row, one WARP per state; returns false on overflow
+__device__ __forceinline__ bool list_from_bits(const uint32_t *src, int Hg, uint32_t *row) {
+  uint16_t *e = reinterpret_cast<uint16_t *>(row);
+  const int lane = threadIdx.x & 31;
+  if (lane < 16) e[lane] = 0xFFFFu;
+  __syncwarp();
+  int base = 0;
+  for (int w0 = 0; w0 < Hg; w0 += 32) {
+    uint32_t word = (w0 + lane < Hg) ? src[w0 + lane] : 0u;
+    const int c = __popc(word);
+    int pre = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += t; }
+    int pos = base + pre - c;
+    while (word) {
+      int bp = __ffs(word) - 1;
+      word &= word - 1;
+      if (pos < LIST_CAP) e[pos] = (uint16_t)(((w0 + lane) << 5) + bp);
+      ++pos;
+    }
+    base += __shfl_sync(0xffffffffu, pre, 31);
+  }
+  __syncwarp();
+  if (lane == 0) e[15] = (uint16_t)(base <= LIST_CAP ? base : LIST_CAP);
+  __syncwarp();
+  return base <= LIST_CAP;
+}
+// list row -> packed bits (Hg words), one thread
+__device__ __forceinline__ void list_to_bits(const uint32_t *row, int Hg, uint32_t *dst) {
+  const uint16_t *e = reinterpret_cast<const uint16_t *>(row);
+  const int cnt = e[15];
+  int p = 0;
+  for (int w = 0; w < Hg; ++w) {
+    uint32_t x = 0u;
+    while (p < cnt && (e[p] >> 5) == w) { x |= 1u << (e[p] & 31); ++p; }
+    dst[w] = x;
+  }
+}
+
 // ---- hash table over packed states --------------------------------------------------------
 __device__ __forceinline__ const uint32_t *tag_state(const EstepDev &a, const EstepSmem &s, int tag) {
   return tag >= TAG_CHILD ? s.st_child + (size_t)(tag - TAG_CHILD) * a.Hs : s.st_uniq + (size_t)tag * a.Hs;
@@ -98,11 +166,11 @@ __device__ __forceinline__ const uint32_t *tag_state(const EstepDev &a, const Es
 // read-only probe: index of the uniq entry equal to st, or -1
 __device__ __forceinline__ int table_find(const EstepDev &a, const EstepSmem &s, const uint32_t *st) {
   uint32_t mask = (uint32_t)a.HT - 1u;
-  uint32_t p = (uint32_t)hash_state(st, a.Hw) & mask;
+  uint32_t p = (uint32_t)hash_state(st, a.Hr) & mask;
   for (int it = 0; it < a.HT; ++it) {
     int tag = s.table[p];
     if (tag == TAG_EMPTY) return -1;
-    if (same_state(tag_state(a, s, tag), st, a.Hw)) return tag;
+    if (same_state(tag_state(a, s, tag), st, a.Hr)) return tag;
     p = (p + 1) & mask;
   }
   return -1;
@@ -110,14 +178,14 @@ __device__ __forceinline__ int table_find(const EstepDev &a, const EstepSmem &s,
 // concurrent insert; equal states converge on one slot holding the smallest tag.  Returns the slot.
 __device__ __forceinline__ int table_insert(const EstepDev &a, const EstepSmem &s, const uint32_t *st, int tag) {
   uint32_t mask = (uint32_t)a.HT - 1u;
-  uint32_t p = (uint32_t)hash_state(st, a.Hw) & mask;
+  uint32_t p = (uint32_t)hash_state(st, a.Hr) & mask;
   for (int it = 0; it < a.HT; ++it) {
     int cur = s.table[p];
     if (cur == TAG_EMPTY) {
       cur = atomicCAS(&s.table[p], TAG_EMPTY, tag);
       if (cur == TAG_EMPTY) return (int)p;
     }
-    if (same_state(tag_state(a, s, cur), st, a.Hw)) {
+    if (same_state(tag_state(a, s, cur), st, a.Hr)) {
       atomicMin(&s.table[p], tag);
       return (int)p;
     }
@@ -201,30 +269,44 @@ __device__ inline void sparseflip_state(uint32_t *st, int Hm, double sparseness,
 // ------------------------------------------------------------------------------------------
 // FAST = the RNG hot path only (randflip mutation, no injected candidates, no background unit): the
 // other operators are compiled out, which shrinks the kernel's instruction footprint.
-template <class Eval, int T, bool FAST = false>
+// LIST = states live in shared memory as index lists (see above); requires FAST and an evaluator with eval_batch<T, true>.
+template <class Eval, int T, bool FAST = false, bool LIST = false>
 __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   EstepSmem s;
   estep_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
-  const int Hw = a.Hw, Hs = a.Hs, S = a.S;
+  const int Hw = a.Hr, Hg = a.Hw, Hs = a.Hs, S = a.S;  // Hw: words of a shared-memory row, Hg: of a global row
   const bool bgu = FAST ? false : (a.background != 0);
   const int Hm = bgu ? a.H - 1 : a.H;
   double acc_F = 0.0, acc_U = 0.0, acc_sub = 0.0, acc_eval = 0.0;
   unsigned long long cnt_nan = 0, cnt_small = 0, cnt_inf = 0;
 
-  for (int64_t n = blockIdx.x; n < a.N; n += gridDim.x) {
+  const int64_t n_total = a.n_list ? (int64_t)a.n_list[0] : a.N;
+  for (int64_t it = blockIdx.x; it < n_total; it += gridDim.x) {
+    const int64_t n = a.n_list ? (int64_t)a.n_list[1 + it] : it;
     RngCtx rng(a.seed, a.n_offset + n, a.iteration);
     gsync<T>();  // previous datapoint fully done with shared memory
     // ---- load K^n, evaluator tables ---------------------------------------------------------
     {
-      const uint32_t *src = a.states + n * (int64_t)S * Hw;
-      for (int i = tid; i < S * Hw; i += T) s.st_uniq[(i / Hw) * Hs + (i % Hw)] = src[i];
+      const uint32_t *src = a.states + n * (int64_t)S * Hg;
+      if (LIST) {
+        if (tid == 0) s.sh[0] = 0;
+        gsync<T>();
+        for (int i = tid >> 5; i < S; i += T / 32)
+          if (!list_from_bits(src + (size_t)i * Hg, Hg, s.st_uniq + (size_t)i * Hs) && (tid & 31) == 0) s.sh[0] = 1;
+      } else {
+        for (int i = tid; i < S * Hw; i += T) s.st_uniq[(i / Hw) * Hs + (i % Hw)] = src[i];
+      }
       for (int i = tid; i < a.HT; i += T) s.table[i] = TAG_EMPTY;
       for (int i = tid; i < S + a.Ctot; i += T) s.redisc[i] = 0;
       ev.template setup<T>(n, s.eval_smem);
     }
     gsync<T>();
+    if (LIST && s.sh[0]) {  // a state of K^n has more than LIST_CAP active latents: not for this kernel
+      if (tid == 0) a.ovf_list[1 + atomicAdd(a.ovf_list, 1)] = (int32_t)n;
+      continue;
+    }
     // ---- lpj of the permanent state and of K^n ------------------------------------------------
     double lpj_perm = 0.0;
     {
@@ -234,7 +316,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         lpj_perm = ev.eval_zero(f0);
         if (tid == 0 && f0) { if (f0 & 1) ++cnt_nan; else if (f0 & 2) ++cnt_small; else ++cnt_inf; }
       }
-      ev.template eval_batch<T>(s.st_uniq, Hs, S, s.lpj_uniq, fl);
+      ev.template eval_batch<T, LIST>(s.st_uniq, Hs, S, s.lpj_uniq, fl);
       fl = group_or<T>(fl, s.red_i);
       if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
       for (int i = tid; i < S; i += T) table_insert(a, s, s.st_uniq + (size_t)i * Hs, i);
@@ -252,7 +334,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         // ---- injected candidates (parity runs) -------------------------------------------------
         nc = a.inj_count[n * (int64_t)a.n_generations + g];
         if (nc > a.Cg) nc = a.Cg;
-        const uint32_t *src = a.inj_children + ((n * (int64_t)a.n_generations + g) * a.inj_cmax) * (int64_t)Hw;
+        const uint32_t *src = a.inj_children + ((n * (int64_t)a.n_generations + g) * a.inj_cmax) * (int64_t)Hg;
         for (int i = tid; i < nc * Hw; i += T) s.st_child[(i / Hw) * Hs + (i % Hw)] = src[i];
       } else {
         // ---- parent selection (eas.py:138-150) -------------------------------------------------
@@ -315,7 +397,8 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             uint32_t *dst = s.st_child + (size_t)c * Hs;
             for (int w = 0; w < Hw; ++w) dst[w] = src[w];
             if (bgu) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
-            if (FAST || mut == EVO_MUT_RANDFLIP) flip_bit(dst, s.slot[c]);
+            if (LIST) { if (!list_toggle(dst, s.slot[c])) s.sh[0] = 1; }
+            else if (FAST || mut == EVO_MUT_RANDFLIP) flip_bit(dst, s.slot[c]);
             else sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_MUTATE, g, (uint32_t)c);
             if (bgu) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
           }
@@ -354,12 +437,13 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         }
       }
       gsync<T>();
+      if (LIST && s.sh[0]) break;  // a child does not fit the list form: the packed-bits kernel redoes this datapoint
 
       // ---- de-duplicate against (permanent, K^n, earlier new) and among the children ----------
       for (int c = tid; c < nc; c += T) {
         const uint32_t *st = s.st_child + (size_t)c * Hs;
         unsigned char stt = 1;  // candidate
-        if (a.S_perm > 0 && popc_state(st, Hw) == 0) stt = 0;
+        if (a.S_perm > 0 && (LIST ? reinterpret_cast<const uint16_t *>(st)[15] == 0 : popc_state(st, Hw) == 0)) stt = 0;
         else {
           int hit = table_find(a, s, st);
           if (hit >= 0) { s.redisc[hit] = 1; stt = 0; }
@@ -395,7 +479,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       {
         unsigned fl = 0;
         if (u_g > 0) {
-          ev.template eval_batch<T>(s.st_uniq + (size_t)(S + U) * Hs, Hs, u_g, s.lpj_uniq + S + U, fl);
+          ev.template eval_batch<T, LIST>(s.st_uniq + (size_t)(S + U) * Hs, Hs, u_g, s.lpj_uniq + S + U, fl);
           fl = group_or<T>(fl, s.red_i);
           if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
         }
@@ -421,6 +505,10 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       U += u_g;
       pool_n = pn;
       if (pool_n == 0) break;  // "No new and unique states" (eas.py:306-308)
+    }
+    if (LIST && s.sh[0]) {  // nothing of this datapoint has been written yet
+      if (tid == 0) a.ovf_list[1 + atomicAdd(a.ovf_list, 1)] = (int32_t)n;
+      continue;
     }
 
     // ---- vary_Kn: j-th best new replaces j-th worst old while it is better ----------------------
@@ -455,8 +543,13 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           if (!(v > s.lpj_uniq[k])) continue;
           const uint32_t *src = s.st_uniq + (size_t)(S + i) * Hs;
           uint32_t *dst = s.st_uniq + (size_t)k * Hs;
-          uint32_t *gdst = a.states + (n * (int64_t)S + k) * Hw;
-          for (int w = 0; w < Hw; ++w) { uint32_t x = src[w]; dst[w] = x; gdst[w] = x; }
+          uint32_t *gdst = a.states + (n * (int64_t)S + k) * Hg;
+          if (LIST) {
+            for (int w = 0; w < Hw; ++w) dst[w] = src[w];
+            list_to_bits(src, Hg, gdst);
+          } else {
+            for (int w = 0; w < Hw; ++w) { uint32_t x = src[w]; dst[w] = x; gdst[w] = x; }
+          }
           s.rnk[i] = -1 - k;  // remembered; lpj written after the barrier (other threads still compare against it)
           ++acc_local;
         }
@@ -499,40 +592,64 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
 // ---- launch: threads per datapoint group -------------------------------------------------------
 // T in {32, 64, 128, 256}: the evaluator's hint for the work per datapoint (max(S, children per
 // generation)); EVO_ESTEP_T overrides it (tuning runs).  Persistent grid = SMs x resident CTAs.
+// Kernel variants: generic (every operator, injected candidates), FAST (randflip RNG path), and for
+// evaluators that read index lists FAST+LIST followed by a FAST packed-bits launch over the datapoints
+// the list form could not hold (device-side list, normally empty).
+template <class Eval, int TT, bool FAST, bool LIST>
+static int launch_estep_variant(const EstepDev &dv, Eval ev, int64_t items, cudaStream_t st) {
+  size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes(TT, LIST);
+  if (smem > 227 * 1024) {
+    set_error("evo_estep: %zu bytes of shared memory per datapoint exceed 227 KB", smem);
+    return EVO_ERR_UNSUPPORTED;
+  }
+  auto k = estep_kernel<Eval, TT, FAST, LIST>;
+  if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 1;
+  EVO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, TT, smem));
+  if (per_sm < 1) {
+    set_error("evo_estep: %zu bytes of shared memory per datapoint exceed the SM", smem);
+    return EVO_ERR_UNSUPPORTED;
+  }
+  int64_t g = (int64_t)sm_count() * per_sm;
+  if (g > items) g = items;
+  if (g < 1) g = 1;
+  k<<<(int)g, TT, smem, st>>>(dv, ev);
+  EVO_LAUNCH_CHECK("estep");
+  return EVO_OK;
+}
+
+template <class Eval, int TT>
+static int launch_estep_T(const EstepDev &dv, Eval ev, bool fast, cudaStream_t st) {
+  if constexpr (Eval::kList) {
+    if (fast && dv.ovf_list && dv.H < 65535 && dv.N < 2147483647LL && !getenv("EVO_ESTEP_BITS")) {
+      EVO_CUDA(cudaMemsetAsync(dv.ovf_list, 0, sizeof(int32_t), st));
+      EstepDev dl = dv;
+      dl.Hr = LIST_WORDS;
+      dl.Hs = LIST_WORDS + 1;
+      int rc = launch_estep_variant<Eval, TT, true, true>(dl, ev, dv.N, st);
+      if (rc) return rc;
+      EstepDev db = dv;
+      db.n_list = dv.ovf_list;
+      db.ovf_list = nullptr;
+      return launch_estep_variant<Eval, TT, true, false>(db, ev, sm_count(), st);
+    }
+  }
+  EstepDev db = dv;
+  db.ovf_list = nullptr;
+  if (fast) return launch_estep_variant<Eval, TT, true, false>(db, ev, dv.N, st);
+  return launch_estep_variant<Eval, TT, false, false>(db, ev, dv.N, st);
+}
+
 template <class Eval>
 static int launch_estep_any(const EstepDev &dv, Eval ev, cudaStream_t st) {
   int work = dv.S > dv.Cg ? dv.S : dv.Cg;
   int T = ev.threads_hint(work);
   const bool fast = !dv.inj_children && dv.mutation == EVO_MUT_RANDFLIP && !dv.background && !getenv("EVO_ESTEP_GENERIC");
   if (const char *e = getenv("EVO_ESTEP_T")) { int t = atoi(e); if (t > 0) T = t; }
-  T = T <= 32 ? 32 : (T <= 64 ? 64 : (T <= 128 ? 128 : 256));
-  size_t smem = estep_carve(dv, nullptr, nullptr) + ev.smem_bytes(T);
-  if (smem > 227 * 1024) {
-    set_error("evo_estep: %zu bytes of shared memory per datapoint exceed 227 KB", smem);
-    return EVO_ERR_UNSUPPORTED;
-  }
-#define EVO_LAUNCH_T(TT)                                                                              \
-  {                                                                                                   \
-    auto k = fast ? estep_kernel<Eval, TT, true> : estep_kernel<Eval, TT, false>;                     \
-    if (smem > 48 * 1024)                                                                             \
-      EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
-    int per_sm = 1;                                                                                   \
-    EVO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, TT, smem));                    \
-    if (per_sm < 1) {                                                                                 \
-      set_error("evo_estep: %zu bytes of shared memory per datapoint exceed the SM", smem);           \
-      return EVO_ERR_UNSUPPORTED;                                                                     \
-    }                                                                                                 \
-    int64_t g = (int64_t)sm_count() * per_sm;                                                         \
-    if (g > dv.N) g = dv.N;                                                                           \
-    k<<<(int)g, TT, smem, st>>>(dv, ev);                                                              \
-  }
-  if (T == 32) EVO_LAUNCH_T(32)
-  else if (T == 64) EVO_LAUNCH_T(64)
-  else if (T == 128) EVO_LAUNCH_T(128)
-  else EVO_LAUNCH_T(256)
-#undef EVO_LAUNCH_T
-  EVO_LAUNCH_CHECK("estep");
-  return EVO_OK;
+  if (T <= 32) return launch_estep_T<Eval, 32>(dv, ev, fast, st);
+  if (T <= 64) return launch_estep_T<Eval, 64>(dv, ev, fast, st);
+  if (T <= 128) return launch_estep_T<Eval, 128>(dv, ev, fast, st);
+  return launch_estep_T<Eval, 256>(dv, ev, fast, st);
 }
 
 }  // namespace evo

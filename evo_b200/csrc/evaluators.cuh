@@ -25,9 +25,10 @@ struct BscGramEval {
   uint16_t *idx;   // smem [MAXA][T] active-latent lists, one column per thread
   double yn2;
   static constexpr int MAXA = 24;
+  static constexpr bool kList = true;  // can evaluate index-list rows (estep.cuh LIST representation)
 
-  __host__ __device__ size_t smem_bytes(int T) const {
-    return (size_t)H * sizeof(double) + (size_t)MAXA * T * sizeof(uint16_t);
+  __host__ __device__ size_t smem_bytes(int T, bool list = false) const {
+    return (size_t)H * sizeof(double) + (list ? 0 : (size_t)MAXA * T * sizeof(uint16_t));
   }
   __host__ int threads_hint(int work) const { return work <= 32 ? 32 : (work <= 64 ? 64 : 128); }
 
@@ -38,6 +39,12 @@ struct BscGramEval {
     const double *src = B + n * (int64_t)H;
     for (int i = threadIdx.x; i < H; i += T) b[i] = __ldg(src + i);
     yn2 = __ldg(ynorm2 + n);
+  }
+
+  // pre1 (|y|^2 - 2 sum b + sum G) + pil_bar |s| with the contraction spelled out, so that every
+  // evaluation form (bits, scratch lists, list rows) rounds alike
+  __device__ __forceinline__ double combine(double sb, double sg, int a) const {
+    return __fma_rn(pre1, __dadd_rn(__fma_rn(-2.0, sb, yn2), sg), __dmul_rn(pil_bar, (double)a));
   }
 
   // generic form: any number of active latents, no scratch
@@ -66,7 +73,7 @@ struct BscGramEval {
         sg += __ldg(Gr + h) + 2.0 * t;
       }
     }
-    return pre1 * (yn2 - 2.0 * sb + sg) + pil_bar * (double)a;
+    return combine(sb, sg, a);
   }
 
   // list form: one pass over the words collects the active latents, then a dense a x a triangle
@@ -94,12 +101,30 @@ struct BscGramEval {
       for (int j = 0; j < i; ++j) t += __ldg(Gr + my[j * T]);
       sg += __ldg(Gr + h) + 2.0 * t;
     }
-    return pre1 * (yn2 - 2.0 * sb + sg) + pil_bar * (double)a;
+    return combine(sb, sg, a);
   }
 
-  template <int T>
+  // index-list row (16 x uint16: ascending active latents, count in e[15]); same summation order as eval_one
+  __device__ __forceinline__ double eval_list(const uint32_t *row) const {
+    const uint16_t *e = reinterpret_cast<const uint16_t *>(row);
+    const int a = e[15];
+    double sb = 0.0, sg = 0.0;
+    for (int i = 0; i < a; ++i) {
+      const int h = e[i];
+      sb += b[h];
+      const double *Gr = G + (int64_t)h * H;
+      double t = 0.0;
+#pragma unroll 4
+      for (int j = 0; j < i; ++j) t += __ldg(Gr + e[j]);
+      sg += __ldg(Gr + h) + 2.0 * t;
+    }
+    return combine(sb, sg, a);
+  }
+
+  template <int T, bool LIST = false>
   __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) const {
-    for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one<T>(st + (size_t)i * ld), flags);
+    for (int i = threadIdx.x; i < cnt; i += T)
+      out[i] = lpj_sanitise(LIST ? eval_list(st + (size_t)i * ld) : eval_one<T>(st + (size_t)i * ld), flags);
   }
   __device__ double eval_zero(unsigned &flags) const { return lpj_sanitise(pre1 * yn2, flags); }
 };
@@ -119,7 +144,8 @@ struct BscDirectEval {
   uint8_t *m;      // smem [D]
   double yn2;
 
-  __host__ __device__ size_t smem_bytes(int) const { return (size_t)D * sizeof(double) + (((size_t)D + 7) & ~(size_t)7); }
+  static constexpr bool kList = false;
+  __host__ __device__ size_t smem_bytes(int, bool = false) const { return (size_t)D * sizeof(double) + (((size_t)D + 7) & ~(size_t)7); }
   __host__ int threads_hint(int work) const { return work <= 32 ? 32 : (work <= 64 ? 64 : 128); }
 
   template <int T>
@@ -153,7 +179,7 @@ struct BscDirectEval {
     return pre1 * resid + pil_bar * (double)popc_state(st, Hw);
   }
 
-  template <int T>
+  template <int T, bool LIST = false>
   __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) const {
     for (int i = threadIdx.x; i < cnt; i += T) out[i] = lpj_sanitise(eval_one(st + (size_t)i * ld), flags);
   }

@@ -240,6 +240,10 @@ class Model:
             assert ch.shape[0] == dd.N and ch.shape[1] == a.n_generations
             a.inj_children, a.inj_count, a.inj_cmax = ch.data_ptr(), cnt.data_ptr(), int(ch.shape[2])
         a.acc = acc.data_ptr()
+        ovf = getattr(self, "_ovf_list", None)
+        if ovf is None or ovf.numel() < dd.N + 1:
+            ovf = self._ovf_list = torch.empty(dd.N + 1, dtype=torch.int32, device=self.device)
+        a.overflow_list = ovf.data_ptr()
         hold = fill(a)
         with torch.cuda.device(self.device):
             ev = self._tick()

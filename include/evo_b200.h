@@ -137,6 +137,11 @@ typedef struct evo_estep_args {
   /* outputs: acc[0] += sum_n logsumexp_k lpj_nk, acc[1] += #new unique, acc[2] += #substituted,
    * acc[3..5] += lpj_reset_check counters (nan, small, inf), acc[6] += #log-joints evaluated */
   double *acc;
+  /* optional workspace of N + 1 int32 (or NULL).  With it, the BSC Gram E-step in RNG mode with randflip
+   * keeps states in shared memory as lists of at most 15 active latents (32 bytes per state instead of
+   * 4*Hw); datapoints that do not fit are collected here and redone by the packed-bits kernel in the same
+   * call.  Results do not depend on which kernel handled a datapoint. */
+  int32_t *overflow_list;
 } evo_estep_args;
 int evo_estep(const evo_estep_args *args, void *stream);
 

@@ -41,6 +41,7 @@ def _oracle(W, Y, X, st, pre1, pil_bar):
         (144, 70, 48, 33, 4.0, 0.3, 1e-3),    # masked entries, tiny W (power-of-two rescaling)
         (300, 130, 64, 20, 6.0, 0.0, 1.0),    # D > 256 with a ragged second column tile
         (1024, 1024, 128, 12, 8.0, 0.0, 1.0),  # cfg5 shape: 4 column tiles, 16 k-blocks
+        (1100, 40, 32, 9, 4.0, 0.0, 1.0),     # D > 1024: y is read from global memory, 5 column tiles
     ],
 )
 def test_dense_lpj_matches_oracle_and_gram(D, H, S, N, act, missing, wscale):
@@ -91,7 +92,7 @@ def test_dense_lpj_linearity_at_full_tile_count():
     assert np.max(np.abs(a - s) / np.maximum(np.abs(s), 1e-12)) < TOL
 
 
-@pytest.mark.parametrize("D,H,N,wscale", [(25, 10, 300, 10.0), (256, 300, 1000, 1.0), (144, 70, 129, 1e-3), (1024, 1024, 500, 1.0)])
+@pytest.mark.parametrize("D,H,N,wscale", [(25, 10, 300, 10.0), (256, 300, 1000, 1.0), (144, 70, 129, 1e-3), (1024, 1024, 500, 1.0), (40, 33, 130, 1.0)])
 def test_tc_table_matches_f64_table(D, H, N, wscale):
     """B = Y W from the tcgen05 split-precision GEMM vs the f64 SIMT GEMM (evo_bsc_prepare) and NumPy.
     Stated bound: 1e-5 of max|B| (fp16 hi+lo operands, three passes, fp32 tensor-core accumulation over
