@@ -147,6 +147,30 @@ __device__ __forceinline__ bool list_from_bits(const uint32_t *src, int Hg, uint
   __syncwarp();
   return base <= LIST_CAP;
 }
+// the same conversion by ONE thread (short rows: fewer instructions than a warp scan per state)
+__device__ __forceinline__ bool list_from_bits_thread(const uint32_t *src, int Hg, uint32_t *row) {
+  uint16_t *e = reinterpret_cast<uint16_t *>(row);
+#pragma unroll
+  for (int w = 0; w < LIST_WORDS; ++w) row[w] = 0xFFFFFFFFu;
+  int cnt = 0;
+  for (int w0 = 0; w0 < Hg; w0 += 4) {
+    uint32_t x[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) x[q] = (w0 + q < Hg) ? __ldg(src + w0 + q) : 0u;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t m = x[q];
+      while (m) {
+        const int bp = __ffs(m) - 1;
+        m &= m - 1;
+        if (cnt < LIST_CAP) e[cnt] = (uint16_t)(((w0 + q) << 5) + bp);
+        ++cnt;
+      }
+    }
+  }
+  e[15] = (uint16_t)(cnt <= LIST_CAP ? cnt : LIST_CAP);
+  return cnt <= LIST_CAP;
+}
 // list row -> packed bits (Hg words), one thread
 __device__ __forceinline__ void list_to_bits(const uint32_t *row, int Hg, uint32_t *dst) {
   const uint16_t *e = reinterpret_cast<const uint16_t *>(row);
@@ -293,8 +317,13 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       if (LIST) {
         if (tid == 0) s.sh[0] = 0;
         gsync<T>();
-        for (int i = tid >> 5; i < S; i += T / 32)
-          if (!list_from_bits(src + (size_t)i * Hg, Hg, s.st_uniq + (size_t)i * Hs) && (tid & 31) == 0) s.sh[0] = 1;
+        if (Hg <= 64) {
+          for (int i = tid; i < S; i += T)
+            if (!list_from_bits_thread(src + (size_t)i * Hg, Hg, s.st_uniq + (size_t)i * Hs)) s.sh[0] = 1;
+        } else {
+          for (int i = tid >> 5; i < S; i += T / 32)
+            if (!list_from_bits(src + (size_t)i * Hg, Hg, s.st_uniq + (size_t)i * Hs) && (tid & 31) == 0) s.sh[0] = 1;
+        }
       } else {
         for (int i = tid; i < S * Hw; i += T) s.st_uniq[(i / Hw) * Hs + (i % Hw)] = src[i];
       }

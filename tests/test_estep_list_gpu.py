@@ -56,6 +56,7 @@ def _run_both(D, H, K, N, act, ea, iters=3):
         (32, 48, 16, 500, 30.0, (4, 3, 2), True),      # dense: (nearly) every datapoint overflows
         (256, 300, 64, 2000, 5.0, (8, 8, 2), None),    # cfg2 shape (a handful of initial states overflow)
         (40, 1030, 32, 300, 4.0, (8, 4, 2), False),    # H > 1024 (33 words per packed state)
+        (16, 2100, 16, 150, 4.0, (4, 3, 2), False),    # more than 64 words per packed state: warp-scan load
     ],
 )
 def test_list_kernel_equals_bits_kernel(D, H, K, N, act, ea, expect_overflow):
