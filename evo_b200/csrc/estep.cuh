@@ -184,32 +184,39 @@ __device__ __forceinline__ void list_to_bits(const uint32_t *row, int Hg, uint32
 }
 
 // ---- hash table over packed states --------------------------------------------------------
+// (LIST rows have a compile-time width, so hashing and comparing unroll fully)
+template <bool LIST>
 __device__ __forceinline__ const uint32_t *tag_state(const EstepDev &a, const EstepSmem &s, int tag) {
-  return tag >= TAG_CHILD ? s.st_child + (size_t)(tag - TAG_CHILD) * a.Hs : s.st_uniq + (size_t)tag * a.Hs;
+  const int hs = LIST ? LIST_WORDS + 1 : a.Hs;
+  return tag >= TAG_CHILD ? s.st_child + (size_t)(tag - TAG_CHILD) * hs : s.st_uniq + (size_t)tag * hs;
 }
 // read-only probe: index of the uniq entry equal to st, or -1
+template <bool LIST>
 __device__ __forceinline__ int table_find(const EstepDev &a, const EstepSmem &s, const uint32_t *st) {
+  const int hw = LIST ? LIST_WORDS : a.Hr;
   uint32_t mask = (uint32_t)a.HT - 1u;
-  uint32_t p = (uint32_t)hash_state(st, a.Hr) & mask;
+  uint32_t p = (uint32_t)hash_state(st, hw) & mask;
   for (int it = 0; it < a.HT; ++it) {
     int tag = s.table[p];
     if (tag == TAG_EMPTY) return -1;
-    if (same_state(tag_state(a, s, tag), st, a.Hr)) return tag;
+    if (same_state(tag_state<LIST>(a, s, tag), st, hw)) return tag;
     p = (p + 1) & mask;
   }
   return -1;
 }
 // concurrent insert; equal states converge on one slot holding the smallest tag.  Returns the slot.
+template <bool LIST>
 __device__ __forceinline__ int table_insert(const EstepDev &a, const EstepSmem &s, const uint32_t *st, int tag) {
+  const int hw = LIST ? LIST_WORDS : a.Hr;
   uint32_t mask = (uint32_t)a.HT - 1u;
-  uint32_t p = (uint32_t)hash_state(st, a.Hr) & mask;
+  uint32_t p = (uint32_t)hash_state(st, hw) & mask;
   for (int it = 0; it < a.HT; ++it) {
     int cur = s.table[p];
     if (cur == TAG_EMPTY) {
       cur = atomicCAS(&s.table[p], TAG_EMPTY, tag);
       if (cur == TAG_EMPTY) return (int)p;
     }
-    if (same_state(tag_state(a, s, cur), st, a.Hr)) {
+    if (same_state(tag_state<LIST>(a, s, cur), st, hw)) {
       atomicMin(&s.table[p], tag);
       return (int)p;
     }
@@ -231,21 +238,25 @@ __device__ __forceinline__ double order_key(double v, uint32_t idx, uint32_t mas
 }
 __device__ __forceinline__ int count_greater(const double *keys, int n, double k) {
   int r = 0, j = 0;
+#pragma unroll 2
   for (; j + 4 <= n; j += 4) {
     const double2 x = *reinterpret_cast<const double2 *>(keys + j);
     const double2 y = *reinterpret_cast<const double2 *>(keys + j + 2);
     r += (int)(x.x > k) + (int)(x.y > k) + (int)(y.x > k) + (int)(y.y > k);
   }
+#pragma unroll 1
   for (; j < n; ++j) r += (int)(keys[j] > k);
   return r;
 }
 __device__ __forceinline__ int count_less(const double *keys, int n, double k) {
   int r = 0, j = 0;
+#pragma unroll 2
   for (; j + 4 <= n; j += 4) {
     const double2 x = *reinterpret_cast<const double2 *>(keys + j);
     const double2 y = *reinterpret_cast<const double2 *>(keys + j + 2);
     r += (int)(x.x < k) + (int)(x.y < k) + (int)(y.x < k) + (int)(y.y < k);
   }
+#pragma unroll 1
   for (; j < n; ++j) r += (int)(keys[j] < k);
   return r;
 }
@@ -300,7 +311,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
   EstepSmem s;
   estep_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
-  const int Hw = a.Hr, Hg = a.Hw, Hs = a.Hs, S = a.S;  // Hw: words of a shared-memory row, Hg: of a global row
+  const int Hw = LIST ? LIST_WORDS : a.Hr, Hg = a.Hw, Hs = LIST ? LIST_WORDS + 1 : a.Hs, S = a.S;  // Hw: words of a shared-memory row, Hg: of a global row
   const bool bgu = FAST ? false : (a.background != 0);
   const int Hm = bgu ? a.H - 1 : a.H;
   double acc_F = 0.0, acc_U = 0.0, acc_sub = 0.0, acc_eval = 0.0;
@@ -318,17 +329,17 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         if (tid == 0) s.sh[0] = 0;
         gsync<T>();
         if (Hg <= 64) {
-          for (int i = tid; i < S; i += T)
+          _Pragma("unroll 1") for (int i = tid; i < S; i += T)
             if (!list_from_bits_thread(src + (size_t)i * Hg, Hg, s.st_uniq + (size_t)i * Hs)) s.sh[0] = 1;
         } else {
           for (int i = tid >> 5; i < S; i += T / 32)
             if (!list_from_bits(src + (size_t)i * Hg, Hg, s.st_uniq + (size_t)i * Hs) && (tid & 31) == 0) s.sh[0] = 1;
         }
       } else {
-        for (int i = tid; i < S * Hw; i += T) s.st_uniq[(i / Hw) * Hs + (i % Hw)] = src[i];
+        _Pragma("unroll 1") for (int i = tid; i < S * Hw; i += T) s.st_uniq[(i / Hw) * Hs + (i % Hw)] = src[i];
       }
-      for (int i = tid; i < a.HT; i += T) s.table[i] = TAG_EMPTY;
-      for (int i = tid; i < S + a.Ctot; i += T) s.redisc[i] = 0;
+      _Pragma("unroll 1") for (int i = tid; i < a.HT; i += T) s.table[i] = TAG_EMPTY;
+      _Pragma("unroll 1") for (int i = tid; i < S + a.Ctot; i += T) s.redisc[i] = 0;
       ev.template setup<T>(n, s.eval_smem);
     }
     gsync<T>();
@@ -348,13 +359,13 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       ev.template eval_batch<T, LIST>(s.st_uniq, Hs, S, s.lpj_uniq, fl);
       fl = group_or<T>(fl, s.red_i);
       if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
-      for (int i = tid; i < S; i += T) table_insert(a, s, s.st_uniq + (size_t)i * Hs, i);
+      _Pragma("unroll 1") for (int i = tid; i < S; i += T) table_insert<LIST>(a, s, s.st_uniq + (size_t)i * Hs, i);
     }
     gsync<T>();
 
     int U = 0;        // accepted new unique states so far
     int pool_n = S;   // generation 0 selects from K^n
-    for (int i = tid; i < S; i += T) s.pool[i] = i;
+    _Pragma("unroll 1") for (int i = tid; i < S; i += T) s.pool[i] = i;
     gsync<T>();
 
     for (int g = 0; g < a.n_generations; ++g) {
@@ -364,18 +375,18 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         nc = a.inj_count[n * (int64_t)a.n_generations + g];
         if (nc > a.Cg) nc = a.Cg;
         const uint32_t *src = a.inj_children + ((n * (int64_t)a.n_generations + g) * a.inj_cmax) * (int64_t)Hg;
-        for (int i = tid; i < nc * Hw; i += T) s.st_child[(i / Hw) * Hs + (i % Hw)] = src[i];
+        _Pragma("unroll 1") for (int i = tid; i < nc * Hw; i += T) s.st_child[(i / Hw) * Hs + (i % Hw)] = src[i];
       } else {
         // ---- parent selection (eas.py:138-150) -------------------------------------------------
         int take = pool_n < a.n_parents ? pool_n : a.n_parents;
         {
           double mn = DBL_MAX;
           if (a.selection == EVO_SEL_FIT) {
-            for (int i = tid; i < pool_n; i += T) mn = fmin(mn, s.lpj_uniq[s.pool[i]]);
+            _Pragma("unroll 1") for (int i = tid; i < pool_n; i += T) mn = fmin(mn, s.lpj_uniq[s.pool[i]]);
             mn = -group_max<T>(-mn, s.red_d);
           }
           double shift = 2.0 * fmin(mn, 0.0);
-          for (int i = tid; i < pool_n; i += T) {
+          _Pragma("unroll 1") for (int i = tid; i < pool_n; i += T) {
             uint4 r = rng.draw(RNG_SELECT, g, (uint32_t)i);
             double u = u01(r.x, r.y);
             double key;
@@ -390,7 +401,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           }
           gsync<T>();
           // the `take` largest keys, by rank counting (strict total order: key desc, index asc)
-          for (int i = tid; i < pool_n; i += T) {
+          _Pragma("unroll 1") for (int i = tid; i < pool_n; i += T) {
             int r = count_greater(s.keys, pool_n, s.keys[i]);
             if (r < take) s.parents[r] = s.pool[i];
           }
@@ -403,7 +414,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           nc = take * C;
           if (FAST || mut == EVO_MUT_RANDFLIP) {
             // C distinct uniformly drawn positions per parent; child j flips position j
-            for (int p = tid; p < take; p += T) {
+            _Pragma("unroll 1") for (int p = tid; p < take; p += T) {
               uint32_t di = (uint32_t)p * 64u * (uint32_t)(C + 1);
               for (int j = 0; j < C; ++j) {
                 int pos;
@@ -420,7 +431,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             }
             gsync<T>();
           }
-          for (int c = tid; c < nc; c += T) {
+          _Pragma("unroll 1") for (int c = tid; c < nc; c += T) {
             int p = c / C;
             const uint32_t *src = s.st_uniq + (size_t)s.parents[p] * Hs;
             uint32_t *dst = s.st_child + (size_t)c * Hs;
@@ -435,7 +446,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           // one-point crossover of every unordered parent pair, two children per pair
           int npairs = take * (take - 1) / 2;
           nc = 2 * npairs;
-          for (int q = tid; q < npairs; q += T) {
+          _Pragma("unroll 1") for (int q = tid; q < npairs; q += T) {
             int i = 0, rem = q;
             while (rem >= take - 1 - i) { rem -= take - 1 - i; ++i; }
             int j = i + 1 + rem;
@@ -469,19 +480,19 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       if (LIST && s.sh[0]) break;  // a child does not fit the list form: the packed-bits kernel redoes this datapoint
 
       // ---- de-duplicate against (permanent, K^n, earlier new) and among the children ----------
-      for (int c = tid; c < nc; c += T) {
+      _Pragma("unroll 1") for (int c = tid; c < nc; c += T) {
         const uint32_t *st = s.st_child + (size_t)c * Hs;
         unsigned char stt = 1;  // candidate
         if (a.S_perm > 0 && (LIST ? reinterpret_cast<const uint16_t *>(st)[15] == 0 : popc_state(st, Hw) == 0)) stt = 0;
         else {
-          int hit = table_find(a, s, st);
+          int hit = table_find<LIST>(a, s, st);
           if (hit >= 0) { s.redisc[hit] = 1; stt = 0; }
         }
         s.status[c] = stt;
       }
       gsync<T>();
-      for (int c = tid; c < nc; c += T)
-        if (s.status[c]) s.slot[c] = table_insert(a, s, s.st_child + (size_t)c * Hs, TAG_CHILD + c);
+      _Pragma("unroll 1") for (int c = tid; c < nc; c += T)
+        if (s.status[c]) s.slot[c] = table_insert<LIST>(a, s, s.st_child + (size_t)c * Hs, TAG_CHILD + c);
       gsync<T>();
       // first occurrence of each new state wins; compact winners (child order) behind st_uniq
       int u_g = 0;
@@ -516,7 +527,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       gsync<T>();
       // ---- next pool: this round's new states, then the re-discovered old ones -----------------
       int pn = 0;
-      for (int i = tid; i < u_g && i < a.PK; i += T) s.pool[i] = S + U + i;
+      _Pragma("unroll 1") for (int i = tid; i < u_g && i < a.PK; i += T) s.pool[i] = S + U + i;
       pn = u_g < a.PK ? u_g : a.PK;
       for (int base = 0; base < S + U; base += T) {
         int i = base + tid;
@@ -549,22 +560,22 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       int Mp = U < a.Mprime ? U : a.Mprime;
       if (Mp > 0) {
         double mn = DBL_MAX;
-        for (int i = tid; i < S; i += T) mn = fmin(mn, s.lpj_uniq[i]);
+        _Pragma("unroll 1") for (int i = tid; i < S; i += T) mn = fmin(mn, s.lpj_uniq[i]);
         mn = -group_max<T>(-mn, s.red_d);
         // only candidates above the worst old state can ever be accepted
         const double *ln = s.lpj_uniq + S;
         double *kn = s.keys, *ko = s.keys + ((a.Ctot + 1) & ~1);
-        for (int i = tid; i < U; i += T) kn[i] = order_key(ln[i], (uint32_t)i, a.mask_c, true);
-        for (int k = tid; k < S; k += T) ko[k] = order_key(s.lpj_uniq[k], (uint32_t)k, a.mask_s, false);
+        _Pragma("unroll 1") for (int i = tid; i < U; i += T) kn[i] = order_key(ln[i], (uint32_t)i, a.mask_c, true);
+        _Pragma("unroll 1") for (int k = tid; k < S; k += T) ko[k] = order_key(s.lpj_uniq[k], (uint32_t)k, a.mask_s, false);
         gsync<T>();
-        for (int i = tid; i < U; i += T) s.rnk[i] = (ln[i] > mn) ? count_greater(kn, U, kn[i]) : Mp;
-        for (int k = tid; k < S; k += T) {
+        _Pragma("unroll 1") for (int i = tid; i < U; i += T) s.rnk[i] = (ln[i] > mn) ? count_greater(kn, U, kn[i]) : Mp;
+        _Pragma("unroll 1") for (int k = tid; k < S; k += T) {
           int r = count_less(ko, S, ko[k]);
           if (r < Mp) s.old_by_rank[r] = k;
         }
         gsync<T>();
         int acc_local = 0;
-        for (int i = tid; i < U; i += T) {
+        _Pragma("unroll 1") for (int i = tid; i < U; i += T) {
           int r = s.rnk[i];
           if (r >= Mp) continue;
           int k = s.old_by_rank[r];
@@ -583,7 +594,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           ++acc_local;
         }
         gsync<T>();
-        for (int i = tid; i < U; i += T) { int r = s.rnk[i]; if (r < 0) s.lpj_uniq[-1 - r] = ln[i]; }
+        _Pragma("unroll 1") for (int i = tid; i < U; i += T) { int r = s.rnk[i]; if (r < 0) s.lpj_uniq[-1 - r] = ln[i]; }
         n_sub = group_sum_i<T>(acc_local, s.red_i);
         gsync<T>();
       }
@@ -592,11 +603,11 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
     {
       double *row = a.lpj + n * (int64_t)(S + a.S_perm);
       double mx = -DBL_MAX;
-      for (int i = tid; i < S; i += T) { double v = s.lpj_uniq[i]; row[a.S_perm + i] = v; mx = fmax(mx, v); }
+      _Pragma("unroll 1") for (int i = tid; i < S; i += T) { double v = s.lpj_uniq[i]; row[a.S_perm + i] = v; mx = fmax(mx, v); }
       if (a.S_perm > 0) { if (tid == 0) row[0] = lpj_perm; mx = fmax(mx, lpj_perm); }
       mx = group_max<T>(mx, s.red_d);
       double se = 0.0;
-      for (int i = tid; i < S; i += T) se += exp(s.lpj_uniq[i] - mx);
+      _Pragma("unroll 1") for (int i = tid; i < S; i += T) se += exp(s.lpj_uniq[i] - mx);
       if (a.S_perm > 0 && tid == 0) se += exp(lpj_perm - mx);
       se = group_sum<T>(se, s.red_d);
       if (tid == 0) {
