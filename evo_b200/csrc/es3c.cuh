@@ -402,27 +402,26 @@ struct Es3cEval {
   __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) {
     if (masked) yn2 = masked_yn2();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (max_batch <= 0 || cnt > max_batch) {  // no index lists: one warp per state
-      for (int i = warp; i < cnt; i += T / 32) {
-        double v = warp_lpj(st + (size_t)i * ld);
-        v = lpj_sanitise(v, flags);
-        if (lane == 0) out[i] = v;
-      }
-      return;
-    }
-    // split the batch by |s|: systems with a <= 8 are packed four per warp
+    // split the batch by |s|: systems with a <= 8 are packed four per warp (without list space every
+    // state goes to the warp-per-state solver)
+    const bool listed = max_batch > 0 && cnt <= max_batch;
     int *cn = reinterpret_cast<int *>(lsm);
     uint16_t *small = reinterpret_cast<uint16_t *>(lsm + 8), *big = small + max_batch;
-    gsync<T>();
-    if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; }
-    gsync<T>();
-    for (int i = threadIdx.x; i < cnt; i += T) {
-      const int a = popc_state(st + (size_t)i * ld, Hw);
-      if (a <= G8) small[atomicAdd(&cn[0], 1)] = (uint16_t)i;
-      else big[atomicAdd(&cn[1], 1)] = (uint16_t)i;
+    int ns = 0, nb = cnt;
+    if (listed) {
+      gsync<T>();
+      if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; }
+      gsync<T>();
+#pragma unroll 1
+      for (int i = threadIdx.x; i < cnt; i += T) {
+        const int a = popc_state(st + (size_t)i * ld, Hw);
+        if (a <= G8) small[atomicAdd(&cn[0], 1)] = (uint16_t)i;
+        else big[atomicAdd(&cn[1], 1)] = (uint16_t)i;
+      }
+      gsync<T>();
+      ns = cn[0], nb = cn[1];
     }
-    gsync<T>();
-    const int ns = cn[0], nb = cn[1];
+#pragma unroll 1
     for (int q = warp; q * 4 < ns; q += T / 32) {
       const int j = q * 4 + (lane >> 3);
       if (j < ns) {  // whole 8-lane groups take or skip this branch together
@@ -433,8 +432,9 @@ struct Es3cEval {
       }
     }
     __syncwarp();
+#pragma unroll 1
     for (int q = warp; q < nb; q += T / 32) {
-      const int i = big[q];
+      const int i = listed ? (int)big[q] : q;
       double v = warp_lpj(st + (size_t)i * ld);
       v = lpj_sanitise(v, flags);
       if (lane == 0) out[i] = v;

@@ -347,29 +347,22 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       if (tid == 0) a.ovf_list[1 + atomicAdd(a.ovf_list, 1)] = (int32_t)n;
       continue;
     }
-    // ---- lpj of the permanent state and of K^n ------------------------------------------------
+    // ---- lpj of the permanent state ---------------------------------------------------------------
     double lpj_perm = 0.0;
-    {
-      unsigned fl = 0;
-      if (a.S_perm > 0) {
-        unsigned f0 = 0;
-        lpj_perm = ev.eval_zero(f0);
-        if (tid == 0 && f0) { if (f0 & 1) ++cnt_nan; else if (f0 & 2) ++cnt_small; else ++cnt_inf; }
-      }
-      ev.template eval_batch<T, LIST>(s.st_uniq, Hs, S, s.lpj_uniq, fl);
-      fl = group_or<T>(fl, s.red_i);
-      if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
-      _Pragma("unroll 1") for (int i = tid; i < S; i += T) table_insert<LIST>(a, s, s.st_uniq + (size_t)i * Hs, i);
+    if (a.S_perm > 0) {
+      unsigned f0 = 0;
+      lpj_perm = ev.eval_zero(f0);
+      if (tid == 0 && f0) { if (f0 & 1) ++cnt_nan; else if (f0 & 2) ++cnt_small; else ++cnt_inf; }
     }
-    gsync<T>();
 
     int U = 0;        // accepted new unique states so far
     int pool_n = S;   // generation 0 selects from K^n
-    _Pragma("unroll 1") for (int i = tid; i < S; i += T) s.pool[i] = i;
-    gsync<T>();
 
-    for (int g = 0; g < a.n_generations; ++g) {
-      int nc = 0;
+    // pass g = -1 evaluates K^n, passes 0.. are the generations: ONE call site of the evaluator, so its
+    // code is instantiated once (instruction-cache footprint)
+    for (int g = -1; g < a.n_generations; ++g) {
+      int nc = 0, u_g = 0;
+      if (g >= 0) {
       if (!FAST && a.inj_children) {
         // ---- injected candidates (parity runs) -------------------------------------------------
         nc = a.inj_count[n * (int64_t)a.n_generations + g];
@@ -495,7 +488,6 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         if (s.status[c]) s.slot[c] = table_insert<LIST>(a, s, s.st_child + (size_t)c * Hs, TAG_CHILD + c);
       gsync<T>();
       // first occurrence of each new state wins; compact winners (child order) behind st_uniq
-      int u_g = 0;
       for (int base = 0; base < nc; base += T) {
         int c = base + tid;
         bool win = false;
@@ -515,16 +507,27 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         gsync<T>();
       }
 
-      // ---- lpj of the genuinely new states ------------------------------------------------------
+      }  // g >= 0
+
+      // ---- lpj of K^n (g = -1) or of the genuinely new states -----------------------------------
       {
+        const int first = g < 0 ? 0 : S + U, cnt = g < 0 ? S : u_g;
         unsigned fl = 0;
-        if (u_g > 0) {
-          ev.template eval_batch<T, LIST>(s.st_uniq + (size_t)(S + U) * Hs, Hs, u_g, s.lpj_uniq + S + U, fl);
+        if (cnt > 0) {
+          ev.template eval_batch<T, LIST>(s.st_uniq + (size_t)first * Hs, Hs, cnt, s.lpj_uniq + first, fl);
           fl = group_or<T>(fl, s.red_i);
           if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
         }
       }
       gsync<T>();
+      if (g < 0) {
+        _Pragma("unroll 1") for (int i = tid; i < S; i += T) {
+          table_insert<LIST>(a, s, s.st_uniq + (size_t)i * Hs, i);
+          s.pool[i] = i;
+        }
+        gsync<T>();
+        continue;
+      }
       // ---- next pool: this round's new states, then the re-discovered old ones -----------------
       int pn = 0;
       _Pragma("unroll 1") for (int i = tid; i < u_g && i < a.PK; i += T) s.pool[i] = S + U + i;
