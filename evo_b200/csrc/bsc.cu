@@ -146,113 +146,175 @@ struct WpLists {
 };
 constexpr int WP_OFF = 40;
 
-template <int T>
-__global__ void __launch_bounds__(T) bsc_suffstats_kernel(const uint32_t *__restrict__ states,
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_max_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// One WARP per datapoint (persistent loop; no CTA barrier anywhere).  Lane k owns state k of a batch of
+// 32: it lists the state's active latents once (SS_LS entries; longer states take the bit-scan path)
+// and issues one global f64 atomic per pair.  <s>_n is gathered latent by latent over the union of the
+// states' active latents (lane per latent, fixed summation order k = 0..S-1), so no shared-memory atomics.
+constexpr int SS_LS = 16, SS_LD = 18;  // list capacity / row stride in uint16 (9 words: conflict-free rows)
+__host__ __device__ inline size_t suffstats_warp_bytes(int H, int Hw, int cols) {
+  size_t b = (size_t)8 * H + (size_t)8 * cols;       // es, q
+  b += ((size_t)4 * Hw + 7) & ~(size_t)7;             // union words
+  b += ((size_t)2 * H + 7) & ~(size_t)7;              // act
+  b += (size_t)2 * 32 * SS_LD;                        // per-lane state lists
+  return (b + 15) & ~(size_t)15;
+}
+
+__global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__restrict__ states,
                                                           const double *__restrict__ lpj,
                                                           const float *__restrict__ Ym, int64_t N, int D, int H, int Hw,
                                                           int S, int S_perm, double pre1, double pil_bar,
                                                           double *__restrict__ stats, float *__restrict__ Es_out,
                                                           WpLists lists) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ double red_d[8];
-  __shared__ int red_i[8];
-  __shared__ int n_act;
-  double *es = reinterpret_cast<double *>(smem_raw);          // [H]
-  double *q = es + H;                                          // [S + S_perm]
-  float *y = reinterpret_cast<float *>(q + S + S_perm);        // [D]
-  int *act = reinterpret_cast<int *>(y + D);                   // [H]
+  const int cols = S + S_perm;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+  unsigned char *mine = smem_raw + (size_t)warp * suffstats_warp_bytes(H, Hw, cols);
+  double *es = reinterpret_cast<double *>(mine);  // [H]
+  double *q = es + H;                              // [cols]
+  uint32_t *uni = reinterpret_cast<uint32_t *>(q + cols);
+  uint16_t *act = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(uni) + (((size_t)4 * Hw + 7) & ~(size_t)7));
+  uint16_t *slist = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(act) + (((size_t)2 * H + 7) & ~(size_t)7));
+  uint16_t *my_list = slist + lane * SS_LD;
   double *Wp = stats, *Wq = stats + (int64_t)H * D, *pies = Wq + (int64_t)H * H, *sig = pies + H;
   double sig_acc = 0.0;
-  const int cols = S + S_perm;
-  for (int h = threadIdx.x; h < H; h += T) es[h] = 0.0;  // kept zero between datapoints (active entries reset below)
-  for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
-    __syncthreads();
-    if (!lists.off)
-      for (int d = threadIdx.x; d < D; d += T) y[d] = Ym[n * D + d];
-    posterior<T>(lpj + n * cols, cols, q, red_d);
+  for (int h = lane; h < H; h += 32) es[h] = 0.0;  // kept zero between datapoints (active entries reset below)
+  __syncwarp();
+  for (int64_t n = (int64_t)blockIdx.x * wpc + warp; n < N; n += (int64_t)gridDim.x * wpc) {
+    // ---- posterior weights (bsc.py:176-177,219) ------------------------------------------------
+    const double *row = lpj + n * cols;
+    double mx = -DBL_MAX;
+    for (int i = lane; i < cols; i += 32) { double v = row[i]; q[i] = v; mx = fmax(mx, v); }
+    mx = warp_max_d(mx);
+    double se = 0.0;
+    for (int i = lane; i < cols; i += 32) { double e = exp(q[i] - mx); q[i] = e; se += e; }
+    se = warp_sum_d(se);
+    const double inv = 1.0 / se;
+    for (int i = lane; i < cols; i += 32) q[i] *= inv;
+    __syncwarp();
+    // ---- per state: sigma (every state), Wq pairs (states that carry mass) --------------------
     const uint32_t *st = states + n * (int64_t)S * Hw;
-    // per state: es, Wq, sigma
     double sg = 0.0;
-    for (int k = threadIdx.x; k < S; k += T) {
-      double qk = q[S_perm + k];
+#pragma unroll 1
+    for (int k = lane; k < S; k += 32) {
+      const double qk = q[S_perm + k];
       const uint32_t *sk = st + (int64_t)k * Hw;
+      const bool live = qk > Q_SKIP;
       int a = 0;
-      bool live = qk > Q_SKIP;
-      for (int w1 = 0; w1 < Hw; ++w1) {
-        uint32_t m1 = sk[w1];
-        a += __popc(m1);
-        if (!live) continue;
-        while (m1) {
-          int b1 = __ffs(m1) - 1;
-          m1 &= m1 - 1;
-          int h = (w1 << 5) + b1;
-          atomicAdd(&es[h], qk);
-          double *row = Wq + (int64_t)h * H;
-          for (int w2 = 0; w2 <= w1; ++w2) {
-            uint32_t m2 = sk[w2];
-            if (w2 == w1) m2 &= (b1 == 31) ? 0xFFFFFFFFu : ((2u << b1) - 1u);  // h' <= h
-            while (m2) {
-              int b2 = __ffs(m2) - 1;
-              m2 &= m2 - 1;
-              atomicAdd(row + (w2 << 5) + b2, qk);
+      for (int w = 0; w < Hw; ++w) {
+        uint32_t m = sk[w];
+        if (live)
+          while (m) {
+            const int bp = __ffs(m) - 1;
+            m &= m - 1;
+            if (a < SS_LS) my_list[a] = (uint16_t)((w << 5) + bp);
+            ++a;
+          }
+        else
+          a += __popc(m);
+      }
+      sg += qk * (row[S_perm + k] - pil_bar * (double)a) / pre1;
+      if (!live) continue;
+      if (a <= SS_LS) {
+        for (int i = 0; i < a; ++i) {
+          double *wrow = Wq + (int64_t)my_list[i] * H;
+          for (int j = 0; j <= i; ++j) atomicAdd(wrow + my_list[j], qk);  // h' <= h
+        }
+      } else {  // long state: enumerate the pairs from the bits
+        for (int w1 = 0; w1 < Hw; ++w1) {
+          uint32_t m1 = sk[w1];
+          while (m1) {
+            const int b1 = __ffs(m1) - 1;
+            m1 &= m1 - 1;
+            double *wrow = Wq + (int64_t)((w1 << 5) + b1) * H;
+            for (int w2 = 0; w2 <= w1; ++w2) {
+              uint32_t m2 = sk[w2];
+              if (w2 == w1) m2 &= (b1 == 31) ? 0xFFFFFFFFu : ((2u << b1) - 1u);
+              while (m2) {
+                const int b2 = __ffs(m2) - 1;
+                m2 &= m2 - 1;
+                atomicAdd(wrow + (w2 << 5) + b2, qk);
+              }
             }
           }
         }
       }
-      sg += qk * (lpj[n * cols + S_perm + k] - pil_bar * (double)a) / pre1;
     }
-    if (S_perm > 0 && threadIdx.x == 0) sg += q[0] * lpj[n * cols] / pre1;  // all-zero state: |y|^2
+    if (S_perm > 0 && lane == 0) sg += q[0] * row[0] / pre1;  // all-zero state: |y|^2
     sig_acc += sg;
-    __syncthreads();
-    // active latents
-    if (threadIdx.x == 0) n_act = 0;
-    __syncthreads();
-    for (int base = 0; base < H; base += T) {
-      int h = base + threadIdx.x;
-      bool f = h < H && es[h] != 0.0;
-      int tot;
-      int off = group_scan_flag<T>(f, tot, red_i);
-      if (f) act[n_act + off] = h;
-      __syncthreads();
-      if (threadIdx.x == 0) n_act += tot;
-      __syncthreads();
+    // ---- <s>_n over the union of the live states' active latents --------------------------------
+    for (int w = lane; w < Hw; w += 32) {
+      uint32_t u = 0u;
+      for (int k = 0; k < S; ++k)
+        if (q[S_perm + k] > Q_SKIP) u |= st[(int64_t)k * Hw + w];
+      uni[w] = u;
     }
-    int na = n_act;
-    for (int i = threadIdx.x; i < na; i += T) atomicAdd(pies + act[i], es[act[i]]);
+    __syncwarp();
+    int nu = 0;  // union, ascending -> act
+    for (int w0 = 0; w0 < Hw; w0 += 32) {
+      uint32_t word = (w0 + lane < Hw) ? uni[w0 + lane] : 0u;
+      const int c = __popc(word);
+      int pre = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += t; }
+      int pos = nu + pre - c;
+      while (word) {
+        const int bp = __ffs(word) - 1;
+        word &= word - 1;
+        act[pos++] = (uint16_t)(((w0 + lane) << 5) + bp);
+      }
+      nu += __shfl_sync(0xffffffffu, pre, 31);
+    }
+    __syncwarp();
+    for (int i = lane; i < nu; i += 32) {
+      const int h = act[i], w = h >> 5, bit = h & 31;
+      double e = 0.0;
+      for (int k = 0; k < S; ++k) {
+        const double qk = q[S_perm + k];
+        if (qk > Q_SKIP && ((st[(int64_t)k * Hw + w] >> bit) & 1u)) e += qk;
+      }
+      es[h] = e;  // > 0: the latent is active in a live state
+    }
+    __syncwarp();
+    const int na = nu;
     if (Es_out)
-      for (int h = threadIdx.x; h < H; h += T) Es_out[n * H + h] = (float)es[h];
+      for (int h = lane; h < H; h += 32) Es_out[n * H + h] = (float)es[h];
+    for (int i = lane; i < na; i += 32) atomicAdd(pies + act[i], es[act[i]]);
     if (lists.off) {
       // hand the sparse <s>_n (ascending h) to the Wp pass; overflow entries are accumulated here
       const int nl = na < WP_LCAP ? na : WP_LCAP;
-      if (threadIdx.x <= WP_WARPS) {
-        const int hb = (H + WP_WARPS - 1) / WP_WARPS, bound = threadIdx.x * hb;
+      for (int t = lane; t <= WP_WARPS; t += 32) {
+        const int hb = (H + WP_WARPS - 1) / WP_WARPS, bound = t * hb;
         int lo = 0, hi = nl;  // first entry with h >= bound
         while (lo < hi) { int mid = (lo + hi) >> 1; if (act[mid] < bound) lo = mid + 1; else hi = mid; }
-        lists.off[n * WP_OFF + threadIdx.x] = (uint8_t)lo;
+        lists.off[n * WP_OFF + t] = (uint8_t)lo;
       }
-      for (int i = threadIdx.x; i < na && i < WP_LCAP; i += T) {
-        lists.h[n * WP_LCAP + i] = (uint16_t)act[i];
+      for (int i = lane; i < nl; i += 32) {
+        lists.h[n * WP_LCAP + i] = act[i];
         lists.e[n * WP_LCAP + i] = es[act[i]];
       }
-      for (int i = WP_LCAP; i < na; ++i) {
-        int h = act[i];
-        double e = es[h];
-        double *row = Wp + (int64_t)h * D;
-        for (int d = threadIdx.x; d < D; d += T) atomicAdd(row + d, e * (double)Ym[n * D + d]);
-      }
-    } else {
-      for (int i = 0; i < na; ++i) {
-        int h = act[i];
-        double e = es[h];
-        double *row = Wp + (int64_t)h * D;
-        for (int d = threadIdx.x; d < D; d += T) atomicAdd(row + d, e * (double)y[d]);
-      }
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < na; i += T) es[act[i]] = 0.0;
+    for (int i = lists.off ? WP_LCAP : 0; i < na; ++i) {  // not listed: straight to Wp
+      const double e = es[act[i]];
+      double *wrow = Wp + (int64_t)act[i] * D;
+      for (int d = lane; d < D; d += 32) atomicAdd(wrow + d, e * (double)Ym[n * D + d]);
+    }
+    __syncwarp();
+    for (int i = lane; i < na; i += 32) es[act[i]] = 0.0;
+    __syncwarp();
   }
-  sig_acc = group_sum<T>(sig_acc, red_d);
-  if (threadIdx.x == 0) atomicAdd(sig, sig_acc);
+  sig_acc = warp_sum_d(sig_acc);
+  if (lane == 0 && sig_acc != 0.0) atomicAdd(sig, sig_acc);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -528,12 +590,19 @@ extern "C" int evo_bsc_suffstats(const uint32_t *states, const double *lpj, cons
     lists.h = reinterpret_cast<uint16_t *>(p + (size_t)N * WP_LCAP * sizeof(double));
     lists.off = p + (size_t)N * WP_LCAP * (sizeof(double) + sizeof(uint16_t));
   }
-  size_t smem = sizeof(double) * ((size_t)H + S + S_perm) + sizeof(float) * (size_t)D + sizeof(int) * (size_t)H;
-  constexpr int T = 128;
-  auto k = bsc_suffstats_kernel<T>;
+  EVO_REQUIRE(H <= 65535, "H > 65535 not supported by the statistics kernel");
+  const size_t per_warp = suffstats_warp_bytes(H, Hw, S + S_perm);
+  int wpc = (int)((200 * 1024) / per_warp);
+  if (wpc > 8) wpc = 8;
+  if (wpc < 1) {
+    set_error("evo_bsc_suffstats: H = %d needs %zu bytes of shared memory per datapoint", H, per_warp);
+    return EVO_ERR_UNSUPPORTED;
+  }
+  const size_t smem = per_warp * wpc;
+  auto k = bsc_suffstats_kernel;
   if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  k<<<grid_for((const void *)k, T, smem, N), T, smem, (cudaStream_t)stream>>>(states, lpj, Ym, N, D, H, Hw, S, S_perm,
-                                                                              pre1, pil_bar, stats, Es_out, lists);
+  k<<<grid_for((const void *)k, 32 * wpc, smem, (N + wpc - 1) / wpc), 32 * wpc, smem, (cudaStream_t)stream>>>(
+      states, lpj, Ym, N, D, H, Hw, S, S_perm, pre1, pil_bar, stats, Es_out, lists);
   EVO_LAUNCH_CHECK("bsc_suffstats");
   if (lists.off) {
     int n_slices = (D + WP_CW - 1) / WP_CW;

@@ -50,7 +50,9 @@ struct Es3cEval {
   __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(8 + (size_t)4 * max_batch) : 0; }
   static constexpr bool kList = false;
   __host__ __device__ size_t smem_bytes(int T, bool = false) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM + list_bytes(); }
-  __host__ int threads_hint(int work) const { return work < 64 ? 64 : 256; }  // one warp per state: 8 states in flight
+  // measured (cfg3/cfg4, 64 states + 64 children): complete data is fastest with 4 warps and more resident
+  // CTAs, masked data (a D-long Gram gather per system) with 8 warps per datapoint
+  __host__ int threads_hint(int work) const { return work < 64 ? 64 : (masked ? 256 : 128); }
 
   template <int T>
   __device__ void setup(int64_t n, unsigned char *smem) {
