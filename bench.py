@@ -170,6 +170,9 @@ def algorithmic_bytes(w, N, U_mean):
         "evo_bsc_tables_tc": N * (4 * D + 8 * H),
         # (d): read K^n + lpj + y_n, one pass over the outputs
         "evo_bsc_suffstats": N * (K * (4 * Hw + 4) + 4 * D) + 8 * (H * D + H * H),
+        "evo_bsc_suffstats_tc": N * (K * (4 * Hw + 4) + 4 * D) + 8 * (H * D + H * H),
+        # transposed fp16 hi + lo planes of Y: read f32, write 2 x fp16
+        "evo_bsc_wp_tc_set_data": N * D * 8,
         # ES3C (d): as above + mask bits + y_rec write, one pass over the four H x H + H x D outputs
         "evo_es3c_suffstats": N * (K * (4 * Hw + 4) + 4 * D + (D + 7) // 8 + 4 * D) + 8 * (H * D + 4 * H * H),
     }
@@ -277,6 +280,7 @@ def run_ours(args):
         from evo_b200.bsc import BSC
         model = BSC(w["D"], w["H"], w["K"], comm=comm, device=device)
         model.tables = args.tables
+        model.stats = args.stats
     else:
         from evo_b200.sssc import SSSC
         model = SSSC(w["D"], w["H"], w["K"], comm=comm, device=device)
@@ -411,6 +415,8 @@ def run_ours(args):
                    else "working set fits L2 (small reference config)",
                    "tables": ("B = Y W by tcgen05 fp16 hi+lo split GEMM (lpj within 1e-5 of f64)" if args.tables == "tc"
                               else "f64 SIMT GEMM") if w["model"] == "bsc" else "f64",
+                   "statistics": ("Wp = <S>'Y by split-K tcgen05 fp16 hi+lo GEMM (within 1e-5 of max|Wp|), Wq/pi/sigma f64"
+                                  if args.stats == "tc" else "f64") if w["model"] == "bsc" else "f64",
                    "parallelism": "dp%d over N" % world},
         "em_iters_per_sec": args.steps / (ms * 1e-3),
         "lpj_per_step": lpj_total / args.steps, "new_unique_per_datapoint": U_mean, "free_energy": F,
@@ -530,6 +536,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--tables", default="tc", choices=["tc", "f64"],
                     help="BSC table B = Y W: tcgen05 split-precision GEMM (default) or the f64 SIMT GEMM")
+    ap.add_argument("--stats", default="tc", choices=["tc", "f64"],
+                    help="BSC M-step statistic Wp = <S>'Y: split-K tcgen05 GEMM (default) or f64 kernels")
     ap.add_argument("--lpj-compare", action="store_true",
                     help="time the dense tcgen05 log-joint against the sparse Gram kernel (BSC workloads)")
     ap.add_argument("--cpu-worker", type=int, default=-1, help=argparse.SUPPRESS)

@@ -76,6 +76,9 @@ SIGNATURES = {
     "evo_free_energy": (_i, [_vp, _i64, _i, _i64, _vp, _vp]),
     "evo_bsc_suffstats_workspace_bytes": (_i64, [_i64, _i, _i]),
     "evo_bsc_suffstats": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _i64, _vp]),
+    "evo_bsc_wp_tc_workspace_bytes": (_i64, [_i64, _i, _i]),
+    "evo_bsc_wp_tc_set_data": (_i, [_vp, _i64, _i, _i, _vp, _vp]),
+    "evo_bsc_suffstats_tc": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp]),
     "evo_es3c_set_scratch": (_i, [_vp, _i]),
     "evo_es3c_lpj": (_i, [_vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _vp, _i64, _vp, _vp]),
     "evo_es3c_suffstats": (_i, [C.POINTER(Es3cStatsArgs), _vp]),

@@ -18,6 +18,7 @@ class BSC(Model):
         # table B = Y W of the Gram form: "f64" (SIMT GEMM, bit-reproducible parity path) or "tc"
         # (tcgen05 split-precision GEMM, lpj within 1e-5 of the f64 reference)
         self.tables = "f64"
+        self.stats = "f64"  # or "tc": Wp = <S>' Y by the split-precision tensor-core GEMM
 
     # ---- generative model (bsc.py:27-57), cold path ---------------------------------------------
     def generate_from_hidden(self, model_params, my_hdata):
@@ -282,12 +283,27 @@ class BSC(Model):
         else:
             Ym = dd.Y
         stats = torch.zeros(H * D + H * H + H + 1 + ACC_LEN, dtype=torch.float64, device=self.device)
+        S, S_perm = int(ss["ss_dev"].shape[1]), int(ss["S_perm"])
+        if self.stats == "tc":
+            # Wp = <S>' Y on the tensor cores (fp16 hi+lo planes, <= 1e-5 of max|Wp|); Wq, pies, sigma stay f64
+            c = dd.cache
+            if "wp_tc_ws" not in c:
+                nb = int(self.lib.evo_bsc_wp_tc_workspace_bytes(dd.N, D, H))
+                c["wp_tc_ws"] = torch.empty(nb, dtype=torch.uint8, device=self.device)
+                c.pop("wp_tc_valid", None)
+            if dd.incomplete or not c.get("wp_tc_valid"):  # reconstructed data change with every iteration
+                self._call("evo_bsc_wp_tc_set_data", _lib.ptr(Ym), dd.N, D, H, _lib.ptr(c["wp_tc_ws"]))
+                c["wp_tc_valid"] = not dd.incomplete
+            self._call("evo_bsc_suffstats_tc", _lib.ptr(ss["ss_dev"]), _lib.ptr(ss["lpj_dev"]), _lib.ptr(Ym), dd.N, D, H,
+                       S, S_perm, float(model_params["pre1"]), float(model_params["pil_bar"]), _lib.ptr(stats), None,
+                       _lib.ptr(c["wp_tc_ws"]))
+            return stats
         ws = dd.cache.get("stats_ws")
         if ws is None:
             nb = int(self.lib.evo_bsc_suffstats_workspace_bytes(dd.N, D, H))
             ws = dd.cache["stats_ws"] = torch.empty(nb, dtype=torch.uint8, device=self.device) if nb > 0 else False
         self._call("evo_bsc_suffstats", _lib.ptr(ss["ss_dev"]), _lib.ptr(ss["lpj_dev"]), _lib.ptr(Ym), dd.N, D, H,
-                   int(ss["ss_dev"].shape[1]), int(ss["S_perm"]), int(bool(ss["permanent"]["allzero"])),
+                   S, S_perm, int(bool(ss["permanent"]["allzero"])),
                    float(model_params["pre1"]), float(model_params["pil_bar"]), _lib.ptr(stats), None,
                    _lib.ptr(ws) if ws is not False else None, int(ws.numel()) if ws is not False else 0)
         return stats

@@ -2,6 +2,7 @@
 // data estimator.  Reference: evo/models/bsc.py, evo/models/_models.py.
 #include "common.cuh"
 #include "evaluators.cuh"
+#include "stats.cuh"
 
 namespace evo {
 
@@ -133,19 +134,6 @@ constexpr double Q_SKIP = 1e-18;  // posterior mass below f64 resolution of the 
 //   pies += es ; Wp[h,:] += es_h y_n ; Wq[h,h'] += sum_k q_k s_kh s_kh' (h' <= h) ;
 //   sigma += sum_k q_k |y - W s_k|^2 = sum_k q_k (lpj_k - pil_bar |s_k|) / pre1   (same theta)
 // ------------------------------------------------------------------------------------------
-// Sparse <s>_n lists handed from the statistics pass to the Wp pass (bsc_wp_kernel): per datapoint
-// up to WP_LCAP (latent, <s_h>) pairs; entries beyond the capacity are accumulated directly.
-constexpr int WP_LCAP = 64;
-constexpr int WP_CW = 64;  // observables per Wp slice
-constexpr int WP_WARPS = 32;  // warps of the Wp pass; warp w owns the latents [w*hb, (w+1)*hb), hb = ceil(H/32)
-struct WpLists {
-  uint8_t *off;   // [N][WP_WARPS + 1 (+pad to 40)]: the (ascending-h) list of datapoint n restricted to warp w
-                  // is [off[w], off[w+1]); off[WP_WARPS] = number of listed entries
-  uint16_t *h;    // [N][WP_LCAP]
-  double *e;      // [N][WP_LCAP]
-};
-constexpr int WP_OFF = 40;
-
 __device__ __forceinline__ double warp_sum_d(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -290,7 +278,16 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
     if (Es_out)
       for (int h = lane; h < H; h += 32) Es_out[n * H + h] = (float)es[h];
     for (int i = lane; i < na; i += 32) atomicAdd(pies + act[i], es[act[i]]);
-    if (lists.off) {
+    if (lists.et_hi) {
+      // tensor-core Wp: 2^14 <s> as fp16 hi + lo into the transposed planes (zero elsewhere)
+      for (int i = lane; i < na; i += 32) {
+        const int h = act[i];
+        const double v = es[h] * WP_TC_SCALE;
+        const __half hi = __double2half(v);
+        lists.et_hi[(int64_t)h * lists.et_ld + n] = hi;
+        lists.et_lo[(int64_t)h * lists.et_ld + n] = __double2half(v - (double)__half2float(hi));
+      }
+    } else if (lists.off) {
       // hand the sparse <s>_n (ascending h) to the Wp pass; overflow entries are accumulated here
       const int nl = na < WP_LCAP ? na : WP_LCAP;
       for (int t = lane; t <= WP_WARPS; t += 32) {
@@ -304,7 +301,7 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
         lists.e[n * WP_LCAP + i] = es[act[i]];
       }
     }
-    for (int i = lists.off ? WP_LCAP : 0; i < na; ++i) {  // not listed: straight to Wp
+    for (int i = lists.et_hi ? na : (lists.off ? WP_LCAP : 0); i < na; ++i) {  // not listed: straight to Wp
       const double e = es[act[i]];
       double *wrow = Wp + (int64_t)act[i] * D;
       for (int d = lane; d < D; d += 32) atomicAdd(wrow + d, e * (double)Ym[n * D + d]);
@@ -569,6 +566,27 @@ extern "C" int evo_free_energy(const double *lpj, int64_t N, int cols, int64_t l
 static size_t wp_smem(int H) { return 2 * sizeof(WpBatch) + (size_t)H * WP_CW * sizeof(double); }
 static bool wp_lists_applicable(int H) { return wp_smem(H) <= 227 * 1024 && H <= 65535; }
 
+int evo::bsc_suffstats_pass1(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H, int S,
+                             int S_perm, double pre1, double pil_bar, double *stats, float *Es_out, WpLists lists,
+                             cudaStream_t stream) {
+  const int Hw = words_for(H);
+  EVO_REQUIRE(H <= 65535, "H > 65535 not supported by the statistics kernel");
+  const size_t per_warp = suffstats_warp_bytes(H, Hw, S + S_perm);
+  int wpc = (int)((200 * 1024) / per_warp);
+  if (wpc > 8) wpc = 8;
+  if (wpc < 1) {
+    set_error("evo_bsc_suffstats: H = %d needs %zu bytes of shared memory per datapoint", H, per_warp);
+    return EVO_ERR_UNSUPPORTED;
+  }
+  const size_t smem = per_warp * wpc;
+  auto k = bsc_suffstats_kernel;
+  if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k<<<grid_for((const void *)k, 32 * wpc, smem, (N + wpc - 1) / wpc), 32 * wpc, smem, stream>>>(
+      states, lpj, Ym, N, D, H, Hw, S, S_perm, pre1, pil_bar, stats, Es_out, lists);
+  EVO_LAUNCH_CHECK("bsc_suffstats");
+  return EVO_OK;
+}
+
 extern "C" int64_t evo_bsc_suffstats_workspace_bytes(int64_t N, int D, int H) {
   (void)D;
   if (N <= 0 || !wp_lists_applicable(H)) return 0;
@@ -581,8 +599,7 @@ extern "C" int evo_bsc_suffstats(const uint32_t *states, const double *lpj, cons
   (void)allzero;
   EVO_REQUIRE(N >= 0 && D > 0 && H > 0 && S > 0, "bad sizes");
   if (N == 0) return EVO_OK;
-  int Hw = words_for(H);
-  WpLists lists{nullptr, nullptr, nullptr};
+  WpLists lists{};
   if (workspace && wp_lists_applicable(H) && workspace_bytes >= evo_bsc_suffstats_workspace_bytes(N, D, H)) {
     unsigned char *p = reinterpret_cast<unsigned char *>(workspace);
     EVO_REQUIRE(((uintptr_t)p & 15) == 0, "workspace must be 16-byte aligned");
@@ -590,20 +607,9 @@ extern "C" int evo_bsc_suffstats(const uint32_t *states, const double *lpj, cons
     lists.h = reinterpret_cast<uint16_t *>(p + (size_t)N * WP_LCAP * sizeof(double));
     lists.off = p + (size_t)N * WP_LCAP * (sizeof(double) + sizeof(uint16_t));
   }
-  EVO_REQUIRE(H <= 65535, "H > 65535 not supported by the statistics kernel");
-  const size_t per_warp = suffstats_warp_bytes(H, Hw, S + S_perm);
-  int wpc = (int)((200 * 1024) / per_warp);
-  if (wpc > 8) wpc = 8;
-  if (wpc < 1) {
-    set_error("evo_bsc_suffstats: H = %d needs %zu bytes of shared memory per datapoint", H, per_warp);
-    return EVO_ERR_UNSUPPORTED;
-  }
-  const size_t smem = per_warp * wpc;
-  auto k = bsc_suffstats_kernel;
-  if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  k<<<grid_for((const void *)k, 32 * wpc, smem, (N + wpc - 1) / wpc), 32 * wpc, smem, (cudaStream_t)stream>>>(
-      states, lpj, Ym, N, D, H, Hw, S, S_perm, pre1, pil_bar, stats, Es_out, lists);
-  EVO_LAUNCH_CHECK("bsc_suffstats");
+  int rc = bsc_suffstats_pass1(states, lpj, Ym, N, D, H, S, S_perm, pre1, pil_bar, stats, Es_out, lists,
+                               (cudaStream_t)stream);
+  if (rc) return rc;
   if (lists.off) {
     int n_slices = (D + WP_CW - 1) / WP_CW;
     int chunks = sm_count() / n_slices;

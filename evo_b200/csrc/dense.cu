@@ -23,6 +23,7 @@
 #include <cuda_fp16.h>
 
 #include "common.cuh"
+#include "stats.cuh"
 
 namespace evo {
 namespace dense {
@@ -437,13 +438,15 @@ constexpr int T_THREADS = 192;
 constexpr size_t T_SMEM_BYTES = 1024 + (size_t)T_STAGES * T_STAGE_BYTES + 8 * (2 * T_STAGES + 4) + 16;
 
 struct TArgs {
-  int64_t N;
-  int H, KB, n_tiles, box_rows;
-  int64_t a_plane_rows;  // rows of one Y plane (N rounded up to 128)
-  int b_plane_rows;      // rows of one W' plane (n_tiles * box_rows)
+  int64_t N;             // valid output rows (A-operand rows)
+  int H, KB, n_tiles, box_rows;  // valid output columns, k-blocks in all, column tiles, B-operand rows per tile
+  int64_t a_plane_rows;  // rows of one A plane (rounded up to 128)
+  int b_plane_rows;      // rows of one B plane (n_tiles * box_rows)
   int Hp;                // H rounded up to 16
-  const float *descale;  // device scalar 2^-(ey + ew)
-  double *B;
+  int k_chunks, kb_chunk;  // split-K: work item = (row tile, column tile, chunk of kb_chunk k-blocks)
+  int accumulate;        // 0: out = C (k_chunks == 1); 1: out += C by f64 atomics
+  const float *descale;  // device scalar 2^-(ea + eb)
+  double *B;             // output, row stride H
 };
 
 __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_constant__ CUtensorMap tmapA,
@@ -473,16 +476,18 @@ __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int64_t tiles = (a.N + BM - 1) / BM;
+  const int64_t items = ((a.N + BM - 1) / BM) * a.n_tiles * a.k_chunks;
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
       int st = 0;
       uint32_t ph = 0;
       const uint32_t tx = 2u * A_BYTES + 2u * (uint32_t)a.box_rows * 128u;
-      for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x)
-        for (int j = 0; j < a.n_tiles; ++j)
-          for (int kb = 0; kb < a.KB; ++kb) {
+      for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
+        const int64_t tj = it / a.k_chunks;
+        const int64_t t = tj / a.n_tiles;
+        const int j = (int)(tj % a.n_tiles), kb0 = (int)(it % a.k_chunks) * a.kb_chunk, kb1 = min(a.KB, kb0 + a.kb_chunk);
+          for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(EMPTY(st), ph ^ 1u);
             mbar_expect_tx(FULL(st), tx);
             const uint32_t base = smem_u32(sm + (size_t)st * T_STAGE_BYTES);
@@ -492,26 +497,28 @@ __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_c
             tma_load_2d(base + 2 * A_BYTES + B_BYTES, &tmapB, FULL(st), kb * BK, a.b_plane_rows + j * a.box_rows);
             if (++st == T_STAGES) { st = 0; ph ^= 1u; }
           }
+      }
     }
   } else if (warp == 1) {
     if (lane == 0) {  // ===== MMA issuer =====
       int st = 0, ts = 0;
       uint32_t ph = 0, tph = 0;
-      for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x)
-        for (int j = 0; j < a.n_tiles; ++j) {
+      for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
+          const int j = (int)((it / a.k_chunks) % a.n_tiles);
+          const int kb0 = (int)(it % a.k_chunks) * a.kb_chunk, kb1 = min(a.KB, kb0 + a.kb_chunk);
           const int nj = min(BN, a.Hp - j * BN);
           const uint32_t idesc = umma_idesc_f16(nj);
           mbar_wait(T_EMPTY(ts), tph ^ 1u);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + (uint32_t)ts * BN;
-          for (int kb = 0; kb < a.KB; ++kb) {
+          for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(FULL(st), ph);
             tc_fence_after();
             const uint32_t base = smem_u32(sm + (size_t)st * T_STAGE_BYTES);
             const uint64_t ahi = umma_desc_sw128(base), alo = umma_desc_sw128(base + A_BYTES);
             const uint64_t bhi = umma_desc_sw128(base + 2 * A_BYTES), blo = umma_desc_sw128(base + 2 * A_BYTES + B_BYTES);
 #pragma unroll
-            for (int k4 = 0; k4 < BK / 16; ++k4) umma_f16(tmem_d, ahi + 2 * k4, bhi + 2 * k4, idesc, (uint32_t)(kb | k4));
+            for (int k4 = 0; k4 < BK / 16; ++k4) umma_f16(tmem_d, ahi + 2 * k4, bhi + 2 * k4, idesc, (uint32_t)((kb - kb0) | k4));
 #pragma unroll
             for (int k4 = 0; k4 < BK / 16; ++k4) umma_f16(tmem_d, ahi + 2 * k4, blo + 2 * k4, idesc, 1u);
 #pragma unroll
@@ -530,11 +537,14 @@ __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_c
     int ts = 0;
     uint32_t tph = 0;
     const bool vec2 = (a.H & 1) == 0;
-    for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+    for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
+      const int64_t tj = it / a.k_chunks;
+      const int64_t t = tj / a.n_tiles;
+      const int j = (int)(tj % a.n_tiles);
       const int64_t n = t * BM + q * 32 + lane;
       const bool valid = n < a.N;
       double *orow = a.B + (valid ? n : 0) * (int64_t)a.H;
-      for (int j = 0; j < a.n_tiles; ++j) {
+      {
         const int nj = min(BN, a.Hp - j * BN);
         mbar_wait(T_FULL(ts), tph);
         tc_fence_after();
@@ -545,7 +555,13 @@ __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_c
           tmem_ld_wait();
           const int h0 = j * BN + c;
           if (valid) {
-            if (vec2 && h0 + 16 <= a.H) {
+            if (a.accumulate) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const float f = __uint_as_float(v[i]);
+                if (h0 + i < a.H && f != 0.f) atomicAdd(orow + h0 + i, (double)f * (double)descale);
+              }
+            } else if (vec2 && h0 + 16 <= a.H) {
 #pragma unroll
               for (int i = 0; i < 16; i += 2)
                 *reinterpret_cast<double2 *>(orow + h0 + i) =
@@ -667,6 +683,70 @@ static int encode_2d(CUtensorMap *tm, void *base, uint64_t cols, uint64_t rows, 
     return EVO_ERR_CUDA;
   }
   return EVO_OK;
+}
+
+// ---- Wp = <S>' Y on the tensor cores (bsc.py:204-206) ----------------------------------------------
+// C[h][d] = sum_n E'[h][n] Y'[d][n]: M = H (tiles of 128), N = D (tiles of <= 256), K = the datapoints,
+// split into chunks of kb_chunk k-blocks; every work item adds its fp32 tile into the f64 statistics
+// by atomics.  E' = 2^14 <s> (written by the statistics pass), Y' = 2^ey y: fp16 hi + lo planes, K-major.
+// Y (f32 [N][D]) -> transposed planes [2][Dr][Np].  hdr[0] = max|Y| bits; hdr[1] <- 2^-ey; hdr[4] <- 2^-(ey+14)
+__global__ void __launch_bounds__(256) ytsplit_kernel(const float *__restrict__ Y, int64_t N, int D, int64_t Np, int Dr,
+                                                      __half *planes, unsigned int *hdr) {
+  // 32 (d) x 32 (n) tiles through shared memory: reads coalesced along d, writes along n
+  __shared__ float tile[32][33];
+  const int e = scale_exp(__uint_as_float(hdr[0]));
+  const float scale = (float)ldexp(1.0, e);  // power of two: exact in f32
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t n_tiles = Np / 32, total = (int64_t)Dr * Np;
+  const int d_tiles = (Dr + 31) / 32;
+  for (int64_t t = blockIdx.x; t < n_tiles * d_tiles; t += gridDim.x) {
+    const int64_t n0 = (t / d_tiles) * 32;
+    const int d0 = (int)(t % d_tiles) * 32;
+    __syncthreads();
+#pragma unroll
+    for (int r = ty; r < 32; r += 8) {
+      const int64_t n = n0 + r;
+      const int d = d0 + tx;
+      tile[r][tx] = (n < N && d < D) ? Y[n * D + d] * scale : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = ty; r < 32; r += 8) {
+      const int d = d0 + r;
+      if (d < Dr) {
+        __half hi, lo;
+        split_half((double)tile[tx][r], hi, lo);
+        const int64_t i = (int64_t)d * Np + n0 + tx;
+        planes[i] = hi;
+        planes[total + i] = lo;
+      }
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    float *f = reinterpret_cast<float *>(hdr);
+    f[1] = (float)ldexp(1.0, -e);
+    f[4] = (float)ldexp(1.0, -e - 14);
+  }
+}
+
+struct WGeometry {
+  int64_t Np;  // datapoints rounded up to a k-block
+  int KB, Hr, Dp, n_tiles, box_rows, Dr;
+  size_t yt_bytes, et_bytes, total_bytes;
+};
+static WGeometry wgeometry(int64_t N, int D, int H) {
+  WGeometry g;
+  g.Np = (N + BK - 1) / BK * BK;
+  g.KB = (int)(g.Np / BK);
+  g.Hr = (H + BM - 1) / BM * BM;
+  g.Dp = (D + 15) & ~15;
+  g.box_rows = g.Dp < BN ? g.Dp : BN;
+  g.n_tiles = (g.Dp + BN - 1) / BN;
+  g.Dr = g.n_tiles * g.box_rows;
+  g.yt_bytes = ((size_t)2 * g.Dr * g.Np * sizeof(__half) + 255) & ~(size_t)255;
+  g.et_bytes = ((size_t)2 * g.Hr * g.Np * sizeof(__half) + 255) & ~(size_t)255;
+  g.total_bytes = 256 + g.yt_bytes + g.et_bytes;
+  return g;
 }
 
 }  // namespace dense
@@ -792,6 +872,7 @@ extern "C" int evo_bsc_tables_tc(const double *W, int64_t N, int D, int H, void 
   dense::TArgs a;
   a.N = N; a.H = H; a.KB = g.KB; a.n_tiles = g.n_tiles; a.box_rows = g.box_rows;
   a.a_plane_rows = g.Np; a.b_plane_rows = g.b_plane_rows; a.Hp = g.Hp;
+  a.k_chunks = 1; a.kb_chunk = g.KB; a.accumulate = 0;
   a.descale = reinterpret_cast<const float *>(ws) + 4;
   a.B = B;
   static bool attr_set = false;
@@ -800,9 +881,72 @@ extern "C" int evo_bsc_tables_tc(const double *W, int64_t N, int D, int H, void 
                                   (int)dense::T_SMEM_BYTES));
     attr_set = true;
   }
-  int64_t tiles = (N + dense::BM - 1) / dense::BM;
+  int64_t tiles = (N + dense::BM - 1) / dense::BM * g.n_tiles;
   int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   dense::table_gemm_kernel<<<grid, dense::T_THREADS, dense::T_SMEM_BYTES, st>>>(ta, tb, a);
   EVO_LAUNCH_CHECK("table_gemm");
+  return EVO_OK;
+}
+
+extern "C" int64_t evo_bsc_wp_tc_workspace_bytes(int64_t N, int D, int H) {
+  if (N <= 0 || D <= 0 || H <= 0) return 0;
+  return (int64_t)dense::wgeometry(N, D, H).total_bytes;
+}
+
+extern "C" int evo_bsc_wp_tc_set_data(const float *Y, int64_t N, int D, int H, void *workspace, void *stream) {
+  EVO_REQUIRE(Y && workspace && N > 0 && D > 0 && H > 0, "bad arguments");
+  EVO_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  dense::WGeometry g = dense::wgeometry(N, D, H);
+  unsigned int *hdr = reinterpret_cast<unsigned int *>(workspace);
+  __half *yt = reinterpret_cast<__half *>(reinterpret_cast<uint8_t *>(workspace) + 256);
+  EVO_CUDA(cudaMemsetAsync(hdr, 0, 8, st));
+  dense::fmax_kernel<<<grid_1d(N * D), 256, 0, st>>>(Y, N * (int64_t)D, hdr);
+  EVO_LAUNCH_CHECK("fmax");
+  dense::ytsplit_kernel<<<grid_1d((int64_t)g.Dr * g.Np / 4), 256, 0, st>>>(Y, N, D, g.Np, g.Dr, yt, hdr);
+  EVO_LAUNCH_CHECK("ytsplit");
+  return EVO_OK;
+}
+
+extern "C" int evo_bsc_suffstats_tc(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H,
+                                    int S, int S_perm, double pre1, double pil_bar, double *stats, float *Es_out,
+                                    void *workspace, void *stream) {
+  EVO_REQUIRE(states && lpj && stats && workspace && N > 0 && D > 0 && H > 0 && S > 0, "bad arguments");
+  EVO_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  dense::WGeometry g = dense::wgeometry(N, D, H);
+  uint8_t *ws = reinterpret_cast<uint8_t *>(workspace);
+  __half *yt = reinterpret_cast<__half *>(ws + 256);
+  __half *et = reinterpret_cast<__half *>(ws + 256 + g.yt_bytes);
+  EVO_CUDA(cudaMemsetAsync(et, 0, (size_t)2 * g.Hr * g.Np * sizeof(__half), st));
+  WpLists lists{};
+  lists.et_hi = et;
+  lists.et_lo = et + (size_t)g.Hr * g.Np;
+  lists.et_ld = g.Np;
+  int rc = bsc_suffstats_pass1(states, lpj, Ym, N, D, H, S, S_perm, pre1, pil_bar, stats, Es_out, lists, st);
+  if (rc) return rc;
+  CUtensorMap ta, tb;
+  rc = dense::encode_2d(&ta, et, (uint64_t)g.Np, (uint64_t)(2 * g.Hr), (uint32_t)dense::BM);
+  if (rc) return rc;
+  rc = dense::encode_2d(&tb, yt, (uint64_t)g.Np, (uint64_t)(2 * g.Dr), (uint32_t)g.box_rows);
+  if (rc) return rc;
+  const int base_items = (g.Hr / dense::BM) * g.n_tiles;
+  int per = sm_count() / base_items;  // k-chunks that fill the machine once
+  if (per < 1) per = 1;
+  int kb_chunk = (g.KB + per - 1) / per;
+  if (kb_chunk < 8) kb_chunk = 8;     // >= 512 datapoints per item
+  if (kb_chunk > 64) kb_chunk = 64;   // <= 4096 datapoints in one fp32 accumulation
+  dense::TArgs a;
+  a.N = H; a.H = D; a.KB = g.KB; a.n_tiles = g.n_tiles; a.box_rows = g.box_rows;
+  a.a_plane_rows = g.Hr; a.b_plane_rows = g.Dr; a.Hp = g.Dp;
+  a.kb_chunk = kb_chunk; a.k_chunks = (g.KB + kb_chunk - 1) / kb_chunk; a.accumulate = 1;
+  a.descale = reinterpret_cast<const float *>(ws) + 4;
+  a.B = stats;  // Wp [H][D] leads the statistics block
+  EVO_CUDA(cudaFuncSetAttribute(dense::table_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)dense::T_SMEM_BYTES));
+  const int64_t items = (int64_t)base_items * a.k_chunks;
+  int grid = (int)(items < sm_count() ? items : sm_count());
+  dense::table_gemm_kernel<<<grid, dense::T_THREADS, dense::T_SMEM_BYTES, st>>>(ta, tb, a);
+  EVO_LAUNCH_CHECK("wp_gemm");
   return EVO_OK;
 }

@@ -96,6 +96,7 @@ class Model:
         if dd.incomplete:
             dd.Y.copy_(torch.where(dd.mask.bool(), dd.Y, torch.zeros_like(dd.Y)))
         dd.cache.pop("ynorm2", None)
+        dd.cache.pop("wp_tc_valid", None)
         return dd
 
     def stage_data(self, my_data):
@@ -134,6 +135,7 @@ class Model:
         dd.spare_free.record(cur)
         dd.Y, dd.Y_spare = dd.Y_spare, dd.Y
         dd.cache.pop("ynorm2", None)
+        dd.cache.pop("wp_tc_valid", None)
         return dd
 
     def _call(self, name, *args):

@@ -165,6 +165,17 @@ int64_t evo_bsc_suffstats_workspace_bytes(int64_t N, int D, int H);
 int evo_bsc_suffstats(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D,
                       int H, int S, int S_perm, int allzero, double pre1, double pil_bar,
                       double *stats, float *Es_out, void *workspace, int64_t workspace_bytes, void *stream);
+/* The same statistics with Wp = sum_n <s>_n y_n' (bsc.py:204-206) on the tensor cores: the statistics pass
+ * writes 2^14 <s> as fp16 hi + lo into transposed planes, Y' = 2^ey y lives there as hi + lo planes too
+ * (evo_bsc_wp_tc_set_data, once per dataset / per reconstructed Ym), and a split-K tcgen05 GEMM (three
+ * passes hi*hi, hi*lo, lo*hi, fp32 accumulation over <= 4096 datapoints per work item, f64 atomics across
+ * work items) adds into stats.  Wq, pies and sigma are f64 as in evo_bsc_suffstats.
+ * |Wp_tc - Wp_f64| <= 1e-5 max|Wp| (measured <= 2e-6).  Workspace: 256-byte aligned. */
+int64_t evo_bsc_wp_tc_workspace_bytes(int64_t N, int D, int H);
+int evo_bsc_wp_tc_set_data(const float *Ym, int64_t N, int D, int H, void *workspace, void *stream);
+int evo_bsc_suffstats_tc(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H,
+                         int S, int S_perm, double pre1, double pil_bar, double *stats, float *Es_out,
+                         void *workspace, void *stream);
 /* y_rec[n][d] = sum_h <s_h>_n W[d][h] where recon_mask[n][d] == 0 (x false); other entries copy y;
  * rows whose infer_mask is all zero are left untouched (_models.py:646-648). */
 int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double *W, const float *Y,

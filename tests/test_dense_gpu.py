@@ -174,3 +174,70 @@ def test_gram_lpj_from_tc_table(D, H, S, N, act, bound):
     err = np.max(np.abs(got - ref) / np.abs(ref))
     print("gram lpj from tc table, max rel err:", D, H, err)
     assert err < bound, err
+
+
+@pytest.mark.parametrize("D,H,K,N", [(25, 10, 20, 700), (256, 300, 64, 5000), (144, 70, 48, 3001), (1024, 1024, 32, 600), (300, 130, 16, 129)])
+def test_tc_wp_statistics_match_f64_statistics(D, H, K, N):
+    """M-step statistics with Wp = <S>' Y from the split-K tcgen05 GEMM (`evo_bsc_suffstats_tc`) vs the f64
+    path (`evo_bsc_suffstats`) on the same K sets and lpj.  Stated bound: 1e-5 of max|Wp| on Wp (fp16 hi+lo
+    operands, three passes, fp32 accumulation over <= 4096 datapoints, f64 across work items); Wq, pies
+    and sigma come from the same f64 code (equal to summation order)."""
+    import torch
+
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import init_states
+
+    rng = np.random.RandomState(D + H)
+    Wg = rng.normal(size=(D, H)) * 2.0
+    s = rng.random_sample((N, H)) < 3.0 / H
+    Y = (s @ Wg.T + rng.normal(size=(N, D))).astype(np.float32)
+    m = BSC(D, H, K)
+    data = {"y": torch.as_tensor(Y, device=m.device), "x_infr": None}
+    np.random.seed(1)
+    th = m.check_params(m.standard_init(data))
+    cont = init_states(N, K, H, "fit", "randflip", 4, 3, 2, device=m.device, seed=11)
+    m.E_step(th, cont, data)
+    dd = m.device_data(data)
+    out = {}
+    for mode in ("f64", "tc"):
+        m.stats = mode
+        out[mode] = m._stats_enqueue(th, cont, dd).cpu().numpy()
+    m.stats = "f64"
+    nWp = H * D
+    a, b = out["f64"], out["tc"]
+    err = np.abs(a[:nWp] - b[:nWp]).max() / np.abs(a[:nWp]).max()
+    print("tc Wp err / max|Wp|:", D, H, N, err)
+    assert err < 1e-5, err
+    rest = np.abs(a[nWp:] - b[nWp:]).max() / np.abs(a[nWp:]).max()
+    assert rest < 1e-12, rest
+
+
+def test_tc_statistics_em_trajectory_matches_f64():
+    """Three EM iterations with tables and statistics both on the tensor cores vs both f64: F within 1e-5
+    relative, W within 1e-4 of its scale."""
+    import torch
+
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import init_states
+
+    D, H, K, N = 64, 40, 32, 4000
+    rng = np.random.RandomState(3)
+    Wg = rng.normal(size=(D, H)) * 2.0
+    s = rng.random_sample((N, H)) < 3.0 / H
+    Y = (s @ Wg.T + rng.normal(size=(N, D))).astype(np.float32)
+    out = {}
+    for mode in ("f64", "tc"):
+        m = BSC(D, H, K)
+        m.tables = m.stats = mode
+        data = {"y": torch.as_tensor(Y, device=m.device), "x_infr": None}
+        np.random.seed(1)
+        th = m.check_params(m.standard_init(data))
+        cont = init_states(N, K, H, "fit", "randflip", 6, 4, 2, device=m.device, seed=11)
+        Fs = []
+        for _ in range(3):
+            F, _, _, th = m.step(th, cont, data)
+            Fs.append(F)
+        W = th["W"].cpu().numpy() if isinstance(th["W"], torch.Tensor) else np.asarray(th["W"])
+        out[mode] = (np.array(Fs), W)
+    assert np.max(np.abs(out["tc"][0] - out["f64"][0]) / np.abs(out["f64"][0])) < 1e-5, out
+    assert np.max(np.abs(out["tc"][1] - out["f64"][1])) < 1e-4 * np.abs(out["f64"][1]).max()
