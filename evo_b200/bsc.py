@@ -18,7 +18,7 @@ class BSC(Model):
         # table B = Y W of the Gram form: "f64" (SIMT GEMM, bit-reproducible parity path) or "tc"
         # (tcgen05 split-precision GEMM, lpj within 1e-5 of the f64 reference)
         self.tables = "f64"
-        self.stats = "f64"  # or "tc": Wp = <S>' Y by the split-precision tensor-core GEMM
+        self.stats = "f64"  # "tc": Wp = <S>' Y by the split-precision tensor-core GEMM; "auto": tc for H D <= 2^17
 
     # ---- generative model (bsc.py:27-57), cold path ---------------------------------------------
     def generate_from_hidden(self, model_params, my_hdata):
@@ -145,7 +145,7 @@ class BSC(Model):
         return self._estep_finish(red, model_params, my_suff_stat, dd)
 
     def _estep_finish(self, red, model_params, my_suff_stat, dd):
-        r = red.cpu().numpy()
+        r = red.cpu().numpy() if isinstance(red, torch.Tensor) else red
         for i, k in enumerate(("reset_lpj_isnan", "reset_lpj_smaller_eps_lpj", "reset_lpj_isinf")):
             dict.__setitem__(my_suff_stat, k, int(r[3 + i]))
         self.last_counts = {"lpj_evaluated": float(r[6])}
@@ -271,8 +271,11 @@ class BSC(Model):
         stats = self._stats_enqueue(model_params, my_suff_stat, dd)
         stats[-ACC_LEN:] = acc
         self.comm.allreduce_(stats)
-        F, S_nunique, S_sub = self._estep_finish(stats[-ACC_LEN:], model_params, my_suff_stat, dd)
-        return F, S_nunique, S_sub, self._solve_update(model_params, my_suff_stat, dd, stats)
+        # the solve is enqueued before anything is read back: ONE device->host read per EM iteration
+        pend = self._solve_enqueue(model_params, my_suff_stat, dd, stats)
+        host = torch.cat([stats[-ACC_LEN:], pend["scal"]]).cpu().numpy()
+        F, S_nunique, S_sub = self._estep_finish(host[:ACC_LEN], model_params, my_suff_stat, dd)
+        return F, S_nunique, S_sub, self._solve_finish(model_params, my_suff_stat, dd, pend, host[ACC_LEN:])
 
     def _stats_enqueue(self, model_params, my_suff_stat, dd):
         D, H = self.D, self.H
@@ -284,7 +287,12 @@ class BSC(Model):
             Ym = dd.Y
         stats = torch.zeros(H * D + H * H + H + 1 + ACC_LEN, dtype=torch.float64, device=self.device)
         S, S_perm = int(ss["ss_dev"].shape[1]), int(ss["S_perm"])
-        if self.stats == "tc":
+        mode = self.stats
+        if mode == "auto":
+            # measured on B200: the dense split-K GEMM costs ~ N H D, the f64 path ~ the number
+            # of active (datapoint, latent) pairs x D; the GEMM wins for the small H D of cfg2, loses at cfg5
+            mode = "tc" if H * D <= (1 << 17) else "f64"
+        if mode == "tc":
             # Wp = <S>' Y on the tensor cores (fp16 hi+lo planes, <= 1e-5 of max|Wp|); Wq, pies, sigma stay f64
             c = dd.cache
             if "wp_tc_ws" not in c:
@@ -315,39 +323,50 @@ class BSC(Model):
         return self._solve_update(model_params, my_suff_stat, dd, stats)
 
     def _solve_update(self, model_params, my_suff_stat, dd, stats):
+        pend = self._solve_enqueue(model_params, my_suff_stat, dd, stats)
+        return self._solve_finish(model_params, my_suff_stat, dd, pend, pend["scal"].cpu().numpy())
+
+    def _solve_enqueue(self, model_params, my_suff_stat, dd, stats):
+        """Parameter update from the reduced statistics (bsc.py:226-262), enqueued without a host read;
+        `scal` = (cholesky info, solution finite, sum of pies / N, sigma statistic) is read once by the caller."""
         D, H = self.D, self.H
-        ss = my_suff_stat
         Wp = stats[: H * D].view(H, D)
         Wq = stats[H * D: H * D + H * H].view(H, H)
         Wq = torch.tril(Wq) + torch.tril(Wq, -1).T
-        pies = stats[H * D + H * H: H * D + H * H + H]
+        p = stats[H * D + H * H: H * D + H * H + H] / dd.N_total
+        if my_suff_stat["permanent"]["background"]:
+            p[-1] = 1.0 - 1.1e-5
+        pend = {"Wq": Wq, "Wp": Wp, "p": p, "sol": None}
+        flags = torch.ones(2, dtype=torch.float64, device=self.device)
+        if "W" in self.to_learn:
+            # Wq is symmetric PSD: Cholesky on the device; the host falls back to the reference's
+            # minimum-norm lstsq when it is not positive definite (checked in _solve_finish)
+            L, info = torch.linalg.cholesky_ex(Wq)
+            sol = torch.cholesky_solve(Wp, L)
+            pend["sol"] = sol
+            flags = torch.stack([info.to(torch.float64), torch.isfinite(sol).all().to(torch.float64)])
+        pend["scal"] = torch.cat([flags, p.sum().reshape(1), stats[H * D + H * H + H].reshape(1)])
+        return pend
+
+    def _solve_finish(self, model_params, my_suff_stat, dd, pend, scal):
+        D, H = self.D, self.H
         N = dd.N_total
         as_numpy = not isinstance(model_params["W"], torch.Tensor)
         sigma_old = float(model_params["sigma"])
         if "W" in self.to_learn:
-            Wn = self._solve(Wq, Wp)  # (H, D) = lstsq(Wq, Wp)
+            if int(scal[0]) == 0 and scal[1] > 0.5:
+                Wn = pend["sol"]
+            else:
+                Wn = torch.as_tensor(np.linalg.lstsq(pend["Wq"].cpu().numpy(), pend["Wp"].cpu().numpy(), rcond=-1)[0],
+                                     device=self.device)
             model_params["W"] = Wn.T.contiguous().cpu().numpy() if as_numpy else Wn.T.contiguous()
         if "pi" in self.to_learn:
-            p = pies / N
-            if ss["permanent"]["background"]:
-                p[-1] = 1.0 - 1.1e-5
-            model_params["pi"] = float((p.sum() / H).item())
-            model_params["pies"] = p.cpu().numpy() if as_numpy else p
+            model_params["pi"] = float(scal[2] / H)
+            model_params["pies"] = pend["p"].cpu().numpy() if as_numpy else pend["p"]
         if "sigma" in self.to_learn:
-            sig = float(stats[H * D + H * H + H].item())
+            sig = float(scal[3])
             if dd.incomplete:
                 model_params["sigma"] = float(np.sqrt((sig + dd.n_obs_total * sigma_old ** 2) / N / D))
             else:
                 model_params["sigma"] = float(np.sqrt(sig / N / D))
         return model_params
-
-    def _solve(self, Wq, Wp):
-        """lstsq(Wq, Wp) (bsc.py:232-237).  Wq is symmetric PSD: Cholesky on the device when it is
-        positive definite, otherwise the reference's minimum-norm lstsq (rcond=-1) on the host."""
-        L, info = torch.linalg.cholesky_ex(Wq)
-        if int(info.item()) == 0:
-            sol = torch.cholesky_solve(Wp, L)
-            if bool(torch.isfinite(sol).all().item()):
-                return sol
-        sol = np.linalg.lstsq(Wq.cpu().numpy(), Wp.cpu().numpy(), rcond=-1)[0]
-        return torch.as_tensor(sol, device=self.device)

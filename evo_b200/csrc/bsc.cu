@@ -155,6 +155,7 @@ __host__ __device__ inline size_t suffstats_warp_bytes(int H, int Hw, int cols) 
   b += ((size_t)4 * Hw + 7) & ~(size_t)7;             // union words
   b += ((size_t)2 * H + 7) & ~(size_t)7;              // act
   b += (size_t)2 * 32 * SS_LD;                        // per-lane state lists
+  b += ((size_t)2 * cols + 7) & ~(size_t)7;           // live states
   return (b + 15) & ~(size_t)15;
 }
 
@@ -174,6 +175,7 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
   uint16_t *act = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(uni) + (((size_t)4 * Hw + 7) & ~(size_t)7));
   uint16_t *slist = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(act) + (((size_t)2 * H + 7) & ~(size_t)7));
   uint16_t *my_list = slist + lane * SS_LD;
+  uint16_t *lk = slist + 32 * SS_LD;  // [S] states that carry posterior mass (q > Q_SKIP), ascending
   double *Wp = stats, *Wq = stats + (int64_t)H * D, *pies = Wq + (int64_t)H * H, *sig = pies + H;
   double sig_acc = 0.0;
   for (int h = lane; h < H; h += 32) es[h] = 0.0;  // kept zero between datapoints (active entries reset below)
@@ -190,29 +192,36 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
     const double inv = 1.0 / se;
     for (int i = lane; i < cols; i += 32) q[i] *= inv;
     __syncwarp();
-    // ---- per state: sigma (every state), Wq pairs (states that carry mass) --------------------
+    // ---- states that carry posterior mass; the others (q <= 1e-18) are below the f64 resolution of
+    //      every sum they would enter and are not even read ------------------------------------------
     const uint32_t *st = states + n * (int64_t)S * Hw;
+    int nlive = 0;
+    for (int k0 = 0; k0 < S; k0 += 32) {
+      const int k = k0 + lane;
+      const bool f = k < S && q[S_perm + k] > Q_SKIP;
+      const unsigned m = __ballot_sync(0xffffffffu, f);
+      if (f) lk[nlive + __popc(m & ((1u << lane) - 1u))] = (uint16_t)k;
+      nlive += __popc(m);
+    }
+    __syncwarp();
+    // ---- per live state: sigma, Wq pairs -------------------------------------------------------
     double sg = 0.0;
 #pragma unroll 1
-    for (int k = lane; k < S; k += 32) {
+    for (int i0 = lane; i0 < nlive; i0 += 32) {
+      const int k = lk[i0];
       const double qk = q[S_perm + k];
       const uint32_t *sk = st + (int64_t)k * Hw;
-      const bool live = qk > Q_SKIP;
       int a = 0;
       for (int w = 0; w < Hw; ++w) {
         uint32_t m = sk[w];
-        if (live)
-          while (m) {
-            const int bp = __ffs(m) - 1;
-            m &= m - 1;
-            if (a < SS_LS) my_list[a] = (uint16_t)((w << 5) + bp);
-            ++a;
-          }
-        else
-          a += __popc(m);
+        while (m) {
+          const int bp = __ffs(m) - 1;
+          m &= m - 1;
+          if (a < SS_LS) my_list[a] = (uint16_t)((w << 5) + bp);
+          ++a;
+        }
       }
       sg += qk * (row[S_perm + k] - pil_bar * (double)a) / pre1;
-      if (!live) continue;
       if (a <= SS_LS) {
         for (int i = 0; i < a; ++i) {
           double *wrow = Wq + (int64_t)my_list[i] * H;
@@ -243,8 +252,7 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
     // ---- <s>_n over the union of the live states' active latents --------------------------------
     for (int w = lane; w < Hw; w += 32) {
       uint32_t u = 0u;
-      for (int k = 0; k < S; ++k)
-        if (q[S_perm + k] > Q_SKIP) u |= st[(int64_t)k * Hw + w];
+      for (int i = 0; i < nlive; ++i) u |= st[(int64_t)lk[i] * Hw + w];
       uni[w] = u;
     }
     __syncwarp();
@@ -267,9 +275,9 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
     for (int i = lane; i < nu; i += 32) {
       const int h = act[i], w = h >> 5, bit = h & 31;
       double e = 0.0;
-      for (int k = 0; k < S; ++k) {
-        const double qk = q[S_perm + k];
-        if (qk > Q_SKIP && ((st[(int64_t)k * Hw + w] >> bit) & 1u)) e += qk;
+      for (int j = 0; j < nlive; ++j) {
+        const int k = lk[j];
+        if ((st[(int64_t)k * Hw + w] >> bit) & 1u) e += q[S_perm + k];
       }
       es[h] = e;  // > 0: the latent is active in a live state
     }
