@@ -357,6 +357,8 @@ def run_ours(args):
                for k, v in th.items()}
         if not last:
             model.stage_data(hdata)
+            if os.environ.get("EVO_BENCH_E2E_SERIAL"):  # diagnostic: no copy/compute overlap
+                torch.cuda.current_stream().wait_stream(model._copy_stream)
         F, nu, nsub, thd = model.step(thd, cont, hdata, do_reconstruction=recon)
         th = {k: (v.cpu().numpy() if isinstance(v, torch.Tensor) else v) for k, v in thd.items()}
         return th, model.last_counts["lpj_evaluated"]
@@ -376,6 +378,8 @@ def run_ours(args):
         import cProfile
         prof = cProfile.Profile()
         prof.enable()
+    if os.environ.get("EVO_BENCH_E2E_KERNELS"):  # diagnostic: per-call device time inside the e2e loop (stderr)
+        model.timing = []
     for i in range(args.steps):
         th_host, cnt = e2e_step(th_host, i == args.steps - 1)
         e2e_lpj += cnt
@@ -389,6 +393,9 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
     e2e_ms = float(e2e_ms.item())
+    if model.timing is not None:
+        print("e2e kernels:", {k: round(v[1], 3) for k, v in model.timing_summary().items()}, file=sys.stderr)
+        model.timing = None
 
     if rank != 0:
         if world > 1:

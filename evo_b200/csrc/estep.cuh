@@ -674,7 +674,8 @@ static int launch_estep_T(const EstepDev &dv, Eval ev, bool fast, cudaStream_t s
       EstepDev db = dv;
       db.n_list = dv.ovf_list;
       db.ovf_list = nullptr;
-      return launch_estep_variant<Eval, TT, true, false>(db, ev, sm_count(), st);
+      // full persistent grid: the number of overflowed datapoints is only known on the device
+      return launch_estep_variant<Eval, TT, true, false>(db, ev, dv.N, st);
     }
   }
   EstepDev db = dv;
