@@ -16,6 +16,7 @@ from . import variational as V
 from .bsc import lpj_reset_check, posterior  # noqa: F401  (same sanitising rule, _models.py:567-596)
 
 TOL = 1e-5          # sssc.py:40 (noise policy bound)
+EPS_W = 5e-5        # sssc.py:39,44 (noise added to a non-invertible W update)
 EPS_PIES = 5e-5     # sssc.py:39,45
 EPS_MUS = np.finfo(np.float64).eps   # sssc.py:46
 EPS_PSI = 1e-5      # sssc.py:47
@@ -166,7 +167,15 @@ def em_step(theta, container, data, D, H, S, to_learn=("W", "pies", "mus", "sigm
                                sum_s_sz=sum_s_sz, sum_szsz_outer=sum_szsz_outer, trace_masked=trace_masked)
     # ---- parameter updates (sssc.py:688-770)
     if "W" in to_learn:
-        theta["W"] = Wp @ np.linalg.inv(sum_szsz)
+        # sssc.py:692-709: singular second moments -> pinv with rank-one noise -> else W + noise
+        try:
+            theta["W"] = Wp @ np.linalg.inv(sum_szsz)
+        except np.linalg.LinAlgError:
+            try:
+                noise = np.random.normal(0, EPS_W, H)
+                theta["W"] = Wp @ np.linalg.pinv(sum_szsz + np.outer(noise, noise))
+            except np.linalg.LinAlgError:
+                theta["W"] = W + EPS_W * np.random.normal(0, 1, [D, H])
     if "pies" in to_learn:
         p = sum_s / N
         p[p <= EPS_PIES] = EPS_PIES
