@@ -423,7 +423,7 @@ def run_ours(args):
                    "tables": ("B = Y W by tcgen05 fp16 hi+lo split GEMM (lpj within 1e-5 of f64)" if args.tables == "tc"
                               else "f64 SIMT GEMM") if w["model"] == "bsc" else "f64",
                    "statistics": ("Wp = <S>'Y by split-K tcgen05 fp16 hi+lo GEMM (within 1e-5 of max|Wp|), Wq/pi/sigma f64"
-                                  if (args.stats == "tc" or (args.stats == "auto" and w["H"] * w["D"] <= (1 << 17)))
+                                  if args.stats in ("tc", "auto")
                                   else "f64") if w["model"] == "bsc" else "f64",
                    "parallelism": "dp%d over N" % world},
         "em_iters_per_sec": args.steps / (ms * 1e-3),
@@ -545,7 +545,7 @@ def main():
     ap.add_argument("--tables", default="tc", choices=["tc", "f64"],
                     help="BSC table B = Y W: tcgen05 split-precision GEMM (default) or the f64 SIMT GEMM")
     ap.add_argument("--stats", default="auto", choices=["auto", "tc", "f64"],
-                    help="BSC M-step statistic Wp = <S>'Y: split-K tcgen05 GEMM, f64 kernels, or auto (GEMM when H*D <= 2^17)")
+                    help="BSC M-step statistic Wp = <S>'Y: split-K tcgen05 GEMM (tc, = auto) or f64 kernels")
     ap.add_argument("--lpj-compare", action="store_true",
                     help="time the dense tcgen05 log-joint against the sparse Gram kernel (BSC workloads)")
     ap.add_argument("--cpu-worker", type=int, default=-1, help=argparse.SUPPRESS)

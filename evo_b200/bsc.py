@@ -18,7 +18,7 @@ class BSC(Model):
         # table B = Y W of the Gram form: "f64" (SIMT GEMM, bit-reproducible parity path) or "tc"
         # (tcgen05 split-precision GEMM, lpj within 1e-5 of the f64 reference)
         self.tables = "f64"
-        self.stats = "f64"  # "tc": Wp = <S>' Y by the split-precision tensor-core GEMM; "auto": tc for H D <= 2^17
+        self.stats = "f64"  # "tc": Wp = <S>' Y by the split-precision tensor-core GEMM; "auto": tc
 
     # ---- generative model (bsc.py:27-57), cold path ---------------------------------------------
     def generate_from_hidden(self, model_params, my_hdata):
@@ -289,9 +289,10 @@ class BSC(Model):
         S, S_perm = int(ss["ss_dev"].shape[1]), int(ss["S_perm"])
         mode = self.stats
         if mode == "auto":
-            # measured on B200: the dense split-K GEMM costs ~ N H D, the f64 path ~ the number
-            # of active (datapoint, latent) pairs x D; the GEMM wins for the small H D of cfg2, loses at cfg5
-            mode = "tc" if H * D <= (1 << 17) else "f64"
+            # measured on B200: the f64 path costs ~ (active latents per datapoint) x D atomics
+            # and swings 20x with the posterior's spread (cfg5, N = 1M: 69 ms); the GEMM is bounded by
+            # N H D (22 ms there, 1.0 vs 2.0 ms at cfg2)
+            mode = "tc"
         if mode == "tc":
             # Wp = <S>' Y on the tensor cores (fp16 hi+lo planes, <= 1e-5 of max|Wp|); Wq, pies, sigma stay f64
             c = dd.cache
