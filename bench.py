@@ -243,11 +243,17 @@ def run_lpj_compare(args):
     print(json.dumps(line), flush=True)
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` captures of exactly the
-# default command (profiles/r01e_cfg2_full_ncu_summary.txt); None where no capture at that size exists.
-NCU_TRAFFIC = {("cfg2", 100000): {"evo_estep": 498.436352e6 + 96.002304e6,
-                                  "evo_bsc_suffstats": 316.745216e6 + 52.972288e6 + 171.225088e6 + 7.877376e6,
-                                  "evo_bsc_tables_tc": 104.104704e6 + 186.958336e6}}
+# dram__bytes_read.sum + dram__bytes_write.sum per call from the `ncu --set full` capture of exactly the
+# default command (profiles/r01g_cfg2_full_ncu_summary.txt; a call = all its kernels); None where no
+# capture at that size exists.
+NCU_TRAFFIC = {("cfg2", 100000): {
+    # list kernel + packed-bits pass over the overflow list
+    "evo_estep": 497.345280e6 + 93.370880e6 + 0.060672e6,
+    # statistics pass + split-K Wp GEMM (the memset of the <s> planes, 154 MB, is not a kernel)
+    "evo_bsc_suffstats_tc": 413.756672e6 + 141.957888e6 + 260.738560e6 + 6.116864e6,
+    # wmax + W' split + table GEMM
+    "evo_bsc_tables_tc": 0.620288e6 + 0.629760e6 + 167.747072e6 + 188.397568e6,
+    "evo_bsc_prepare": 0.621568e6}}
 
 
 def measured_peaks():

@@ -218,6 +218,20 @@ typedef struct evo_es3c_stats_args {
 } evo_es3c_stats_args;
 int evo_es3c_suffstats(const evo_es3c_stats_args *args, void *stream);
 
+/* ---- overlapping-patch pipeline of the image drivers (tvutil.prepost OverlappingPatches /
+ *      MultiDimOverlappingPatches .get / .set_and_merge with mean_merger / median_merger; call sites
+ *      examples/image-denoising/main.py:85-88,169-177, examples/image-inpainting/main.py:86-88,174-182) ----
+ * image f32 [C][Hi][Wi]; patches f32 [N][D], D = C*ph*pw (channel, patch row, patch column), N = ny*nx
+ * top-left positions (multiples of shift that fit), row-major.  merge method: 0 = nan-mean, 1 = nan-median
+ * over the estimates of all patches covering a pixel (<= 256 per pixel for the median); uncovered = NaN. */
+int64_t evo_patches_count(int Hi, int Wi, int ph, int pw, int shift);
+int evo_patches_extract(const float *image, int C, int Hi, int Wi, int ph, int pw, int shift, float *patches,
+                        void *stream);
+int evo_patches_merge(const float *patches, int C, int Hi, int Wi, int ph, int pw, int shift, int method,
+                      float *image, void *stream);
+/* *out += sum_i (a_i - b_i)^2 in f64 (PSNR = 10 log10(R^2 n / sum), examples/image-denoising/utils.py:8-18) */
+int evo_sum_sqdiff(const float *a, const float *b, int64_t n, double *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
