@@ -178,6 +178,49 @@ def algorithmic_bytes(w, N, U_mean):
     }
 
 
+def run_patches(args):
+    """the overlapping-patch kernels either side of the ES3C path in the denoising driver
+    (12 x 12 patches, shift 1), each call alone between CUDA events, against the HBM roofline: extract
+    writes N*D*4 bytes, merge reads them.  One JSON line; not the headline metric."""
+    import torch
+
+    from evo_b200.patches import OverlappingPatches, mean_merger, median_merger
+
+    torch.cuda.set_device(0)
+    side, ph = (args.n if args.n else 2048), 12
+    g = torch.Generator(device="cuda")
+    g.manual_seed(0)
+    img = torch.rand((side, side), generator=g, device="cuda") * 255
+    ovp = OverlappingPatches(img, ph, ph, patch_shift=1)
+    nbytes = ovp.N * ovp.D * 4
+    peak, src = measured_peaks()
+
+    def timed(fn):
+        for _ in range(max(args.warmup, 3)):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(args.steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / args.steps
+
+    def extract():
+        ovp._patches = None
+        ovp.get()
+
+    res = {}
+    for name, fn in (("extract", extract), ("merge_mean", lambda: ovp.merge(mean_merger)),
+                     ("merge_median", lambda: ovp.merge(median_merger))):
+        ms = timed(fn)
+        res[name] = {"ms": ms, "GB/s": nbytes / ms * 1e-6, "frac": nbytes / ms * 1e-6 / peak}
+    print(json.dumps({"metric": "patch_pipeline", "image": [side, side], "patch": [ph, ph], "shift": 1, "patches": ovp.N,
+                      "D": ovp.D, "algorithmic_bytes": nbytes, "peak_GB/s": peak, "peak_source": src,
+                      "l2": "patch matrix larger than L2" if nbytes > 126e6 else "fits L2", "kernels": res}), flush=True)
+
+
 def run_lpj_compare(args):
     """north_star (a): the dense tcgen05 log-joint (evo_bsc_lpj_gemm) timed against the sparse
     Gram/popc kernel (evo_bsc_lpj) on the SAME evolved K sets of a BSC workload, each call alone
@@ -554,6 +597,8 @@ def main():
                     help="BSC M-step statistic Wp = <S>'Y: split-K tcgen05 GEMM (tc, = auto) or f64 kernels")
     ap.add_argument("--lpj-compare", action="store_true",
                     help="time the dense tcgen05 log-joint against the sparse Gram kernel (BSC workloads)")
+    ap.add_argument("--patches", action="store_true",
+                    help="time the overlapping-patch kernels (SURVEY 8f row 1) against the HBM roofline; --n = image side")
     ap.add_argument("--cpu-worker", type=int, default=-1, help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.cpu_worker >= 0:
@@ -562,6 +607,8 @@ def main():
         return run_reference(args)
     if args.lpj_compare:
         return run_lpj_compare(args)
+    if args.patches:
+        return run_patches(args)
     return run_ours(args)
 
 

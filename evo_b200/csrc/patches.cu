@@ -21,15 +21,23 @@ struct PatchGeom {
   int C, Hi, Wi, ph, pw, shift, ny, nx, D;
 };
 
+// one warp per patch: the D image offsets of a patch's elements are tabulated once per CTA in shared
+// memory, so the inner loop is one table read, one image read (L2-resident) and one coalesced store
 __global__ void __launch_bounds__(256) patches_extract_kernel(const float *__restrict__ img, PatchGeom g,
                                                               float *__restrict__ out) {
-  const int64_t total = (int64_t)g.ny * g.nx * g.D;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int d = (int)(i % g.D);
-    const int64_t p = i / g.D;
-    const int px = (int)(p % g.nx) * g.shift, py = (int)(p / g.nx) * g.shift;
+  extern __shared__ int off[];  // [D]
+  for (int d = threadIdx.x; d < g.D; d += blockDim.x) {
     const int c = d / (g.ph * g.pw), r = (d / g.pw) % g.ph, q = d % g.pw;
-    out[i] = __ldg(img + ((int64_t)c * g.Hi + py + r) * g.Wi + px + q);
+    off[d] = (c * g.Hi + r) * g.Wi + q;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t N = (int64_t)g.ny * g.nx, warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t p = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; p < N; p += warps) {
+    const int ky = (int)(p / g.nx), kx = (int)(p - (int64_t)ky * g.nx);
+    const float *src = img + (int64_t)ky * g.shift * g.Wi + kx * g.shift;
+    float *dst = out + p * g.D;
+    for (int d = lane; d < g.D; d += 32) dst[d] = __ldg(src + off[d]);
   }
 }
 
@@ -62,7 +70,7 @@ __global__ void __launch_bounds__(256) patches_merge_mean_kernel(const float *__
 }
 
 // one warp per pixel: the estimates are spread over the lanes (<= PM_MAX per lane), the median is found by
-// rank counting on (value, position) pairs through shuffles -- no sorting, no local arrays
+// radix selection on order-preserving keys (one warp reduction per bit) -- no sorting, no local arrays
 constexpr int PM_MAX = 8;  // estimates per lane: up to 256 covering patches per pixel (16x16 patches at shift 1)
 __global__ void __launch_bounds__(256) patches_merge_median_kernel(const float *__restrict__ pat, PatchGeom g,
                                                                    float *__restrict__ img) {
@@ -92,29 +100,38 @@ __global__ void __launch_bounds__(256) patches_merge_median_kernel(const float *
         v[t] = __ldg(pat + ((int64_t)ky * g.nx + kx) * g.D + ((int64_t)c * g.ph + r) * g.pw + q);
       }
     }
-    // ranks (cnt-1)/2 and cnt/2 of the order (value, position)
-    const int lo_rank = (cnt - 1) >> 1, hi_rank = cnt >> 1;
-    float m_lo = 0.f, m_hi = 0.f;
+    // order-preserving keys; lanes past the count hold the largest key and never rank
+    uint32_t key[PM_MAX];
 #pragma unroll
     for (int t = 0; t < PM_MAX; ++t) {
-      if (t >= per) break;
-      for (int src = 0; src < 32; ++src) {
-        const int e = t * 32 + src;
-        if (e >= cnt) break;  // uniform across the warp
-        const float cand = __shfl_sync(0xffffffffu, v[t], src);
-        int less = 0;
-#pragma unroll
-        for (int u = 0; u < PM_MAX; ++u) {
-          if (u >= per) break;
-          const int f = u * 32 + lane;
-          if (f < cnt) less += (v[u] < cand) || (v[u] == cand && f < e);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) less += __shfl_xor_sync(0xffffffffu, less, o);
-        if (less == lo_rank) m_lo = cand;
-        if (less == hi_rank) m_hi = cand;
-      }
+      const uint32_t b = __float_as_uint(v[t]);
+      key[t] = (t * 32 + lane < cnt) ? ((b & 0x80000000u) ? ~b : (b | 0x80000000u)) : 0xFFFFFFFFu;
     }
+    // lower median = element of rank (cnt-1)/2 by MSB-first radix selection (32 passes, one warp reduction each)
+    uint32_t prefix = 0u;
+    int k = (cnt - 1) >> 1;
+    for (int bit = 31; bit >= 0; --bit) {
+      int c0 = 0;  // keys that match the prefix above `bit` and have this bit clear
+#pragma unroll
+      for (int t = 0; t < PM_MAX; ++t)
+        if (t < per) c0 += (((key[t] ^ prefix) >> bit) == 0u) && (t * 32 + lane < cnt);
+      c0 = __reduce_add_sync(0xffffffffu, c0);
+      if (k >= c0) { k -= c0; prefix |= 1u << bit; }
+    }
+    // upper median (even count): the same value if enough copies of it reach rank cnt/2, else the next larger key
+    int le = 0;
+    uint32_t nxt = 0xFFFFFFFFu;
+#pragma unroll
+    for (int t = 0; t < PM_MAX; ++t)
+      if (t < per && t * 32 + lane < cnt) {
+        le += key[t] <= prefix;
+        if (key[t] > prefix) nxt = min(nxt, key[t]);
+      }
+    le = __reduce_add_sync(0xffffffffu, le);
+    nxt = __reduce_min_sync(0xffffffffu, nxt);
+    const uint32_t hi_key = ((cnt >> 1) < le) ? prefix : nxt;
+    auto unkey = [](uint32_t x) { return __uint_as_float((x & 0x80000000u) ? (x & 0x7FFFFFFFu) : ~x); };
+    const float m_lo = unkey(prefix), m_hi = unkey(hi_key);
     if (lane == 0) img[i] = (m_lo + m_hi) * 0.5f;
   }
 }
@@ -163,7 +180,11 @@ extern "C" int evo_patches_extract(const float *image, int C, int Hi, int Wi, in
   int rc = patch_geom(C, Hi, Wi, ph, pw, shift, g);
   if (rc) return rc;
   const int64_t total = (int64_t)g.ny * g.nx * g.D;
-  patches_extract_kernel<<<grid_for_items(total), 256, 0, (cudaStream_t)stream>>>(image, g, patches);
+  if ((size_t)g.D * sizeof(int) > 48 * 1024) {
+    set_error("patches: D = %d elements per patch not supported (offset table > 48 KB)", g.D);
+    return EVO_ERR_UNSUPPORTED;
+  }
+  patches_extract_kernel<<<grid_for_items(total / 4 + 1), 256, (size_t)g.D * sizeof(int), (cudaStream_t)stream>>>(image, g, patches);
   EVO_LAUNCH_CHECK("patches_extract");
   return EVO_OK;
 }
