@@ -241,3 +241,38 @@ def test_tc_statistics_em_trajectory_matches_f64():
         out[mode] = (np.array(Fs), W)
     assert np.max(np.abs(out["tc"][0] - out["f64"][0]) / np.abs(out["f64"][0])) < 1e-5, out
     assert np.max(np.abs(out["tc"][1] - out["f64"][1])) < 1e-4 * np.abs(out["f64"][1]).max()
+
+
+def test_tc_statistics_with_missing_data_match_f64():
+    """Incomplete data: the M-step sums over the reconstructed y, which changes with every iteration, so the
+    transposed Y planes of the tensor-core Wp are rebuilt per call (`evo_bsc_wp_tc_set_data`).  Three EM
+    iterations with reconstruction, statistics tc vs f64 (tables stay f64: the direct evaluator is used)."""
+    import torch
+
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import init_states
+
+    D, H, K, N = 48, 30, 24, 3000
+    rng = np.random.RandomState(5)
+    Wg = rng.normal(size=(D, H)) * 2.0
+    s = rng.random_sample((N, H)) < 3.0 / H
+    Y = (s @ Wg.T + rng.normal(size=(N, D))).astype(np.float32)
+    X = rng.random_sample((N, D)) >= 0.25
+    out = {}
+    for mode in ("f64", "tc"):
+        m = BSC(D, H, K)
+        m.stats = mode
+        data = {"y": torch.as_tensor(Y, device=m.device), "x_infr": torch.as_tensor(X, device=m.device),
+                "x": torch.as_tensor(X, device=m.device)}
+        np.random.seed(1)
+        th = m.check_params(m.standard_init(data))
+        cont = init_states(N, K, H, "fit", "randflip", 6, 4, 2, device=m.device, seed=11)
+        Fs = []
+        for _ in range(3):
+            F, _, _, th = m.step(th, cont, data, do_reconstruction=True)
+            Fs.append(F)
+        W = th["W"].cpu().numpy() if isinstance(th["W"], torch.Tensor) else np.asarray(th["W"])
+        out[mode] = (np.array(Fs), W, float(th["sigma"]))
+    assert np.max(np.abs(out["tc"][0] - out["f64"][0]) / np.abs(out["f64"][0])) < 1e-5, out
+    assert np.max(np.abs(out["tc"][1] - out["f64"][1])) < 1e-4 * np.abs(out["f64"][1]).max()
+    assert abs(out["tc"][2] - out["f64"][2]) < 1e-5 * out["f64"][2]
