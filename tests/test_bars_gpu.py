@@ -8,9 +8,11 @@ counters, so trajectories agree in distribution, not draw for draw (draw-for-dra
 tests/test_bsc_gpu.py with injected candidates).  What is compared, with the tolerance beside it:
   * epoch 1 free energy (depends on the initial K sets only)       within 0.1 of the reference's (its own
     spread over four operator seeds: 0.012)
-  * the optimum: the reference reaches F = L = -40.1999 on two of four seeds and stalls in a local optimum
-    on the others (no annealing in the example); the CUDA path must reach that value within 2e-3 on at
-    least one of 12 seeds, with pi / sigma within 1 % and the bars dictionary within 0.05 max-abs (up to a
+  * the optimum: the reference reaches F = L = -40.1999 on 8 of 12 seeds and stalls in a local optimum
+    (F between -55.4 and -64.2) on the others -- the example has no annealing; the CUDA path reaches it on
+    46 of 64 seeds and stalls at -55.4 .. -57.7 on the others (profiles/r01h_bars_seeds.log; the two
+    rates agree, Fisher exact p = 0.74).  Asserted: that value within 2e-3 on at least one of 12 seeds,
+    none above it, with pi / sigma within 1 % and the bars dictionary within 0.05 max-abs (up to a
     column permutation) of the reference's converged parameters
   * every run: F(K sets) <= exact log-likelihood L(theta) (free_energy(full=True)) + 1e-9, F finite, and F
     of the last epoch above F of the first by at least 5 nats (every reference seed gains >= 14)
@@ -120,3 +122,44 @@ def test_train_resumes_from_its_checkpoint(tmp_path):
     _, rest = eem.train(BSC(D, H, K), th2, cont2, data, 8, start_epoch=int(extra["epoch"]))
     # f64 atomics in the statistics pass make two runs differ in the last bits (2e-16 relative observed)
     assert np.allclose(first["F"] + rest["F"], full["F"], rtol=1e-10, atol=0.0)
+
+
+def test_es3c_bars_free_run_tracks_the_reference(tmp_path):
+    """`--algo es3c` of the example (W, pies, sigma2, mus, Psi all learned), same protocol.  The reference's
+    three free runs are still climbing at epoch 40 (final F -46.95 / -47.94 / -47.13, spread over seeds
+    <= 2.9 nats at every epoch), so the trajectory itself is compared.  Sixteen CUDA runs
+    (profiles/r01h_bars_seeds.log) end between -46.4 and -49.8 and run up to 4.3 nats ahead of / behind the
+    reference's mean in the steep part (epochs 8-16), hence: every CUDA run within 6 nats of the reference's
+    mean trajectory at every epoch and within 3 nats at the last, the median final F within 1 nat of the
+    reference's mean final F, epoch 1 within 0.1 (the reference's spread there: 0.0125), F <= L(theta) + 1e-9."""
+    from evo_b200 import eem
+    from evo_b200.sssc import SSSC
+    from evo_b200.variational import init_states
+
+    z = np.load(os.path.join(P.GOLDEN, "sssc_bars_free.npz"))
+    Y = z["Y"].astype(np.float64)
+    N, D = Y.shape
+    H, K = z["W0"].shape[1], int(z["K"])
+    n_par, n_chi, n_gen = (int(v) for v in z["ea"])
+    F_ref = z["F_ref"]
+    epochs = F_ref.shape[1]
+    mean_ref = F_ref.mean(0)
+    model = SSSC(D, H, K)
+    data = {"y": Y, "x_infr": np.ones_like(Y, dtype=bool)}
+    finals = []
+    for seed in range(6):
+        theta = model.check_params({"W": z["W0"].copy(), "pies": z["pies0"].copy(), "sigma2": np.float64(z["sigma20"]),
+                                    "mus": z["mus0"].copy(), "Psi": z["Psi0"].copy()})
+        cont = init_states(N, K, H, "fit", "randflip", n_par, n_chi, n_gen, device=model.device, seed=2000 + seed)
+        theta, hist = eem.train(model, theta, cont, data, epochs)
+        F = np.asarray(hist["F"], dtype=np.float64)
+        assert np.isfinite(F).all()
+        assert abs(F[0] - mean_ref[0]) < 0.1, (seed, F[0], F_ref[:, 0])
+        dev = np.abs(F - mean_ref)
+        assert dev.max() < 6.0 and dev[-1] < 3.0, (seed, int(dev.argmax()), float(dev.max()), float(dev[-1]))
+        L = model.free_energy(data, dict(theta), cont, full=True)
+        F_now = model.free_energy(data, dict(theta), cont, full=False)
+        assert F_now <= L + 1e-9, (seed, F_now, L)
+        finals.append(F[-1])
+    print("ES3C final F per seed:", np.round(finals, 4), "reference:", np.round(F_ref[:, -1], 4))
+    assert abs(np.median(finals) - mean_ref[-1]) < 1.0, (finals, F_ref[:, -1])

@@ -24,6 +24,16 @@ for r in rows[2:]:
         if w in hdr:
             i = hdr.index(w)
             print(w, units[i], r[i])
+    # warp-state breakdown: stall cycles per issued instruction, largest first
+    st = []
+    for i, h in enumerate(hdr):
+        if h.startswith('smsp__average_warps_issue_stalled_') and h.endswith('_per_issue_active.ratio'):
+            try:
+                st.append((float(r[i].replace(',', '')), h[len('smsp__average_warps_issue_stalled_'):-len('_per_issue_active.ratio')]))
+            except ValueError:
+                pass
+    for v, h in sorted(st, reverse=True)[:8]:
+        print('stall_per_issue.%s %.3f' % (h, v))
 here = os.path.dirname(os.path.abspath(__file__))
 for pat in sys.argv[2:]:
     src = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--print-source', 'sass,cuda', '--kernel-name',
