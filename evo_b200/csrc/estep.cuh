@@ -48,7 +48,8 @@ struct EstepSmem {
   uint32_t *st_uniq;   // [(S + Ctot)][Hs]
   uint32_t *st_child;  // [Cg][Hs]
   double *lpj_uniq;    // [S + Ctot]
-  double *keys;        // [PK]
+  double *keys;        // [PK] order keys of the parent-selection pool
+  double *vkeys;       // [Ctot + S] order keys of vary_Kn (aliases st_child / table)
   double *red_d;       // [8]
   int *table;          // [HT]
   int *pool;           // [PK]
@@ -75,18 +76,28 @@ __host__ __device__ inline size_t estep_carve(const EstepDev &a, unsigned char *
     off = align16(off + sizeof(type) * (size_t)(count));          \
   } while (0)
   CARVE(lpj_uniq, double, U);
-  CARVE(keys, double, U + 2);  // order keys: selection pool [PK] / new [Ctot] then old [S]
+  CARVE(keys, double, a.PK + 2);  // order keys of the selection pool
   CARVE(red_d, double, 8);
   CARVE(st_uniq, uint32_t, U * a.Hs);
-  CARVE(st_child, uint32_t, (size_t)a.Cg * a.Hs);
-  CARVE(table, int, a.HT);
+  // Two phases share one region: the generations need the children and the hash table, the top-K
+  // replacement afterwards (vary_Kn) needs order keys of the new and the old states and their ranks --
+  // nothing of the first set is read once the generation loop has ended.
+  {
+    const size_t base_off = off;
+    CARVE(st_child, uint32_t, (size_t)a.Cg * a.Hs);
+    CARVE(table, int, a.HT);
+    const size_t end_gen = off;
+    off = base_off;
+    CARVE(vkeys, double, (size_t)((a.Ctot + 1) & ~1) + a.S + 2);  // new [Ctot] then old [S]
+    CARVE(rnk, int, a.Ctot > 0 ? a.Ctot : 1);
+    CARVE(old_by_rank, int, a.S);
+    if (off < end_gen) off = end_gen;
+  }
   CARVE(pool, int, a.PK);
   CARVE(slot, int, a.Cg > 0 ? a.Cg : 1);
   CARVE(parents, int, a.n_parents > 0 ? a.n_parents : 1);
   CARVE(red_i, int, 8);
   CARVE(sh, int, 8);
-  CARVE(rnk, int, a.Ctot > 0 ? a.Ctot : 1);
-  CARVE(old_by_rank, int, a.S);
   CARVE(redisc, unsigned char, U);
   CARVE(status, unsigned char, a.Cg > 0 ? a.Cg : 1);
 #undef CARVE
@@ -567,7 +578,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         mn = -group_max<T>(-mn, s.red_d);
         // only candidates above the worst old state can ever be accepted
         const double *ln = s.lpj_uniq + S;
-        double *kn = s.keys, *ko = s.keys + ((a.Ctot + 1) & ~1);
+        double *kn = s.vkeys, *ko = s.vkeys + ((a.Ctot + 1) & ~1);
         _Pragma("unroll 1") for (int i = tid; i < U; i += T) kn[i] = order_key(ln[i], (uint32_t)i, a.mask_c, true);
         _Pragma("unroll 1") for (int k = tid; k < S; k += T) ko[k] = order_key(s.lpj_uniq[k], (uint32_t)k, a.mask_s, false);
         gsync<T>();
