@@ -351,7 +351,8 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       }
       _Pragma("unroll 1") for (int i = tid; i < a.HT; i += T) s.table[i] = TAG_EMPTY;
       _Pragma("unroll 1") for (int i = tid; i < S + a.Ctot; i += T) s.redisc[i] = 0;
-      ev.template setup<T>(n, s.eval_smem);
+      if constexpr (LIST) ev.template setup<T, true>(n, s.eval_smem);
+      else ev.template setup<T>(n, s.eval_smem);
     }
     gsync<T>();
     if (LIST && s.sh[0]) {  // a state of K^n has more than LIST_CAP active latents: not for this kernel

@@ -21,24 +21,29 @@ struct BscGramEval {
   double pre1, pil_bar;
   int H, Hw;
   // per datapoint (set in setup)
-  double *b;       // smem [H]
+  double *b;       // smem [H] (packed-bits forms)
   uint16_t *idx;   // smem [MAXA][T] active-latent lists, one column per thread
   double yn2;
+  const double *bg;  // this datapoint's row of B in global memory (the list form reads it through L1/L2)
   static constexpr int MAXA = 24;
   static constexpr bool kList = true;  // can evaluate index-list rows (estep.cuh LIST representation)
 
   __host__ __device__ size_t smem_bytes(int T, bool list = false) const {
-    return (size_t)H * sizeof(double) + (list ? 0 : (size_t)MAXA * T * sizeof(uint16_t));
+    // list form: no staging at all -- a state touches |s| entries of the row, and the shared memory
+    // it would take (8 KB at H = 1024) costs a resident CTA per SM
+    return list ? 0 : (size_t)H * sizeof(double) + (size_t)MAXA * T * sizeof(uint16_t);
   }
   __host__ int threads_hint(int work) const { return work <= 32 ? 32 : (work <= 64 ? 64 : 128); }
 
-  template <int T>
+  template <int T, bool LIST = false>
   __device__ void setup(int64_t n, unsigned char *smem) {
+    const double *src = B + n * (int64_t)H;
+    bg = src;
+    yn2 = __ldg(ynorm2 + n);
+    if (LIST) return;
     b = reinterpret_cast<double *>(smem);
     idx = reinterpret_cast<uint16_t *>(smem + (size_t)H * sizeof(double));
-    const double *src = B + n * (int64_t)H;
     for (int i = threadIdx.x; i < H; i += T) b[i] = __ldg(src + i);
-    yn2 = __ldg(ynorm2 + n);
   }
 
   // pre1 (|y|^2 - 2 sum b + sum G) + pil_bar |s| with the contraction spelled out, so that every
@@ -111,7 +116,7 @@ struct BscGramEval {
     double sb = 0.0, sg = 0.0;
     for (int i = 0; i < a; ++i) {
       const int h = e[i];
-      sb += b[h];
+      sb += __ldg(bg + h);
       const double *Gr = G + (int64_t)h * H;
       double t = 0.0;
 #pragma unroll 4
