@@ -58,8 +58,9 @@ struct EstepSmem {
   int *red_i;          // [8]
   int *sh;             // [8] shared scalars
   unsigned char *redisc;  // [S + Ctot]
-  int *rnk;               // [Ctot] rank of each new state among the new ones (by lpj, descending)
+  int *rnk;               // [Ctot] rank of each eligible new state among the new ones (by lpj, descending)
   int *old_by_rank;       // [S] slot of the r-th worst old state
+  int *eidx;              // [Ctot] indices of the new states that beat the worst old one (compacted)
   unsigned char *status;  // [Cg]
   unsigned char *eval_smem;
 };
@@ -91,6 +92,7 @@ __host__ __device__ inline size_t estep_carve(const EstepDev &a, unsigned char *
     CARVE(vkeys, double, (size_t)((a.Ctot + 1) & ~1) + a.S + 2);  // new [Ctot] then old [S]
     CARVE(rnk, int, a.Ctot > 0 ? a.Ctot : 1);
     CARVE(old_by_rank, int, a.S);
+    CARVE(eidx, int, a.Ctot > 0 ? a.Ctot : 1);
     if (off < end_gen) off = end_gen;
   }
   CARVE(pool, int, a.PK);
@@ -577,39 +579,55 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         double mn = DBL_MAX;
         _Pragma("unroll 1") for (int i = tid; i < S; i += T) mn = fmin(mn, s.lpj_uniq[i]);
         mn = -group_max<T>(-mn, s.red_d);
-        // only candidates above the worst old state can ever be accepted
+        // Only candidates above the worst old state can ever be accepted.  They are compacted (in index
+        // order) and ranked among themselves: every other candidate is smaller than all of them, so the
+        // ranks are those of the full list at E^2 instead of U^2 compares -- late in training E is a few.
         const double *ln = s.lpj_uniq + S;
         double *kn = s.vkeys, *ko = s.vkeys + ((a.Ctot + 1) & ~1);
-        _Pragma("unroll 1") for (int i = tid; i < U; i += T) kn[i] = order_key(ln[i], (uint32_t)i, a.mask_c, true);
-        _Pragma("unroll 1") for (int k = tid; k < S; k += T) ko[k] = order_key(s.lpj_uniq[k], (uint32_t)k, a.mask_s, false);
-        gsync<T>();
-        _Pragma("unroll 1") for (int i = tid; i < U; i += T) s.rnk[i] = (ln[i] > mn) ? count_greater(kn, U, kn[i]) : Mp;
-        _Pragma("unroll 1") for (int k = tid; k < S; k += T) {
-          int r = count_less(ko, S, ko[k]);
-          if (r < Mp) s.old_by_rank[r] = k;
-        }
-        gsync<T>();
-        int acc_local = 0;
-        _Pragma("unroll 1") for (int i = tid; i < U; i += T) {
-          int r = s.rnk[i];
-          if (r >= Mp) continue;
-          int k = s.old_by_rank[r];
-          double v = ln[i];
-          if (!(v > s.lpj_uniq[k])) continue;
-          const uint32_t *src = s.st_uniq + (size_t)(S + i) * Hs;
-          uint32_t *dst = s.st_uniq + (size_t)k * Hs;
-          uint32_t *gdst = a.states + (n * (int64_t)S + k) * Hg;
-          if (LIST) {
-            for (int w = 0; w < Hw; ++w) dst[w] = src[w];
-            list_to_bits(src, Hg, gdst);
-          } else {
-            for (int w = 0; w < Hw; ++w) { uint32_t x = src[w]; dst[w] = x; gdst[w] = x; }
+        int E = 0;
+        for (int base = 0; base < U; base += T) {
+          const int i = base + tid;
+          const bool f = i < U && ln[i] > mn;
+          int tot;
+          const int off = group_scan_flag<T>(f, tot, s.red_i);
+          if (f) {
+            kn[E + off] = order_key(ln[i], (uint32_t)i, a.mask_c, true);
+            s.eidx[E + off] = i;
           }
-          s.rnk[i] = -1 - k;  // remembered; lpj written after the barrier (other threads still compare against it)
-          ++acc_local;
+          E += tot;
         }
-        gsync<T>();
-        _Pragma("unroll 1") for (int i = tid; i < U; i += T) { int r = s.rnk[i]; if (r < 0) s.lpj_uniq[-1 - r] = ln[i]; }
+        int acc_local = 0;
+        if (E > 0) {  // uniform over the group
+          _Pragma("unroll 1") for (int k = tid; k < S; k += T) ko[k] = order_key(s.lpj_uniq[k], (uint32_t)k, a.mask_s, false);
+          gsync<T>();
+          _Pragma("unroll 1") for (int e = tid; e < E; e += T) s.rnk[e] = count_greater(kn, E, kn[e]);
+          _Pragma("unroll 1") for (int k = tid; k < S; k += T) {
+            int r = count_less(ko, S, ko[k]);
+            if (r < Mp) s.old_by_rank[r] = k;
+          }
+          gsync<T>();
+          _Pragma("unroll 1") for (int e = tid; e < E; e += T) {
+            int r = s.rnk[e];
+            if (r >= Mp) continue;
+            const int i = s.eidx[e];
+            int k = s.old_by_rank[r];
+            double v = ln[i];
+            if (!(v > s.lpj_uniq[k])) continue;
+            const uint32_t *src = s.st_uniq + (size_t)(S + i) * Hs;
+            uint32_t *dst = s.st_uniq + (size_t)k * Hs;
+            uint32_t *gdst = a.states + (n * (int64_t)S + k) * Hg;
+            if (LIST) {
+              for (int w = 0; w < Hw; ++w) dst[w] = src[w];
+              list_to_bits(src, Hg, gdst);
+            } else {
+              for (int w = 0; w < Hw; ++w) { uint32_t x = src[w]; dst[w] = x; gdst[w] = x; }
+            }
+            s.rnk[e] = -1 - k;  // remembered; lpj written after the barrier (other threads still compare against it)
+            ++acc_local;
+          }
+          gsync<T>();
+          _Pragma("unroll 1") for (int e = tid; e < E; e += T) { int r = s.rnk[e]; if (r < 0) s.lpj_uniq[-1 - r] = ln[s.eidx[e]]; }
+        }
         n_sub = group_sum_i<T>(acc_local, s.red_i);
         gsync<T>();
       }
