@@ -287,12 +287,12 @@ def run_lpj_compare(args):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per call from the `ncu --set full` capture of exactly the
-# default command (E-step: profiles/r01h_cfg2_full_estep_ncu_summary.txt, the other calls:
+# default command (E-step: profiles/r01i_cfg2_full_estep_ncu_summary.txt, the other calls:
 # profiles/r01g_cfg2_full_ncu_summary.txt -- unchanged kernels; a call = all its kernels); None where no
 # capture at that size exists.
 NCU_TRAFFIC = {("cfg2", 100000): {
     # list kernel + packed-bits pass over the overflow list
-    "evo_estep": 497.630208e6 + 97.808128e6 + 0.061440e6,
+    "evo_estep": 497.574656e6 + 97.439744e6 + 0.063488e6,
     # statistics pass + split-K Wp GEMM (the memset of the <s> planes, 154 MB, is not a kernel)
     "evo_bsc_suffstats_tc": 413.756672e6 + 141.957888e6 + 260.738560e6 + 6.116864e6,
     # wmax + W' split + table GEMM
