@@ -8,7 +8,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libevo_b200.so")
 
-SEL = {"fit": 0, "rand": 1}
+SEL = {"fit": 0, "rand": 1, "all": 2}
 MUT = {"randflip": 0, "sparseflip": 1, "cross": 2, "cross_randflip": 3, "cross_sparseflip": 4}
 EVAL_BSC_GRAM, EVAL_BSC_DIRECT, EVAL_ES3C = 0, 1, 2
 
@@ -36,6 +36,20 @@ class EstepArgs(C.Structure):
         ("sigma2", C.c_double),
         ("acc", C.c_void_p),
         ("overflow_list", C.c_void_p),
+    ]
+
+
+class EvolveArgs(C.Structure):
+    """Mirror of `evo_evolve_args` (include/evo_b200.h)."""
+
+    _fields_ = [
+        ("e", EstepArgs),
+        ("evolve_only", C.c_int32), ("lpj_given", C.c_int32), ("skip_eval", C.c_int32), ("gen0", C.c_int32),
+        ("pool0", C.c_void_p), ("pool0_n", C.c_void_p),
+        ("tr_parents", C.c_void_p), ("tr_npar", C.c_void_p), ("tr_children", C.c_void_p), ("tr_count", C.c_void_p),
+        ("tr_pos", C.c_void_p),
+        ("ev_states", C.c_void_p), ("ev_lpj", C.c_void_p), ("ev_count", C.c_void_p), ("ev_pool", C.c_void_p),
+        ("ev_pool_n", C.c_void_p),
     ]
 
 
@@ -72,6 +86,8 @@ SIGNATURES = {
     "evo_bsc_lpj_gemm_prepare": (_i, [_vp, _i, _i, _vp, _vp]),
     "evo_bsc_lpj_gemm": (_i, [_vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _d, _d, _vp, _i64, _vp, _vp]),
     "evo_estep": (_i, [C.POINTER(EstepArgs), _vp]),
+    "evo_evolve": (_i, [C.POINTER(EvolveArgs), _vp]),
+    "evo_evolve_dims": (_i, [C.POINTER(EstepArgs), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "evo_select_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "evo_free_energy": (_i, [_vp, _i64, _i, _i64, _vp, _vp]),
     "evo_bsc_suffstats_workspace_bytes": (_i64, [_i64, _i, _i]),

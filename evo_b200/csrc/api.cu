@@ -128,14 +128,19 @@ extern "C" int evo_version(void) { return 100; }
 extern "C" int evo_device_sm_count(void) { return sm_count(); }
 extern "C" unsigned long long evo_launch_count(void) { return launches(); }
 
-extern "C" int evo_estep(const evo_estep_args *x, void *stream) {
+// fills the derived sizes of an E-step launch (children capacity, hash table, pool) from the caller's arguments
+static int estep_dims(const evo_estep_args *x, EstepDev &dv);
+
+static int estep_impl(const evo_estep_args *x, const evo_evolve_args *t, void *stream) {
   EVO_REQUIRE(x != nullptr, "null args");
   EVO_REQUIRE(x->N >= 0 && x->H > 0 && x->S > 0 && x->D > 0, "bad sizes");
   EVO_REQUIRE(x->S_perm == 0 || x->S_perm == 1, "S_perm must be 0 or 1 (only the all-zero state is implemented)");
   EVO_REQUIRE(!(x->background && x->S_perm), "background unit and permanent all-zero state are exclusive");
   EVO_REQUIRE(x->n_generations >= 0 && x->n_generations < 256, "bad n_generations");
   EVO_REQUIRE(x->states && x->lpj, "states/lpj null");
-  EVO_REQUIRE(x->selection == EVO_SEL_FIT || x->selection == EVO_SEL_RAND, "bad selection");
+  EVO_REQUIRE(x->selection == EVO_SEL_FIT || x->selection == EVO_SEL_RAND || (t && x->selection == EVO_SEL_ALL),
+              "bad selection");
+  EVO_REQUIRE(x->H <= 65535 && x->S <= 65535, "H and S must not exceed 65535 (latent / state indices are 16 bit)");
   EVO_REQUIRE(x->mutation >= EVO_MUT_RANDFLIP && x->mutation <= EVO_MUT_CROSS_SPARSEFLIP, "bad mutation");
   if (x->N == 0) return EVO_OK;
   EstepDev dv;
@@ -150,6 +155,43 @@ extern "C" int evo_estep(const evo_estep_args *x, void *stream) {
   dv.states = x->states; dv.lpj = x->lpj;
   dv.inj_children = x->inj_children; dv.inj_count = x->inj_count; dv.inj_cmax = x->inj_cmax;
   dv.acc = x->acc;
+  {
+    int rc = estep_dims(x, dv);
+    if (rc) return rc;
+  }
+  if (t) {
+    dv.generic_only = 1;
+    dv.evolve_only = t->evolve_only; dv.lpj_given = t->lpj_given; dv.skip_eval = t->skip_eval; dv.gen0 = t->gen0;
+    dv.pool0 = t->pool0; dv.pool0_n = t->pool0_n;
+    dv.tr_parents = t->tr_parents; dv.tr_npar = t->tr_npar; dv.tr_children = t->tr_children; dv.tr_count = t->tr_count;
+    dv.tr_pos = t->tr_pos;
+    dv.ev_states = t->ev_states; dv.ev_lpj = t->ev_lpj; dv.ev_count = t->ev_count; dv.ev_pool = t->ev_pool;
+    dv.ev_pool_n = t->ev_pool_n;
+    EVO_REQUIRE(!t->pool0 || t->pool0_n, "pool0 needs pool0_n");
+    EVO_REQUIRE(!t->tr_parents || t->tr_npar, "tr_parents needs tr_npar");
+    EVO_REQUIRE(!t->tr_children || t->tr_count, "tr_children needs tr_count");
+    EVO_REQUIRE(!t->evolve_only || (t->ev_states && t->ev_lpj && t->ev_count), "evolve_only needs ev_states, ev_lpj, ev_count");
+    EVO_REQUIRE(!t->ev_pool || t->ev_pool_n, "ev_pool needs ev_pool_n");
+    EVO_REQUIRE(t->gen0 >= 0 && t->gen0 + x->n_generations < 256, "bad gen0");
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (x->eval == EVO_EVAL_BSC_GRAM) {
+    EVO_REQUIRE(x->G && x->B && x->ynorm2, "gram evaluator needs G, B, ynorm2");
+    EVO_REQUIRE(x->mask == nullptr, "gram evaluator needs complete data");
+    BscGramEval ev{x->G, x->B, x->ynorm2, x->pre1, x->pil_bar, dv.H, dv.Hw, nullptr, nullptr, 0.0};
+    return launch_estep_any(dv, ev, st);
+  } else if (x->eval == EVO_EVAL_BSC_DIRECT) {
+    EVO_REQUIRE(x->W && x->Y, "direct evaluator needs W, Y");
+    BscDirectEval ev{x->W, x->Y, x->mask, x->pre1, x->pil_bar, dv.D, dv.H, dv.Hw, nullptr, nullptr, 0.0};
+    return launch_estep_any(dv, ev, st);
+  } else if (x->eval == EVO_EVAL_ES3C) {
+    return es3c_launch_estep(dv, x, st);
+  }
+  set_error("evo_estep: unknown evaluator %d", x->eval);
+  return EVO_ERR_ARG;
+}
+
+static int estep_dims(const evo_estep_args *x, EstepDev &dv) {
   int P = x->n_parents < x->S ? x->n_parents : x->S;
   int Cg;
   if (x->inj_children) {
@@ -180,21 +222,27 @@ extern "C" int evo_estep(const evo_estep_args *x, void *stream) {
   dv.ovf_list = x->overflow_list;
   dv.n_list = nullptr;
   dv.mask_c = pow2mask(dv.Ctot); dv.mask_s = pow2mask(dv.S); dv.mask_p = pow2mask(dv.PK);
-  cudaStream_t st = (cudaStream_t)stream;
-  if (x->eval == EVO_EVAL_BSC_GRAM) {
-    EVO_REQUIRE(x->G && x->B && x->ynorm2, "gram evaluator needs G, B, ynorm2");
-    EVO_REQUIRE(x->mask == nullptr, "gram evaluator needs complete data");
-    BscGramEval ev{x->G, x->B, x->ynorm2, x->pre1, x->pil_bar, dv.H, dv.Hw, nullptr, nullptr, 0.0};
-    return launch_estep_any(dv, ev, st);
-  } else if (x->eval == EVO_EVAL_BSC_DIRECT) {
-    EVO_REQUIRE(x->W && x->Y, "direct evaluator needs W, Y");
-    BscDirectEval ev{x->W, x->Y, x->mask, x->pre1, x->pil_bar, dv.D, dv.H, dv.Hw, nullptr, nullptr, 0.0};
-    return launch_estep_any(dv, ev, st);
-  } else if (x->eval == EVO_EVAL_ES3C) {
-    return es3c_launch_estep(dv, x, st);
-  }
-  set_error("evo_estep: unknown evaluator %d", x->eval);
-  return EVO_ERR_ARG;
+  return EVO_OK;
+}
+
+extern "C" int evo_estep(const evo_estep_args *x, void *stream) { return estep_impl(x, nullptr, stream); }
+
+extern "C" int evo_evolve(const evo_evolve_args *t, void *stream) {
+  EVO_REQUIRE(t != nullptr, "null args");
+  return estep_impl(&t->e, t, stream);
+}
+
+extern "C" int evo_evolve_dims(const evo_estep_args *x, int32_t *Cg, int32_t *Ctot, int32_t *PK) {
+  EVO_REQUIRE(x != nullptr && x->S > 0 && x->H > 0, "bad sizes");
+  EstepDev dv;
+  memset(&dv, 0, sizeof(dv));
+  dv.S = x->S; dv.H = x->H; dv.Hw = words_for(x->H);
+  int rc = estep_dims(x, dv);
+  if (rc) return rc;
+  if (Cg) *Cg = dv.Cg;
+  if (Ctot) *Ctot = dv.Ctot;
+  if (PK) *PK = dv.PK;
+  return EVO_OK;
 }
 
 extern "C" int evo_select_topk(uint32_t *states, double *lpj, int64_t N, int S, int S_perm, int H, int Mprime,

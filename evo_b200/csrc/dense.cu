@@ -813,12 +813,9 @@ extern "C" int evo_bsc_lpj_gemm(const uint32_t *states, int shared_states, int64
   a.descale = reinterpret_cast<const float *>(workspace) + 1;
   a.pre1 = pre1; a.pil_bar = pil_bar;
   a.out = lpj_out; a.ld = ld_lpj; a.counters = reset_counters;
-  static bool attr_set = false;
-  if (!attr_set) {
-    EVO_CUDA(cudaFuncSetAttribute(dense::dense_lpj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)dense::SMEM_BYTES));
-    attr_set = true;
-  }
+  // per device and cheap: set on every launch (a process may drive several GPUs)
+  EVO_CUDA(cudaFuncSetAttribute(dense::dense_lpj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)dense::SMEM_BYTES));
   int64_t tiles = (a.rows + dense::BM - 1) / dense::BM;
   int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   dense::dense_lpj_kernel<<<grid, dense::THREADS, dense::SMEM_BYTES, (cudaStream_t)stream>>>(tmap, a);
@@ -875,12 +872,8 @@ extern "C" int evo_bsc_tables_tc(const double *W, int64_t N, int D, int H, void 
   a.k_chunks = 1; a.kb_chunk = g.KB; a.accumulate = 0;
   a.descale = reinterpret_cast<const float *>(ws) + 4;
   a.B = B;
-  static bool attr_set = false;
-  if (!attr_set) {
-    EVO_CUDA(cudaFuncSetAttribute(dense::table_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)dense::T_SMEM_BYTES));
-    attr_set = true;
-  }
+  EVO_CUDA(cudaFuncSetAttribute(dense::table_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)dense::T_SMEM_BYTES));
   int64_t tiles = (N + dense::BM - 1) / dense::BM * g.n_tiles;
   int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   dense::table_gemm_kernel<<<grid, dense::T_THREADS, dense::T_SMEM_BYTES, st>>>(ta, tb, a);

@@ -4,8 +4,18 @@
 
 namespace evo {
 
-static double *g_scratch = nullptr;
-static int g_scratch_warps = 0;
+// global workspaces for systems with 17..32 active latents: one registration PER DEVICE (a process may
+// hold models on several GPUs); looked up by the current device at launch time
+constexpr int MAX_DEV = 64;
+static double *g_scratch_tab[MAX_DEV];
+static int g_scratch_warps_tab[MAX_DEV];
+static void current_scratch(double *&scratch, int &warps) {
+  int dev = 0;
+  scratch = nullptr; warps = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) return;
+  scratch = __atomic_load_n(&g_scratch_tab[dev], __ATOMIC_ACQUIRE);
+  warps = scratch ? __atomic_load_n(&g_scratch_warps_tab[dev], __ATOMIC_ACQUIRE) : 0;
+}
 
 int es3c_launch_estep(const EstepDev &dv, const evo_estep_args *x, cudaStream_t st) {
   EVO_REQUIRE(x->Psi && x->mus && x->pil_bar_h, "es3c evaluator needs Psi, mus, pil_bar_h");
@@ -15,7 +25,7 @@ int es3c_launch_estep(const EstepDev &dv, const evo_estep_args *x, cudaStream_t 
   ev.Psi = x->Psi; ev.mus = x->mus; ev.pil_bar = x->pil_bar_h;
   ev.s2i = (double)(1.0L / (long double)x->sigma2);
   ev.D = dv.D; ev.H = dv.H; ev.Hw = dv.Hw;
-  ev.scratch = g_scratch; ev.scratch_warps = g_scratch_warps;
+  current_scratch(ev.scratch, ev.scratch_warps);
   if (x->mask) {
     EVO_REQUIRE(x->W && x->Y, "es3c with incomplete data needs Wt (in W) and Y");
     ev.masked = 1; ev.Wt = x->W; ev.Y = x->Y; ev.mask = x->mask;
@@ -211,8 +221,11 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
 using namespace evo;
 
 extern "C" int evo_es3c_set_scratch(double *scratch, int warps) {
-  g_scratch = scratch;
-  g_scratch_warps = scratch ? warps : 0;
+  int dev = 0;
+  EVO_CUDA(cudaGetDevice(&dev));
+  EVO_REQUIRE(dev >= 0 && dev < MAX_DEV, "device index out of range");
+  __atomic_store_n(&g_scratch_warps_tab[dev], scratch ? warps : 0, __ATOMIC_RELEASE);
+  __atomic_store_n(&g_scratch_tab[dev], scratch, __ATOMIC_RELEASE);
   return EVO_OK;
 }
 
@@ -227,7 +240,7 @@ extern "C" int evo_es3c_suffstats(const evo_es3c_stats_args *x, void *stream) {
   ev.Psi = x->Psi; ev.mus = x->mus; ev.pil_bar = x->mus;  // pil_bar is not used by the moments
   ev.s2i = (double)(1.0L / (long double)x->sigma2);
   ev.D = x->D; ev.H = x->H; ev.Hw = words_for(x->H);
-  ev.scratch = g_scratch; ev.scratch_warps = g_scratch_warps;
+  current_scratch(ev.scratch, ev.scratch_warps);
   ev.Wt = x->Wt; ev.Y = x->Y;
   if (x->mask) {
     ev.masked = 1; ev.mask = x->mask;
@@ -267,7 +280,7 @@ extern "C" int evo_es3c_lpj(const uint32_t *states, int shared_states, int64_t N
   ev.Psi = Psi; ev.mus = mus; ev.pil_bar = pil_bar_h;
   ev.s2i = (double)(1.0L / (long double)sigma2);
   ev.D = D; ev.H = H; ev.Hw = words_for(H);
-  ev.scratch = g_scratch; ev.scratch_warps = g_scratch_warps;
+  current_scratch(ev.scratch, ev.scratch_warps);
   if (mask) {
     EVO_REQUIRE(Wt && Y, "incomplete data needs Wt and Y");
     ev.masked = 1; ev.Wt = Wt; ev.Y = Y; ev.mask = mask;

@@ -33,6 +33,15 @@ struct EstepDev {
   const int32_t *inj_count;
   int inj_cmax;
   double *acc;
+  // ---- generic kernel only: operator trace / stand-alone evolve (evo_evolve, include/evo_b200.h) ----
+  int generic_only;  // any of the fields below is in use: the FAST / LIST variants are not launched
+  int evolve_only, lpj_given, skip_eval, gen0;
+  const int32_t *pool0, *pool0_n;
+  uint32_t *tr_parents, *tr_children;
+  int32_t *tr_npar, *tr_count, *tr_pos;
+  uint32_t *ev_states;
+  double *ev_lpj;
+  int32_t *ev_count, *ev_pool, *ev_pool_n;
   // derived
   int Cg;    // children capacity per generation
   int Ctot;  // Cg * n_generations
@@ -376,6 +385,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
     // code is instantiated once (instruction-cache footprint)
     for (int g = -1; g < a.n_generations; ++g) {
       int nc = 0, u_g = 0;
+      const uint32_t gr = FAST ? (uint32_t)g : (uint32_t)(g + a.gen0);  // generation index of the Philox streams
       if (g >= 0) {
       if (!FAST && a.inj_children) {
         // ---- injected candidates (parity runs) -------------------------------------------------
@@ -393,8 +403,11 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             mn = -group_max<T>(-mn, s.red_d);
           }
           double shift = 2.0 * fmin(mn, 0.0);
+          if (!FAST && a.selection == EVO_SEL_ALL) {  // explicit parents: the pool in its own order
+            _Pragma("unroll 1") for (int i = tid; i < take; i += T) s.parents[i] = s.pool[i];
+          } else {
           _Pragma("unroll 1") for (int i = tid; i < pool_n; i += T) {
-            uint4 r = rng.draw(RNG_SELECT, g, (uint32_t)i);
+            uint4 r = rng.draw(RNG_SELECT, gr, (uint32_t)i);
             double u = u01(r.x, r.y);
             double key;
             if (a.selection == EVO_SEL_FIT) {
@@ -412,7 +425,14 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             int r = count_greater(s.keys, pool_n, s.keys[i]);
             if (r < take) s.parents[r] = s.pool[i];
           }
+          }
           gsync<T>();
+          if (!FAST && a.tr_parents) {
+            uint32_t *dst = a.tr_parents + ((n * (int64_t)a.n_generations + g) * a.n_parents) * (int64_t)Hg;
+            _Pragma("unroll 1") for (int i = tid; i < take * Hw; i += T)
+              dst[i] = s.st_uniq[(size_t)s.parents[i / Hw] * Hs + (i % Hw)];
+            if (tid == 0) a.tr_npar[n * (int64_t)a.n_generations + g] = take;
+          }
         }
         // ---- mutation (eas.py:10-135) -----------------------------------------------------------
         const int mut = FAST ? (int)EVO_MUT_RANDFLIP : a.mutation;
@@ -427,7 +447,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
                 int pos;
                 bool dup;
                 do {
-                  uint4 r = rng.draw(RNG_MUTATE, g, di++);
+                  uint4 r = rng.draw(RNG_MUTATE, gr, di++);
                   pos = (int)urange(r.x, (uint32_t)Hm);
                   dup = false;
                   for (int q = 0; q < j; ++q) dup |= (s.slot[p * C + q] == pos);
@@ -446,8 +466,12 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             if (bgu) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
             if (LIST) { if (!list_toggle(dst, s.slot[c])) s.sh[0] = 1; }
             else if (FAST || mut == EVO_MUT_RANDFLIP) flip_bit(dst, s.slot[c]);
-            else sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_MUTATE, g, (uint32_t)c);
+            else sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_MUTATE, gr, (uint32_t)c);
             if (bgu) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
+            if (!FAST && a.tr_pos) {
+              int32_t *tp = a.tr_pos + ((n * (int64_t)a.n_generations + g) * a.Cg + c) * 2;
+              tp[0] = (mut == EVO_MUT_RANDFLIP) ? s.slot[c] : -1; tp[1] = -1;
+            }
           }
         } else {
           // one-point crossover of every unordered parent pair, two children per pair
@@ -457,7 +481,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             int i = 0, rem = q;
             while (rem >= take - 1 - i) { rem -= take - 1 - i; ++i; }
             int j = i + 1 + rem;
-            uint4 r = rng.draw(RNG_CROSS, g, (uint32_t)q);
+            uint4 r = rng.draw(RNG_CROSS, gr, (uint32_t)q);
             int cp = 1 + (Hm > 1 ? (int)urange(r.x, (uint32_t)(Hm - 1)) : 0);  // cp in {1..Hm-1}
             const uint32_t *pa = s.st_uniq + (size_t)s.parents[i] * Hs;
             const uint32_t *pb = s.st_uniq + (size_t)s.parents[j] * Hs;
@@ -472,11 +496,17 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
               uint32_t *dst = k ? c1 : c0;
               uint32_t cidx = (uint32_t)(2 * q + k);
               if (bgu) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
+              int fp = -1;
               if (mut == EVO_MUT_CROSS_RANDFLIP) {
-                uint4 r2 = rng.draw(RNG_FLIP2, g, cidx);
-                flip_bit(dst, (int)urange(r2.x, (uint32_t)Hm));
+                uint4 r2 = rng.draw(RNG_FLIP2, gr, cidx);
+                fp = (int)urange(r2.x, (uint32_t)Hm);
+                flip_bit(dst, fp);
               } else if (mut == EVO_MUT_CROSS_SPARSEFLIP) {
-                sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_FLIP2, g, cidx);
+                sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_FLIP2, gr, cidx);
+              }
+              if (a.tr_pos) {
+                int32_t *tp = a.tr_pos + ((n * (int64_t)a.n_generations + g) * a.Cg + cidx) * 2;
+                tp[0] = cp; tp[1] = fp;
               }
               if (bgu) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
             }
@@ -485,6 +515,11 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       }
       gsync<T>();
       if (LIST && s.sh[0]) break;  // a child does not fit the list form: the packed-bits kernel redoes this datapoint
+      if (!FAST && a.tr_children) {
+        uint32_t *dst = a.tr_children + ((n * (int64_t)a.n_generations + g) * a.Cg) * (int64_t)Hg;
+        _Pragma("unroll 1") for (int i = tid; i < nc * Hw; i += T) dst[i] = s.st_child[(i / Hw) * Hs + (i % Hw)];
+        if (tid == 0) a.tr_count[n * (int64_t)a.n_generations + g] = nc;
+      }
 
       // ---- de-duplicate against (permanent, K^n, earlier new) and among the children ----------
       _Pragma("unroll 1") for (int c = tid; c < nc; c += T) {
@@ -527,7 +562,12 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       {
         const int first = g < 0 ? 0 : S + U, cnt = g < 0 ? S : u_g;
         unsigned fl = 0;
-        if (cnt > 0) {
+        if (!FAST && g < 0 && a.lpj_given) {  // this_lpj supplied by the caller (eas.py:196)
+          const double *row = a.lpj + n * (int64_t)(S + a.S_perm) + a.S_perm;
+          _Pragma("unroll 1") for (int i = tid; i < S; i += T) s.lpj_uniq[i] = row[i];
+        } else if (!FAST && g >= 0 && a.skip_eval) {  // the caller evaluates the new states itself
+          _Pragma("unroll 1") for (int i = tid; i < cnt; i += T) s.lpj_uniq[first + i] = 0.0;
+        } else if (cnt > 0) {
           ev.template eval_batch<T, LIST>(s.st_uniq + (size_t)first * Hs, Hs, cnt, s.lpj_uniq + first, fl);
           fl = group_or<T>(fl, s.red_i);
           if (tid == 0 && fl) { if (fl & 1) ++cnt_nan; else if (fl & 2) ++cnt_small; else ++cnt_inf; }
@@ -540,8 +580,15 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
           s.pool[i] = i;
         }
         gsync<T>();
+        if (!FAST && a.pool0) {  // caller-supplied first pool (generation-by-generation evolve_states)
+          pool_n = a.pool0_n[n];
+          if (pool_n > S) pool_n = S;
+          _Pragma("unroll 1") for (int i = tid; i < pool_n; i += T) s.pool[i] = a.pool0[n * (int64_t)S + i];
+          gsync<T>();
+        }
         continue;
       }
+      if (!FAST && a.ev_count && tid == 0) a.ev_count[n * (int64_t)(1 + a.n_generations) + 1 + g] = u_g;
       // ---- next pool: this round's new states, then the re-discovered old ones -----------------
       int pn = 0;
       _Pragma("unroll 1") for (int i = tid; i < u_g && i < a.PK; i += T) s.pool[i] = S + U + i;
@@ -568,6 +615,18 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
       continue;
     }
 
+    if (!FAST && a.evolve_only) {  // evolve_states alone (eas.py:313): hand the new states back, leave K^n as it is
+      gsync<T>();
+      uint32_t *dst = a.ev_states + n * (int64_t)a.Ctot * Hg;
+      _Pragma("unroll 1") for (int i = tid; i < U * Hw; i += T) dst[i] = s.st_uniq[(size_t)(S + i / Hw) * Hs + (i % Hw)];
+      _Pragma("unroll 1") for (int i = tid; i < U; i += T) a.ev_lpj[n * (int64_t)a.Ctot + i] = s.lpj_uniq[S + i];
+      if (a.ev_pool) {
+        _Pragma("unroll 1") for (int i = tid; i < pool_n; i += T) a.ev_pool[n * (int64_t)a.PK + i] = s.pool[i];
+        if (tid == 0) a.ev_pool_n[n] = pool_n;
+      }
+      if (tid == 0) a.ev_count[n * (int64_t)(1 + a.n_generations)] = U;
+      continue;
+    }
     // ---- vary_Kn: j-th best new replaces j-th worst old while it is better ----------------------
     // Ranks by counting (strict total orders: new by lpj desc / index asc, old by lpj asc / slot
     // asc).  New state of rank r is accepted iff r < M' and it beats the old state of rank r; the
@@ -718,7 +777,8 @@ template <class Eval>
 static int launch_estep_any(const EstepDev &dv, Eval ev, cudaStream_t st) {
   int work = dv.S > dv.Cg ? dv.S : dv.Cg;
   int T = ev.threads_hint(work);
-  const bool fast = !dv.inj_children && dv.mutation == EVO_MUT_RANDFLIP && !dv.background && !getenv("EVO_ESTEP_GENERIC");
+  const bool fast = !dv.inj_children && dv.mutation == EVO_MUT_RANDFLIP && !dv.background && !dv.generic_only &&
+                    dv.selection != EVO_SEL_ALL && !getenv("EVO_ESTEP_GENERIC");
   if (const char *e = getenv("EVO_ESTEP_T")) { int t = atoi(e); if (t > 0) T = t; }
   if (T <= 32) return launch_estep_T<Eval, 32>(dv, ev, fast, st);
   if (T <= 64) return launch_estep_T<Eval, 64>(dv, ev, fast, st);

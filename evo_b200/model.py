@@ -217,13 +217,20 @@ class Model:
         return F, S_nunique, S_sub, new_params
 
     # ---- fused E-step launcher --------------------------------------------------------------------
-    def _estep_launch(self, my_suff_stat, dd, acc, fill):
-        """Fill an `evo_estep_args`, let the subclass add its evaluator tables (`fill(args)`), launch."""
-        a = _lib.EstepArgs()
+    def _fill_estep_args(self, a, my_suff_stat, dd):
+        """Container fields -> `evo_estep_args` (sizes, EA hyper-parameters, RNG keys, K sets); validates the
+        device buffers against the shard (the kernels index them unchecked)."""
         ss = my_suff_stat
         perm = ss["permanent"]
+        sd, ld = ss["ss_dev"], ss["lpj_dev"]
+        S, S_perm = int(sd.shape[1]), int(ss["S_perm"])
+        assert sd.dtype == torch.int32 and tuple(sd.shape) == (dd.N, S, V.words_for(self.H)) and sd.is_contiguous(), \
+            "ss_dev must be contiguous int32 [%d][S][%d], got %s" % (dd.N, V.words_for(self.H), tuple(sd.shape))
+        assert ld.dtype == torch.float64 and tuple(ld.shape) == (dd.N, S + S_perm) and ld.is_contiguous(), \
+            "lpj_dev must be contiguous float64 [%d][%d], got %s" % (dd.N, S + S_perm, tuple(ld.shape))
+        assert sd.device == self.device and ld.device == self.device, "K sets live on another device than the model"
         a.N, a.n_offset = dd.N, int(ss.get("n_offset", 0) or 0)
-        a.D, a.H, a.S, a.S_perm = self.D, self.H, int(ss["ss_dev"].shape[1]), int(ss["S_perm"])
+        a.D, a.H, a.S, a.S_perm = self.D, self.H, S, S_perm
         a.Mprime = int(ss["Mprime"])
         a.n_parents, a.n_children, a.n_generations = int(ss["n_parents"]), int(ss["n_children"]), int(ss["n_generations"])
         a.selection = _lib.SEL[ss["parent_selection"].name]
@@ -231,7 +238,17 @@ class Model:
         a.background = int(bool(perm["background"]))
         a.bitflip_prob = float(ss["bitflip_prob"]) if ss["bitflip_prob"] is not None else 0.0
         a.seed, a.iteration = int(ss.get("seed", 0x5EED)), int(ss.get("iteration", 0)) + 1
-        a.states, a.lpj = ss["ss_dev"].data_ptr(), ss["lpj_dev"].data_ptr()
+        a.states, a.lpj = sd.data_ptr(), ld.data_ptr()
+
+    def _estep_launch(self, my_suff_stat, dd, acc, fill):
+        """Fill an `evo_estep_args`, let the subclass add its evaluator tables (`fill(args)`), launch.
+        With `my_suff_stat["trace"]` set, the same E-step runs through `evo_evolve` and the selected parents,
+        the children as mutated and their flip positions / cut points are left in `my_suff_stat["trace_out"]`."""
+        ss = my_suff_stat
+        trace = bool(ss.get("trace"))
+        ea = _lib.EvolveArgs() if trace else None
+        a = ea.e if trace else _lib.EstepArgs()
+        self._fill_estep_args(a, ss, dd)
         inj = ss.get("inject")
         keep = None
         if inj is not None:
@@ -240,6 +257,7 @@ class Model:
                 ch, cnt = V.pack_injection(ch, cnt, self.device)
             keep = (ch, cnt)
             assert ch.shape[0] == dd.N and ch.shape[1] == a.n_generations
+            assert ch.shape[3] == V.words_for(self.H) and tuple(cnt.shape) == (dd.N, a.n_generations)
             a.inj_children, a.inj_count, a.inj_cmax = ch.data_ptr(), cnt.data_ptr(), int(ch.shape[2])
         a.acc = acc.data_ptr()
         ovf = getattr(self, "_ovf_list", None)
@@ -249,10 +267,44 @@ class Model:
         hold = fill(a)
         with torch.cuda.device(self.device):
             ev = self._tick()
-            _lib.check(self.lib.evo_estep(C.byref(a), _lib.stream()), "evo_estep")
+            if trace:
+                tr = V.alloc_trace(self.lib, ea, dd.N, self.device)
+                _lib.check(self.lib.evo_evolve(C.byref(ea), _lib.stream()), "evo_evolve")
+                dict.__setitem__(ss, "trace_out", tr)
+            else:
+                _lib.check(self.lib.evo_estep(C.byref(a), _lib.stream()), "evo_estep")
             self._tock("evo_estep", ev)
         ss["iteration"] = a.iteration
         return keep, hold
+
+    def evolve(self, model_params, my_suff_stat, my_data):
+        """`evolve_states` (evo/variational/eas.py:153-313) for EVERY datapoint of the shard in one launch
+        (`evo_evolve`, evolve_only): the K sets are left as they are, the new unique states of all generations
+        and their log-pseudo-joints come back.  Returns `(new_states int32 [N][Ctot][Hw] packed, new_lpj
+        float64 [N][Ctot], counts int32 [N][1+G])` as device tensors, plus the operator trace in
+        `my_suff_stat["trace_out"]`."""
+        ss = my_suff_stat
+        dd = self.device_data(my_data)
+        self._evolve_tables(model_params, ss, my_data, dd)
+        ea = _lib.EvolveArgs()
+        self._fill_estep_args(ea.e, ss, dd)
+        ea.e.acc = None
+        hold = self._fill_eval(ea.e, model_params, dd)  # noqa: F841 (keeps evaluator tables alive)
+        ea.evolve_only = 1
+        with torch.cuda.device(self.device):
+            tr = V.alloc_trace(self.lib, ea, dd.N, self.device, evolve=True)
+            _lib.check(self.lib.evo_evolve(C.byref(ea), _lib.stream()), "evo_evolve")
+        dict.__setitem__(ss, "trace_out", tr)
+        ss["iteration"] = ea.e.iteration
+        return tr["ev_states"], tr["ev_lpj"], tr["ev_count"]
+
+    def _evolve_tables(self, model_params, my_suff_stat, my_data, dd):
+        """State-independent terms + evaluator tables under `model_params` (what E_step does before its launch)."""
+        pil = self.E_step_precompute(model_params, my_suff_stat, my_data)
+        if pil is None:
+            self._tables(model_params, dd)
+        else:
+            self._tables(model_params, dd, pil)
 
     # ---- free energy (_models.py:334-451) -------------------------------------------------------
     def _sum_logsumexp(self, lpj):

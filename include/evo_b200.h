@@ -145,6 +145,45 @@ typedef struct evo_estep_args {
 } evo_estep_args;
 int evo_estep(const evo_estep_args *args, void *stream);
 
+/* ---- evolve_states (evo/variational/eas.py:153-313) as an entry point of its own ----------------------
+ * The generation loop of evo_estep -- parent selection (eas.py:138-150), mutation (eas.py:10-135),
+ * de-duplication against (permanent, K^n, earlier new) (eas.py:252-258), lpj of the new states (eas.py:267),
+ * next pool = new + re-discovered (eas.py:271-295) -- with what evo_estep keeps on-chip made visible:
+ *   - operator trace: the selected parents, the children exactly as mutated (before de-duplication) and the
+ *     positions / cut points that produced them, per datapoint and generation;
+ *   - evolve_only: the K sets, lpj and acc are left untouched and the new unique states of all generations
+ *     come back with their lpj (what the reference's evolve_states returns, eas.py:313), together with the
+ *     parent pool the next generation would select from.
+ * `e` has the meaning it has for evo_estep (RNG mode, or injected children); selection may also be
+ * EVO_SEL_ALL.  Always runs the generic kernel (every operator), never the randflip fast paths, and draws
+ * the same Philox streams: with the same seed / iteration / n_offset the children are those evo_estep makes.
+ * Buffer extents: evo_evolve_dims (Cg = children capacity per generation, Ctot = Cg * generations,
+ * PK = pool capacity = max(S, Cg)).  Caller zeroes tr_count / tr_npar / ev_count (generations that do not
+ * run leave them untouched). */
+#define EVO_SEL_ALL 2 /* every pool member in pool order (first n_parents): operator calls on explicit parents */
+typedef struct evo_evolve_args {
+  evo_estep_args e;
+  int32_t evolve_only; /* 1: do not touch e.states / e.lpj / e.acc; fill ev_* */
+  int32_t lpj_given;   /* 1: e.lpj holds this_lpj of K^n (eas.py:196); K^n is not re-evaluated */
+  int32_t skip_eval;   /* 1: new states come back un-evaluated (lpj 0): the caller applies its own eval_lpj */
+  int32_t gen0;        /* index of the first generation of this call (Philox stream keying) */
+  const int32_t *pool0;   /* [N][S] first parent pool as indices into K^n, pool0_n[n] entries; NULL = all of K^n */
+  const int32_t *pool0_n; /* [N] */
+  uint32_t *tr_parents;  /* [N][G][n_parents][Hw] in selection order, or NULL */
+  int32_t *tr_npar;      /* [N][G] */
+  uint32_t *tr_children; /* [N][G][Cg][Hw], or NULL */
+  int32_t *tr_count;     /* [N][G] */
+  int32_t *tr_pos;       /* [N][G][Cg][2]: randflip (flipped position, -1); cross* (cut point, extra flipped
+                          * position or -1); sparseflip (-1, -1); or NULL */
+  uint32_t *ev_states;   /* [N][Ctot][Hw] new unique states, generation by generation, first occurrence order */
+  double *ev_lpj;        /* [N][Ctot] */
+  int32_t *ev_count;     /* [N][1 + G]: total, then per generation */
+  int32_t *ev_pool;      /* [N][PK] next parent pool: index < S = member of K^n, else S + index into ev_states */
+  int32_t *ev_pool_n;    /* [N] */
+} evo_evolve_args;
+int evo_evolve_dims(const evo_estep_args *e, int32_t *Cg, int32_t *Ctot, int32_t *PK);
+int evo_evolve(const evo_evolve_args *args, void *stream);
+
 /* vary_Kn alone (utils.py:231-337) for one batch of datapoints: new candidates [N][U][Hw] with
  * lpj_new [N][U], n_new[n] valid rows each; updates states/lpj in place; out_counts[n] =
  * (#new unique, #substituted). */

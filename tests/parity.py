@@ -29,6 +29,25 @@ def load_case(path):
     z = np.load(path, allow_pickle=False)
     c = {k: z[k] for k in z.files}
     H, N, S = int(c["H"]), int(c["N"]), int(c["S"])
+    if "sha_W0" in c:
+        # BASELINE-shape fixture (tests/golden/make_golden_shapes.py): the large inputs are regenerated from the
+        # recorded seed and must hash to what the reference run was fed
+        if GOLDEN not in sys.path:
+            sys.path.insert(0, GOLDEN)
+        from shape_inputs import sha, shape_inputs
+
+        model, missing = str(c["model"]), float(c["missing"])
+        inp = shape_inputs(model, int(c["seed"]), int(c["D"]), H, N, float(c["act"]), missing)
+        assert sha(inp["Y"]) == str(c["sha_Y"]) and sha(inp["W0"]) == str(c["sha_W0"]), \
+            "regenerated inputs differ from the ones the fixture was recorded with"
+        X = inp["X"]
+        c["X"] = X
+        c["Y"] = np.where(X, inp["Y"], np.nan)
+        c["W0"] = inp["W0"]
+        if model == "es3c":
+            c["Psi0"] = inp["Psi0"] if missing == 0 else np.eye(H)
+            assert sha(c["Psi0"]) == str(c["sha_Psi0"])
+            c["Xrec"] = X.copy() if missing > 0 else np.zeros_like(X)
     c["ss0_bool"] = np.unpackbits(c["ss0"], axis=-1)[..., :H].astype(bool)
     c["ss_final_bool"] = np.unpackbits(c["ss_final"], axis=-1)[..., :H].astype(bool)
     c["children_bool"] = np.unpackbits(c["children"], axis=-1)[..., :H].astype(bool)
@@ -65,12 +84,17 @@ class OracleReplay:
         self.n = -1
 
 
+def learned(c, default):
+    return tuple(str(c["to_learn"]).split(",")) if "to_learn" in c else default
+
+
 def run_oracle_case(c, iters):
     from oracle import bsc as OB
     from oracle import variational as OV
 
     D, H, N, S = int(c["D"]), int(c["H"]), int(c["N"]), int(c["S"])
     perm = permanent_of(c)
+    to_learn = learned(c, ("W", "pi", "sigma"))
     cont = OV.init_states(1, S, H, str(c["selection"]), str(c["mutation"]), int(c["P"]), int(c["C"]), int(c["G"]),
                           bitflip_prob=1.0 / H, permanent=copy.deepcopy(perm))
     cont["ss"] = c["ss0_bool"].copy()
@@ -83,14 +107,14 @@ def run_oracle_case(c, iters):
     th = {"W": c["W0"].copy(), "pi": float(c["pi0"]), "sigma": float(c["sigma0"])}
     out = []
     for it in range(iters):
-        F, a, b, th = OB.step(th, cont, data, D, H, cont["ss"].shape[1], do_reconstruction=missing,
+        F, a, b, th = OB.step(th, cont, data, D, H, cont["ss"].shape[1], to_learn=to_learn, do_reconstruction=missing,
                               reference_quirks=False)
         out.append((F, a, b, {k: np.array(th[k]) for k in ("W", "pi", "sigma")}))
         rep.next_iteration()
     return out, cont, data
 
 
-def run_gpu_case(c, iters, inject=True):
+def run_gpu_case(c, iters, inject=True, tables="f64", stats="f64"):
     import torch
 
     from evo_b200.bsc import BSC
@@ -98,7 +122,8 @@ def run_gpu_case(c, iters, inject=True):
 
     D, H, N, S = int(c["D"]), int(c["H"]), int(c["N"]), int(c["S"])
     perm = permanent_of(c)
-    model = BSC(D, H, S)
+    model = BSC(D, H, S, to_learn=learned(c, ("W", "pi", "sigma")))
+    model.tables, model.stats = tables, stats
     cont = init_states(N, S, H, str(c["selection"]), str(c["mutation"]), int(c["P"]), int(c["C"]), int(c["G"]),
                        bitflip_prob=1.0 / H, permanent=copy.deepcopy(perm))
     cont["ss"] = c["ss0_bool"]
@@ -117,12 +142,12 @@ def run_gpu_case(c, iters, inject=True):
     return out, cont, data
 
 
-def run_bsc_parity_case(path, iters=None):
+def run_bsc_parity_case(path, iters=None, tables="f64", stats="f64"):
     """GPU vs fixture (reference outputs) vs oracle; returns error summary."""
     c = load_case(path)
     total = int(c["iters"])
     iters = total if iters is None else min(iters, total)
-    gpu, gcont, gdata = run_gpu_case(c, iters)
+    gpu, gcont, gdata = run_gpu_case(c, iters, tables=tables, stats=stats)
     ora, ocont, odata = run_oracle_case(c, iters)
     res = {"F_err": 0.0, "W_err": 0.0, "pi_err": 0.0, "sigma_err": 0.0, "count_err": 0.0,
            "F_err_ref": 0.0, "W_err_ref": 0.0}
@@ -135,7 +160,10 @@ def run_bsc_parity_case(path, iters=None):
         res["sigma_err"] = max(res["sigma_err"], abs(tg["sigma"] - to["sigma"]) / abs(to["sigma"]))
         res["count_err"] = max(res["count_err"], abs(ag - ao), abs(bg - bo))
         res["F_err_ref"] = max(res["F_err_ref"], abs(Fg - c["F"][it]) / abs(c["F"][it]))
-        res["W_err_ref"] = max(res["W_err_ref"], maxrel(tg["W"], c["W"][it]))
+        if "W" in c:
+            res["W_err_ref"] = max(res["W_err_ref"], maxrel(tg["W"], c["W"][it]))
+        res["pi_err"] = max(res["pi_err"], abs(tg["pi"] - c["pi"][it]) / abs(c["pi"][it]))
+        res["sigma_err"] = max(res["sigma_err"], abs(tg["sigma"] - c["sigma"][it]) / abs(c["sigma"][it]))
     gss = gcont["ss"]
     res["ss_equal"] = bool(np.array_equal(gss, ocont["ss"]))
     res["lpj_err"] = maxrel(gcont["lpj"], ocont["lpj"])
@@ -155,6 +183,9 @@ PKEYS = ("W", "pies", "mus", "Psi", "sigma2")
 
 
 def _sssc_theta0(c):
+    if "sigma20" in c:  # BASELINE-shape fixture
+        return {"W": np.array(c["W0"]), "pies": np.array(c["pies0"]), "mus": np.array(c["mus0"]), "Psi": np.array(c["Psi0"]),
+                "sigma2": np.float64(c["sigma20"])}
     return {k: np.array(c[k + "0"]) for k in PKEYS}
 
 
@@ -223,11 +254,14 @@ def run_sssc_parity_case(path, iters=None):
         res["count_err"] = max(res["count_err"], abs(ag - ao), abs(bg - bo))
         for k in PKEYS:
             res[k + "_err"] = max(res[k + "_err"], maxrel(tg[k], to[k]))
-            res[k + "_err_ref"] = max(res[k + "_err_ref"], maxrel(tg[k], c[k][it]))
+            if k in c:
+                res[k + "_err_ref"] = max(res[k + "_err_ref"], maxrel(tg[k], c[k][it]))
     gss = gcont["ss"]
     res["ss_equal"] = bool(np.array_equal(gss, ocont["ss"]))
     res["lpj_err"] = maxrel(gcont["lpj"], ocont["lpj"])
     res["yrec_err"] = maxrel(gdata["y_reconstructed"], odata["y_reconstructed"])
+    if iters == total and "y_reconstructed" in c and np.asarray(c["y_reconstructed"]).size:
+        res["yrec_err_ref"] = maxrel(gdata["y_reconstructed"], c["y_reconstructed"])
     if iters == total:
         res["ss_equal_ref"] = bool(np.array_equal(gss, c["ss_final_bool"]))
         res["lpj_err_ref"] = maxrel(gcont["lpj"], c["lpj_final"])

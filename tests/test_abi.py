@@ -35,13 +35,16 @@ def test_struct_layouts_match_c():
 #include <stdio.h>
 #include <stddef.h>
 #include "evo_b200.h"
-int main(){printf("%zu %zu %zu %zu %zu\n", sizeof(evo_estep_args), offsetof(evo_estep_args, acc),
-  offsetof(evo_estep_args, W), sizeof(evo_es3c_stats_args), offsetof(evo_es3c_stats_args, Yrec));}
+int main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(evo_estep_args), offsetof(evo_estep_args, acc),
+  offsetof(evo_estep_args, W), sizeof(evo_es3c_stats_args), offsetof(evo_es3c_stats_args, Yrec),
+  sizeof(evo_evolve_args), offsetof(evo_evolve_args, pool0), offsetof(evo_evolve_args, ev_pool_n));}
 '''
     path = "/tmp/evo_abi_check.c"
     open(path, "w").write(prog)
     subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), path, "-o", "/tmp/evo_abi_check"])
-    a, b, c, d, e = map(int, subprocess.check_output(["/tmp/evo_abi_check"]).split())
+    a, b, c, d, e, f, g, h = map(int, subprocess.check_output(["/tmp/evo_abi_check"]).split())
+    assert ctypes.sizeof(_lib.EvolveArgs) == f
+    assert _lib.EvolveArgs.pool0.offset == g and _lib.EvolveArgs.ev_pool_n.offset == h
     assert ctypes.sizeof(_lib.EstepArgs) == a
     assert _lib.EstepArgs.acc.offset == b and _lib.EstepArgs.W.offset == c
     assert ctypes.sizeof(_lib.Es3cStatsArgs) == d and _lib.Es3cStatsArgs.Yrec.offset == e

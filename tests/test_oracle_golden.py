@@ -112,3 +112,48 @@ def test_sssc_oracle_lpj_fixture():
         got = OS.lpj_states(states[n], th, Y[n], X[n])[0]
         assert P.maxrel(got, z["lpj"][n]) < 1e-11
         assert abs(OS.lpj_allzero(Y[n], X[n], th["sigma2_inv"])[0] - z["lpj_allzero"][n]) <= 1e-13 * abs(z["lpj_allzero"][n])
+
+
+# ---- fixtures at the BASELINE shapes (tests/golden/make_golden_shapes.py) ---------------------------------
+@pytest.mark.parametrize("name", ["shape_cfg2", "shape_cfg5"])
+def test_oracle_replay_at_baseline_shape(name):
+    c = P.load_case(os.path.join(P.GOLDEN, name + ".npz"))  # regenerates Y / W0 from the seed and checks their SHA-1
+    iters = int(c["iters"])
+    out, cont, data = P.run_oracle_case(c, iters)
+    for it in range(iters):
+        F, a, b, th = out[it]
+        assert abs(F - c["F"][it]) <= 1e-11 * abs(c["F"][it])
+        assert abs(a - c["S_nunique"][it]) < 1e-12 and abs(b - c["S_sub"][it]) < 1e-12
+        assert abs(th["pi"] - c["pi"][it]) <= 1e-10 * c["pi"][it]
+        assert abs(th["sigma"] - c["sigma"][it]) <= 1e-10 * c["sigma"][it]
+    assert np.array_equal(cont["ss"], c["ss_final_bool"])
+    assert P.maxrel(cont["lpj"], c["lpj_final"]) < 1e-11
+
+
+@pytest.mark.parametrize("name", ["shape_cfg3", "shape_cfg4"])
+def test_sssc_oracle_replay_at_baseline_shape(name):
+    c = P.load_case(os.path.join(P.GOLDEN, name + ".npz"))
+    iters = int(c["iters"])
+    out, cont, data = P.run_oracle_sssc_case(c, iters)
+    for it in range(iters):
+        F, a, b, th = out[it]
+        assert abs(F - c["F"][it]) <= 1e-10 * abs(c["F"][it])
+        assert abs(a - c["S_nunique"][it]) < 1e-12 and abs(b - c["S_sub"][it]) < 1e-12
+        for k in ("pies", "mus", "sigma2"):
+            assert P.maxrel(th[k], c[k][it]) < 1e-7, k
+    assert np.array_equal(cont["ss"], c["ss_final_bool"])
+    assert P.maxrel(cont["lpj"], c["lpj_final"]) < 1e-9
+    assert P.maxrel(data["y_reconstructed"], c["y_reconstructed"]) < 1e-6  # stored as float32
+
+
+def test_sssc_oracle_lpj_larger_systems():
+    from oracle import sssc as OS
+
+    z = np.load(os.path.join(P.GOLDEN, "sssc_lpj_dense.npz"))
+    H = int(z["H"])
+    Y, X = z["Y"], z["X"]
+    states = np.unpackbits(z["states"], axis=-1)[..., :H].astype(bool)
+    assert states.sum(-1).max() > 32
+    th = OS.precompute({k: np.array(z[k]) for k in P.PKEYS}, Y.shape[1], Y.shape[0], int(X.sum()))
+    for n in range(Y.shape[0]):
+        assert P.maxrel(OS.lpj_states(states[n], th, Y[n], X[n])[0], z["lpj"][n]) < 1e-9

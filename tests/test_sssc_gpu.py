@@ -50,3 +50,51 @@ def test_sssc_lpj_fixture():
     data = {"y": np.where(X, Y, np.nan), "x_infr": X}
     got = m.lpj_all(dict(th), data, pack_states(states, m.device)).cpu().numpy()
     assert P.maxrel(got, z["lpj"]) < 1e-10
+
+
+@pytest.mark.parametrize("name", ["shape_cfg3", "shape_cfg4"])
+def test_sssc_trajectory_at_baseline_shape(name):
+    """Replayed reference runs at the cfg3 / cfg4 shapes (D=144, H=512, K=64, 128 children per datapoint, dense
+    Psi; cfg4: 30 % of the entries missing); W and Psi fixed (N < H), pies / mus / sigma2 learned."""
+    res = P.run_sssc_parity_case(os.path.join(P.GOLDEN, name + ".npz"))
+    assert res["ss_equal"] and res["ss_equal_ref"], res
+    assert res["count_err"] == 0.0, res
+    for k in ("F_err", "F_err_ref", "lpj_err", "lpj_err_ref"):
+        assert res[k] < 1e-7, (k, res)
+    for k in ("pies", "mus", "sigma2"):
+        assert res[k + "_err"] < 1e-6 and res[k + "_err_ref"] < 1e-6, (k, res)
+    assert res["yrec_err"] < 1e-5 and res["yrec_err_ref"] < 1e-5, res
+
+
+def test_sssc_lpj_larger_systems():
+    """sssc_lpj_dense.npz: reference values for states with 1..8 (four per warp), 9..16 (shared memory),
+    17..32 (global scratch) active latents, H = 80, non-symmetric dense Psi, complete and incomplete rows.
+    States with MORE than 32 active latents are deliberately not evaluated: they get the lowest log-joint
+    (f64 min, what lpj_reset_check gives a NaN) -- a documented difference."""
+    from evo_b200.sssc import SSSC
+    from evo_b200.variational import pack_states
+
+    z = np.load(os.path.join(P.GOLDEN, "sssc_lpj_dense.npz"))
+    H = int(z["H"])
+    Y, X = z["Y"], z["X"]
+    states = np.unpackbits(z["states"], axis=-1)[..., :H].astype(bool)
+    sizes = states.sum(-1)
+    N, S, _ = states.shape
+    D = Y.shape[1]
+    m = SSSC(D, H, S)
+    th = {k: np.array(z[k]) for k in P.PKEYS}
+    th["sigma2"] = np.float64(th["sigma2"])
+    data = {"y": np.where(X, Y, np.nan), "x_infr": X}
+    got = m.lpj_all(dict(th), data, pack_states(states, m.device)).cpu().numpy()
+    ok = sizes <= 32
+    assert (sizes > 16).any() and (sizes[ok] > 16).any() and (~ok).any()
+    for lo, hi in ((1, 8), (9, 16), (17, 32)):
+        sel = (sizes >= lo) & (sizes <= hi)
+        assert sel.any()
+        assert P.maxrel(got[sel], z["lpj"][sel]) < 1e-9, (lo, hi, np.abs(got[sel] - z["lpj"][sel]).max())
+    assert (got[~ok] == np.finfo(np.float64).min).all()
+    # complete rows alone go through the Gram gather (G = W'W, b = W'y) instead of the masked accumulation
+    rows = [n for n in range(N) if X[n].all()]
+    data2 = {"y": Y[rows], "x_infr": X[rows]}
+    got2 = m.lpj_all(dict(th), data2, pack_states(states[rows], m.device)).cpu().numpy()
+    assert P.maxrel(got2[ok[rows]], z["lpj"][rows][ok[rows]]) < 1e-9
