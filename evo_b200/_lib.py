@@ -63,7 +63,7 @@ class Es3cStatsArgs(C.Structure):
         ("states", C.c_void_p), ("lpj", C.c_void_p), ("Y", C.c_void_p), ("mask", C.c_void_p),
         ("recon_keep", C.c_void_p), ("G", C.c_void_p), ("B", C.c_void_p), ("ynorm2", C.c_void_p),
         ("Wt", C.c_void_p), ("Psi", C.c_void_p), ("mus", C.c_void_p),
-        ("sigma2", C.c_double), ("stats", C.c_void_p), ("Yrec", C.c_void_p),
+        ("sigma2", C.c_double), ("stats", C.c_void_p), ("Yrec", C.c_void_p), ("q_skip", C.c_double),
     ]
 
 

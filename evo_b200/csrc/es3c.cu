@@ -79,7 +79,6 @@ __device__ __forceinline__ void gj_inverse(int a, double *A3, double *R, int ld,
   __syncwarp();
 }
 
-constexpr double ES3C_Q_SKIP = 1e-18;
 
 template <int T>
 __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a, Es3cEval ev) {
@@ -122,7 +121,7 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
     const uint32_t *stn = a.states + n * (int64_t)S * Hw;
     for (int k = warp; k < S; k += T / 32) {
       double qk = q[a.S_perm + k];
-      if (!(qk > ES3C_Q_SKIP)) continue;
+      if (!(qk > a.q_skip)) continue;
       uint16_t *idx;
       double *A1, *A2, *A3;
       int ld;

@@ -39,6 +39,8 @@ class SSSC(Model):
         self.eps_Psi = self.eps_sigma2 = tol
         self.dtype_precision = precision
         self.use_storage = use_storage  # the reference's per-state cache; nothing to cache here
+        # statistics pass: states with posterior weight below this are not expanded (include/evo_b200.h, q_skip)
+        self.q_skip = 1e-30
         self.noise_policy = {
             "W": (-np.inf, +np.inf, False, None),
             "pies": (tol, 1.0 - tol, False, None),
@@ -205,6 +207,7 @@ class SSSC(Model):
         a.sigma2 = float(model_params["sigma2"])
         a.stats = stats.data_ptr()
         a.Yrec = dd.Yrec.data_ptr() if do_reconstruction else None
+        a.q_skip = float(self.q_skip)
         with torch.cuda.device(self.device):
             ev = self._tick()
             _lib.check(self.lib.evo_es3c_suffstats(C.byref(a), _lib.stream()), "evo_es3c_suffstats")

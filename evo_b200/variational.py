@@ -49,6 +49,17 @@ class Operator:
         return "Operator(%s:%s)" % (self.kind, self.name)
 
 
+fitparents = Operator("parent_selection", "fit")
+randparents = Operator("parent_selection", "rand")
+randflip = Operator("mutation_algorithm", "randflip")
+sparseflip = Operator("mutation_algorithm", "sparseflip")
+cross = Operator("mutation_algorithm", "cross")
+cross_randflip = Operator("mutation_algorithm", "cross_randflip")
+cross_sparseflip = Operator("mutation_algorithm", "cross_sparseflip")
+_SELECTION = {"fit": fitparents, "rand": randparents}
+_MUTATION = {"randflip": randflip, "sparseflip": sparseflip, "cross": cross,
+             "cross_randflip": cross_randflip, "cross_sparseflip": cross_sparseflip}
+
 OPERATOR_SEED = 0x5EED
 _CALLS = [0]
 

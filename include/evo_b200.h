@@ -254,6 +254,10 @@ typedef struct evo_es3c_stats_args {
   double sigma2;
   double *stats;
   float *Yrec;            /* [N][D] or NULL */
+  double q_skip;          /* states with posterior weight q <= q_skip are not expanded (their slab moments cost a
+                           * factorisation each).  The mus update divides by sum_n <s_h> + 2.2e-16 (sssc.py:726), so the
+                           * weight dropped per latent must stay far below that: 1e-30 bounds the relative change of
+                           * every mu_h by 64 N 1e-30 / 2.2e-16 (< 1e-7 up to N = 3e5); 0 expands every state */
 } evo_es3c_stats_args;
 int evo_es3c_suffstats(const evo_es3c_stats_args *args, void *stream);
 

@@ -77,7 +77,8 @@ class OracleReplay:
 
     def mutate(self, parents, n_children, sparseness, p_bf):
         k = int(self.counts[self.it, self.n, self.g])
-        return self.children[self.it, self.n, self.g, :k].copy()
+        # with a background unit the operators see the first H-1 latents only (eas.py:215-218,233-239)
+        return self.children[self.it, self.n, self.g, :k, :parents.shape[1]].copy()
 
     def next_iteration(self):
         self.it += 1

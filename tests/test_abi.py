@@ -36,7 +36,7 @@ def test_struct_layouts_match_c():
 #include <stddef.h>
 #include "evo_b200.h"
 int main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(evo_estep_args), offsetof(evo_estep_args, acc),
-  offsetof(evo_estep_args, W), sizeof(evo_es3c_stats_args), offsetof(evo_es3c_stats_args, Yrec),
+  offsetof(evo_estep_args, W), sizeof(evo_es3c_stats_args), offsetof(evo_es3c_stats_args, q_skip),
   sizeof(evo_evolve_args), offsetof(evo_evolve_args, pool0), offsetof(evo_evolve_args, ev_pool_n));}
 '''
     path = "/tmp/evo_abi_check.c"
@@ -47,7 +47,7 @@ int main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(evo_estep_args), o
     assert _lib.EvolveArgs.pool0.offset == g and _lib.EvolveArgs.ev_pool_n.offset == h
     assert ctypes.sizeof(_lib.EstepArgs) == a
     assert _lib.EstepArgs.acc.offset == b and _lib.EstepArgs.W.offset == c
-    assert ctypes.sizeof(_lib.Es3cStatsArgs) == d and _lib.Es3cStatsArgs.Yrec.offset == e
+    assert ctypes.sizeof(_lib.Es3cStatsArgs) == d and _lib.Es3cStatsArgs.q_skip.offset == e
 
 
 def test_missing_library_fails_loudly(monkeypatch):

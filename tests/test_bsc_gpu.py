@@ -47,14 +47,21 @@ def test_trajectory_at_baseline_shape(name):
 @pytest.mark.parametrize("name", ["bsc_bars_replay", "bsc_cross", "shape_cfg2", "shape_cfg5"])
 def test_trajectory_with_tensor_core_tables(name):
     """The configuration bench.py times (`tables="tc"`, `stats="tc"`: B = Y W and Wp through fp16 hi+lo split
-    tcgen05 GEMMs) on the recorded trajectories: stated bound 1e-5 on lpj / F / parameters; K sets may differ from
-    the f64 path only where two candidates' lpj are closer than that bound, so they are compared through lpj."""
-    res = P.run_bsc_parity_case(os.path.join(P.GOLDEN, name + ".npz"), tables="tc", stats="tc")
-    for k in ("F_err", "F_err_ref", "pi_err", "sigma_err"):
-        assert res[k] < 1e-5, (k, res)
-    assert res["W_err"] < 1e-4 and res["W_err_ref"] < 1e-4, res
+    tcgen05 GEMMs) on the recorded trajectories.  Stated bound: 1e-5 on lpj / F / parameters for ONE EM iteration
+    from identical parameters (per-call bounds: tests/test_dense_gpu.py); over a recorded trajectory of n <= 6
+    iterations the deviations compound through the parameters, bound 1e-4.  K sets may differ from the f64 path
+    only where two candidates' lpj are closer than that, so lpj is compared when they agree."""
+    path = os.path.join(P.GOLDEN, name + ".npz")
+    one = P.run_bsc_parity_case(path, iters=1, tables="tc", stats="tc")
+    for k in ("F_err", "F_err_ref", "pi_err", "sigma_err", "W_err", "W_err_ref"):
+        assert one[k] < 1e-5, (k, one)
+    if one["ss_equal"]:
+        assert one["lpj_err"] < 1e-5, one
+    res = P.run_bsc_parity_case(path, tables="tc", stats="tc")
+    for k in ("F_err", "F_err_ref", "pi_err", "sigma_err", "W_err", "W_err_ref"):
+        assert res[k] < 1e-4, (k, res)
     if res["ss_equal"]:
-        assert res["lpj_err"] < 1e-5, res
+        assert res["lpj_err"] < 1e-4, res
 
 
 def test_lpj_fixture_direct_and_gram():
