@@ -1,13 +1,16 @@
 #!/usr/bin/env python
 """Benchmark of the evo hot path (truncated-variational E-step + M-step) on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg5] [--impl ours|reference]
 
 A "step" is one EM iteration (`model.step`: E-step over every datapoint of the shard, sufficient
 statistics, all-reduce, parameter update) on synthetic data of the shape BASELINE.json names.
 Metric: log-joints evaluated per second (whole job, all ranks); EM iterations/s rides along.
-Weak scaling: every rank owns N datapoints of the workload (no data-path collective; the only
-collective is the all-reduce of the packed sufficient statistics).
+Default workload: cfg5 (the large BSC config BASELINE.json quotes the scaling metric on), N = 1 000 000
+datapoints IN TOTAL, sharded over the ranks by the reference's array_split rule -- STRONG scaling.  The
+dataset is one dataset whatever the rank count: row n is a pure function of (seed, n) (Philox streams,
+`evo_generate_data` on the device, oracle/datagen.py for the CPU arm), generated from ONE dictionary.
+The only collective is the all-reduce of the packed sufficient statistics.
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -24,7 +27,7 @@ sys.path.insert(0, ROOT)
 
 # synthetic inputs and EA hyper-parameters per config
 WORKLOADS = {
-    # name: model, D, H, N (per GPU), K, (selection, mutation, parents, children, generations), active latents
+    # name: model, D, H, N (total), K, (selection, mutation, parents, children, generations), active latents
     "cfg1": dict(model="bsc", D=25, H=10, N=1000, K=20, ea=("fit", "randflip", 10, 1, 1), act=2.0, bars=True),
     "cfg2": dict(model="bsc", D=256, H=300, N=100000, K=64, ea=("fit", "randflip", 8, 8, 2), act=5.0),
     "cfg5": dict(model="bsc", D=1024, H=1024, N=1000000, K=128, ea=("fit", "randflip", 16, 8, 2), act=8.0),
@@ -34,17 +37,21 @@ WORKLOADS = {
 DESCR = {
     "cfg1": "examples/bars-test BSC, 5x5 bars (D=25, H=10), N=1000, K=20",
     "cfg2": "BSC feature learning, synthetic 16x16 patches (D=256, H=300), N=100k, K=64",
-    "cfg5": "large-scale BSC (D=1024, H=1024), N=1M, K=128",
-    "cfg3": "ES3C image denoising, synthetic 12x12 patches (D=144, H=512), N=250k, K=64",
+    "cfg5": "large-scale BSC scaling sweep (D=1024, H=1024), N=1M, K=128",
+    "cfg3": "ES3C image denoising, synthetic 12x12 noisy patches (D=144, H=512), N=250k, K=64",
     "cfg4": "ES3C image inpainting, 30% missing (D=144, H=512), N=250k, K=64",
 }
 METRIC, UNIT = "log_joints_per_sec", "log-joints/s"
+DATA_SEED, DICT_SEED = 1000, 7
 
 
-def synth_host(w, N, seed):
-    """Synthetic dataset with NumPy's legacy RandomState -- used by the CPU arm and,
-    through the same recipe on the device, by the GPU arm."""
-    rng = np.random.RandomState(seed)
+# ---------------------------------------------------------------------------------------------
+# ONE dataset per workload: generating parameters from a fixed legacy RandomState (identical on every
+# rank and in the CPU arm), rows from Philox streams keyed by the GLOBAL row index.
+# ---------------------------------------------------------------------------------------------
+def gen_params(w):
+    """Generating parameters of SURVEY 8(d): W_gen ~ N(0,1) (bars for cfg1), s ~ Bernoulli(act/H),
+    ES3C z ~ N(1, I), noise N(0,1)."""
     D, H = w["D"], w["H"]
     if w.get("bars"):
         R = H // 2
@@ -54,41 +61,51 @@ def synth_host(w, N, seed):
             Wg[:, i, R + i] = 10.0
         Wg = Wg.reshape(R * R, H)
     else:
-        Wg = rng.normal(size=(D, H))
-    s = rng.random_sample((N, H)) < w["act"] / H
+        Wg = np.random.RandomState(DICT_SEED).normal(size=(D, H))
+    th = {"W": Wg, "pies": np.full(H, w["act"] / H)}
     if w["model"] == "es3c":
-        z = rng.normal(loc=1.0, size=(N, H))
-        Y = (s * z) @ Wg.T + rng.normal(size=(N, D))
+        th.update({"mus": np.ones(H), "Psi": np.eye(H), "sigma2": np.float64(1.0)})
     else:
-        Y = s.astype(np.float64) @ Wg.T + rng.normal(size=(N, D))
-    Y = Y.astype(np.float32)
-    X = None
-    if w.get("missing"):
-        X = rng.random_sample((N, D)) >= w["missing"]
-    return Y, X
+        th["sigma"] = 1.0
+    return th
 
 
-def synth_device(w, N, seed, device):
+def _hash_u32(x):
+    """lowbias32-style integer hash on values held in 64-bit lanes (same arithmetic in NumPy and torch)."""
+    x = x & 0xFFFFFFFF
+    x = ((x ^ (x >> 16)) * 0x7FEB352D) & 0xFFFFFFFF
+    x = ((x ^ (x >> 15)) * 0x846CA68B) & 0xFFFFFFFF
+    return x ^ (x >> 16)
+
+
+def observed_mask(rows, D, p_missing, xp):
+    """Entry (n, d) is missing with probability p: a hash of the GLOBAL entry index (sharding independent)."""
+    idx = rows[:, None] * D + xp.arange(D)[None, :]
+    return _hash_u32(idx + 0x9E3779B9) >= int(p_missing * 4294967296.0)
+
+
+def host_rows(w, rows):
+    """Rows `rows` (global indices) of the workload's dataset on the host (the CPU arm's sample)."""
+    from oracle import datagen as DG
+
+    g = gen_params(w)
+    if w["model"] == "es3c":
+        out = DG.generate(g["W"], g["pies"], 1.0, rows, DATA_SEED, mus=g["mus"], Psi=g["Psi"], psi_diag=True)
+    else:
+        out = DG.generate(g["W"], g["pies"], g["sigma"], rows, DATA_SEED)
+    X = observed_mask(np.asarray(rows, dtype=np.int64), w["D"], w["missing"], np) if w.get("missing") else None
+    return out["y"], X
+
+
+def device_rows(model, w, lo, hi, device):
+    """Rows [lo, hi) of the same dataset, generated on the device by `evo_generate_data`."""
     import torch
 
-    g = torch.Generator(device=device)
-    g.manual_seed(seed)
-    D, H = w["D"], w["H"]
-    if w.get("bars"):
-        Y, X = synth_host(w, N, seed)
-        return torch.as_tensor(Y, device=device), None
-    Wg = torch.randn((D, H), generator=g, device=device)
-    Y = torch.empty((N, D), dtype=torch.float32, device=device)
+    g = gen_params(w)
+    Y = model.generate_data(g, hi - lo, seed=DATA_SEED, n_offset=lo, device_only=True)["y_dev"]
     X = None
-    chunk = 65536
-    for lo in range(0, N, chunk):
-        hi = min(N, lo + chunk)
-        s = (torch.rand((hi - lo, H), generator=g, device=device) < w["act"] / H).float()
-        if w["model"] == "es3c":
-            s = s * (1.0 + torch.randn((hi - lo, H), generator=g, device=device))
-        Y[lo:hi] = s @ Wg.T + torch.randn((hi - lo, D), generator=g, device=device)
     if w.get("missing"):
-        X = torch.rand((N, D), generator=g, device=device) >= w["missing"]
+        X = observed_mask(torch.arange(lo, hi, dtype=torch.int64, device=device), w["D"], w["missing"], torch)
     return Y, X
 
 
@@ -239,7 +256,7 @@ def run_lpj_compare(args):
     D, H, K = w["D"], w["H"], w["K"]
     Hw = (H + 31) // 32
     model = BSC(D, H, K, device=device)
-    Y, X = synth_device(w, N, 1000, device)
+    Y, X = device_rows(model, w, 0, N, device)
     data = {"y": Y, "x_infr": None}
     np.random.seed(1)
     theta = model.check_params(model.standard_init(data))
@@ -286,18 +303,13 @@ def run_lpj_compare(args):
     print(json.dumps(line), flush=True)
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per call from the `ncu --set full` capture of exactly the
-# default command (E-step: profiles/r01i_cfg2_full_estep_ncu_summary.txt, the other calls:
-# profiles/r01g_cfg2_full_ncu_summary.txt -- unchanged kernels; a call = all its kernels); None where no
-# capture at that size exists.
-NCU_TRAFFIC = {("cfg2", 100000): {
-    # list kernel + packed-bits pass over the overflow list
-    "evo_estep": 497.574656e6 + 97.439744e6 + 0.063488e6,
-    # statistics pass + split-K Wp GEMM (the memset of the <s> planes, 154 MB, is not a kernel)
-    "evo_bsc_suffstats_tc": 413.756672e6 + 141.957888e6 + 260.738560e6 + 6.116864e6,
-    # wmax + W' split + table GEMM
-    "evo_bsc_tables_tc": 0.620288e6 + 0.629760e6 + 167.747072e6 + 188.397568e6,
-    "evo_bsc_prepare": 0.621568e6}}
+# dram__bytes_read.sum + dram__bytes_write.sum per call from the `ncu --set full` capture of the same command
+# (profiles/, named per round); None where no capture at that size exists.  Filled by tools/ncu_traffic.py.
+NCU_TRAFFIC = {}
+try:
+    NCU_TRAFFIC = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+except Exception:
+    pass
 
 
 def measured_peaks():
@@ -306,6 +318,154 @@ def measured_peaks():
         j = json.load(open(p))
         return float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def workload_config(name, w, N_total, world, args):
+    return {"workload": "%s: %s" % (name, DESCR[name]), "N_total": N_total,
+            "ea": "%s/%s parents=%d children=%d generations=%d" % tuple(w["ea"]),
+            "dataset": "one synthetic dataset, row n = f(seed %d, n) from one dictionary (seed %d)" % (DATA_SEED, DICT_SEED),
+            "l2": "inputs larger than L2 (K sets + tables > 126 MB per GPU)" if (N_total // world) * w["K"] * 4 * ((w["H"] + 31) // 32) > 126e6
+            else "working set fits L2 (small reference config)",
+            "tables": ("B = Y W by tcgen05 fp16 hi+lo split GEMM (lpj within 1e-5 of f64)" if args.tables == "tc"
+                       else "f64 SIMT GEMM") if w["model"] == "bsc" else "f64",
+            "statistics": ("Wp = <S>'Y by split-K tcgen05 fp16 hi+lo GEMM (within 1e-5 of max|Wp|), Wq/pi/sigma f64"
+                           if args.stats in ("tc", "auto") else "f64") if w["model"] == "bsc" else "f64",
+            "parallelism": "dp%d over N (array_split shards of one dataset)" % world}
+
+
+def dtype_string(w, args):
+    if w["model"] == "bsc" and (args.tables == "tc" or args.stats in ("tc", "auto")):
+        return "f64 + fp16x2-split tensor-core tables (fp32 accumulate)"
+    return "f64"
+
+
+class Job:
+    """One workload on this rank's shard: model, resident data, parameters, K sets."""
+
+    def __init__(self, name, N_total, args, rank, world, device, comm):
+        import torch
+
+        from evo_b200.comm import shard_bounds
+        from evo_b200.variational import init_states
+
+        self.name, self.w = name, WORKLOADS[name]
+        w = self.w
+        self.N_total = N_total
+        self.lo, self.hi = shard_bounds(N_total, world, rank)
+        self.N = self.hi - self.lo
+        self.device, self.world, self.rank = device, world, rank
+        if w["model"] == "bsc":
+            from evo_b200.bsc import BSC
+            self.model = BSC(w["D"], w["H"], w["K"], comm=comm, device=device)
+            self.model.tables, self.model.stats = args.tables, args.stats
+        else:
+            from evo_b200.sssc import SSSC
+            learn = ("W", "pies", "sigma2") if w.get("missing") else ("W", "pies", "mus", "sigma2", "Psi")
+            self.model = SSSC(w["D"], w["H"], w["K"], to_learn=learn, comm=comm, device=device)
+        Y, X = device_rows(self.model, w, self.lo, self.hi, device)
+        self.data = {"y": Y, "x_infr": X}
+        if X is not None:
+            self.data["x"] = X
+        np.random.seed(1)
+        theta = self.model.check_params(self.model.standard_init(self.data))
+        for k in list(theta):
+            if isinstance(theta[k], np.ndarray) and theta[k].ndim >= 1:
+                theta[k] = torch.as_tensor(theta[k], device=device)  # device-resident parameters
+        self.theta = theta
+        sel, mut, P, C, G = w["ea"]
+        self.cont = init_states(self.N, w["K"], w["H"], sel, mut, P, C, G, device=device, seed=0x5EED, n_offset=self.lo)
+        self.recon = bool(w.get("missing")) or w["model"] == "es3c"
+        self.iters_done = 0
+
+    def step(self):
+        F, nu, nsub, self.theta = self.model.step(self.theta, self.cont, self.data, do_reconstruction=self.recon)
+        self.iters_done += 1
+        return F, nu, self.model.last_counts["lpj_evaluated"]
+
+    def mean_active(self, sample=2000):
+        """mean |s|, |s|^2, |s|^3 over the K sets of the first datapoints of the shard"""
+        from evo_b200.variational import unpack_states
+
+        n = min(sample, self.N)
+        a = unpack_states(self.cont["ss_dev"][:n], self.w["H"]).sum(-1).double()
+        return float(a.mean().item()), float((a * a).mean().item()), float((a ** 3).mean().item())
+
+
+def timed_window(job, steps, barrier, sampler=None):
+    """`steps` EM iterations between CUDA events on the launching stream; per-call kernel times alongside."""
+    import torch
+
+    from evo_b200 import _lib
+
+    lib = _lib.load()
+    job.model.timing = []
+    barrier()
+    if sampler is not None:
+        sampler.mark()
+    l0 = lib.evo_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    lpj_total, U_sum, F = 0.0, 0.0, None
+    for _ in range(steps):
+        F, nu, cnt = job.step()
+        lpj_total += cnt
+        U_sum += nu
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=job.device)
+    if job.world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    kern = job.model.timing_summary()
+    job.model.timing = None
+    return {"ms": float(ms.item()), "lpj": lpj_total, "U_mean": U_sum / steps, "F": F, "kern": kern,
+            "launches": int(lib.evo_launch_count() - l0)}
+
+
+def roofline_of(job, win, peak, peak_src, fma=None):
+    """`roofline` of the dominant call: algorithmic bytes / its mean CUDA-event duration / measured HBM
+    peak; for the ES3C E-step also the algorithmic flops against the measured FMA peaks (bound = max of the two)."""
+    w, kern = job.w, win["kern"]
+    own = {k: v for k, v in kern.items() if k.startswith("evo_")}
+    alg = algorithmic_bytes(w, job.N, win["U_mean"])
+    dom = max(own, key=lambda k: own[k][0] * own[k][1])
+    if dom not in alg:
+        return None
+    ach = alg[dom] / (kern[dom][1] * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": (NCU_TRAFFIC.get("%s:%d" % (job.name, job.N), {}) or {}).get(dom), "peak_source": peak_src,
+            "launch_ms": kern[dom][1], "algorithmic_bytes_per_launch": alg[dom]}
+    if w["model"] == "es3c" and fma:
+        a1, a2, a3 = job.mean_active()
+        d_obs = w["D"] * (1.0 - w.get("missing", 0.0))
+        flop_lpj = d_obs * (a2 + 5 * a1) + 2.0 / 3.0 * a3 + 2 * a2
+        t = kern["evo_estep"][1] * 1e-3
+        lpj_launch = win["lpj"] / max(1, kern["evo_estep"][0]) / job.world
+        tf = flop_lpj * lpj_launch / t / 1e12
+        roof["simt"] = {"algorithmic_flop_per_lpj": flop_lpj, "mean_active": a1, "achieved_TFLOPs": tf,
+                        "fp32_fma_peak_TFLOPs": fma[32], "fp64_fma_peak_TFLOPs": fma[64],
+                        "frac_of_fp32_peak": tf / fma[32], "frac_of_fp64_peak": tf / fma[64],
+                        "note": "kernel arithmetic is f64; SURVEY 8(d)(b) formula D_obs(a^2+5a)+2/3a^3+2a^2 at the measured moments of |s|"}
+    return roof
+
+
+def kernels_record(win):
+    kern = win["kern"]
+    tot = sum(c * t for c, t in kern.values())
+    return {k: {"launches": c, "mean_ms": t, "share": c * t / tot} for k, (c, t) in kern.items()}
+
+
+def comm_record(win, steps, world, nbytes):
+    """all-reduce time per step and bus bandwidth of the packed statistics (the only collective), and the time of the
+    replicated parameter solve -- the two terms that do not shrink with the rank count."""
+    out = {}
+    k = win["kern"].get("allreduce")
+    if k:
+        bus = (2.0 * (world - 1) / world) * nbytes / (k[1] * 1e-3) / 1e9 if world > 1 and k[1] > 0 else 0.0
+        out.update({"allreduce_ms_per_step": k[1] * k[0] / steps, "bytes": nbytes, "bus_GBps": bus})
+    if "solve" in win["kern"]:
+        out["replicated_solve_ms_per_step"] = win["kern"]["solve"][1] * win["kern"]["solve"][0] / steps
+    return out or None
 
 
 def run_ours(args):
@@ -321,83 +481,54 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=device)
     from evo_b200 import _lib
     from evo_b200.comm import Comm
-    from evo_b200.variational import init_states
 
-    w = WORKLOADS[args.workload]
-    N = args.n if args.n else w["N"]
-    comm = Comm()
-    if w["model"] == "bsc":
-        from evo_b200.bsc import BSC
-        model = BSC(w["D"], w["H"], w["K"], comm=comm, device=device)
-        model.tables = args.tables
-        model.stats = args.stats
-    else:
-        from evo_b200.sssc import SSSC
-        model = SSSC(w["D"], w["H"], w["K"], comm=comm, device=device)
     lib = _lib.load()
-
-    Y, X = synth_device(w, N, 1000 + rank, device)
-    data = {"y": Y, "x_infr": X}
-    if X is not None:
-        data["x"] = X
-    np.random.seed(1)
-    theta = model.check_params(model.standard_init(data))
-    for k in list(theta):
-        if isinstance(theta[k], np.ndarray) and theta[k].ndim >= 1:
-            theta[k] = torch.as_tensor(theta[k], device=device)  # device-resident parameters
-    sel, mut, P, C, G = w["ea"]
-    cont = init_states(N, w["K"], w["H"], sel, mut, P, C, G, device=device, seed=0x5EED, n_offset=rank * N)
-    recon = bool(w.get("missing")) or w["model"] == "es3c"
+    comm = Comm()
+    name = args.workload
+    w = WORKLOADS[name]
+    N_total = args.n if args.n else w["N"]
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def one_step(th):
-        F, nu, nsub, th = model.step(th, cont, data, do_reconstruction=recon)
-        return F, nu, nsub, th, model.last_counts["lpj_evaluated"]
-
+    peak, peak_src = measured_peaks()
+    fma = None
+    if rank == 0:  # measured FP32 / FP64 FMA peaks (the SIMT denominators of the ES3C roofline)
+        import ctypes
+        fma = {}
+        for bits in (32, 64):
+            v = ctypes.c_double(0.0)
+            _lib.check(lib.evo_fma_peak(bits, 4096, ctypes.byref(v)), "evo_fma_peak")
+            fma[bits] = v.value
+    job = Job(name, N_total, args, rank, world, device, comm)
+    model, data, cont = job.model, job.data, job.cont
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()  # nvidia-smi needs ~0.1 s before its first sample: started ahead, marked below
     for _ in range(args.warmup):
-        F, nu, nsub, theta, _ = one_step(theta)
+        job.step()
     # snapshot of (theta, K sets, lpj, iteration counter): the end-to-end loop below restarts from it, so both
     # timed regions run the SAME EM iterations (the cost of an iteration grows as the states get denser)
-    snap = {"theta": {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in theta.items()},
+    snap = {"theta": {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in job.theta.items()},
             "ss": cont["ss_dev"].clone(), "lpj": cont["lpj_dev"].clone(), "iteration": cont.get("iteration", 0)}
     # ---- timed region: inputs resident in HBM ------------------------------------------------
-    model.timing = []
-    barrier()
-    if rank == 0:
-        sampler.mark()
-    l0 = lib.evo_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    lpj_total, U_sum = 0.0, 0.0
-    for _ in range(args.steps):
-        F, nu, nsub, theta, cnt = one_step(theta)
-        lpj_total += cnt
-        U_sum += nu
-    e1.record()
-    barrier()
+    win = timed_window(job, args.steps, barrier, sampler if rank == 0 else None)
     clocks = sampler.stop() if rank == 0 else None
-    launches = lib.evo_launch_count() - l0
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms = float(ms.item())
-    kern = model.timing_summary()
-    model.timing = None
+    ms, lpj_total, F = win["ms"], win["lpj"], win["F"]
+    act_timed = job.mean_active()[0]
+    roof = roofline_of(job, win, peak, peak_src, fma) if rank == 0 else None
+    comm_rec = comm_record(win, args.steps, world, int(model.last_counts.get("stats_bytes", 0)))
 
     # ---- end to end: batch arrives from pinned host memory, parameters and result go back ------
+    Y = data["y"]
     Yh = torch.empty(Y.shape, dtype=Y.dtype, pin_memory=True)
     Yh.copy_(Y)
     hdata = dict(data)
     hdata["y"] = Yh
-    model._data = {id(Yh): model.device_data(data)}  # same resident shard, now fed from the host buffer
-    th_host = {k: (v.cpu().numpy() if isinstance(v, torch.Tensor) else v) for k, v in theta.items()}
+    model.rebind_data(data, hdata)  # same resident shard, now fed from the host buffer
+    th_host = {k: (v.cpu().numpy() if isinstance(v, torch.Tensor) else v) for k, v in job.theta.items()}
     h2d = Yh.numel() * Yh.element_size() + sum(v.nbytes for v in th_host.values() if isinstance(v, np.ndarray))
     d2h = sum(v.nbytes for v in th_host.values() if isinstance(v, np.ndarray)) + 8 * 8
 
@@ -411,9 +542,7 @@ def run_ours(args):
                for k, v in th.items()}
         if not last:
             model.stage_data(hdata)
-            if os.environ.get("EVO_BENCH_E2E_SERIAL"):  # diagnostic: no copy/compute overlap
-                torch.cuda.current_stream().wait_stream(model._copy_stream)
-        F, nu, nsub, thd = model.step(thd, cont, hdata, do_reconstruction=recon)
+        F, nu, nsub, thd = model.step(thd, cont, hdata, do_reconstruction=job.recon)
         th = {k: (v.cpu().numpy() if isinstance(v, torch.Tensor) else v) for k, v in thd.items()}
         return th, model.last_counts["lpj_evaluated"]
 
@@ -433,80 +562,86 @@ def run_ours(args):
     g0.record()
     e2e_lpj = 0.0
     model.stage_data(hdata)  # the staged copy left by the warm-up is overwritten: steps copies for steps steps
-    prof = None
-    if os.environ.get("EVO_BENCH_PROFILE"):
-        import cProfile
-        prof = cProfile.Profile()
-        prof.enable()
-    if os.environ.get("EVO_BENCH_E2E_KERNELS"):  # diagnostic: per-call device time inside the e2e loop (stderr)
-        model.timing = []
     for i in range(args.steps):
         th_host, cnt = e2e_step(th_host, i == args.steps - 1)
         e2e_lpj += cnt
-    if prof is not None:
-        import pstats
-        prof.disable()
-        pstats.Stats(prof, stream=sys.stderr).sort_stats("cumulative").print_stats(30)
     g1.record()
     barrier()
     e2e_ms = torch.tensor([max(g0.elapsed_time(g1), (time.perf_counter() - t0) * 1e3)], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
     e2e_ms = float(e2e_ms.item())
-    if model.timing is not None:
-        print("e2e kernels:", {k: round(v[1], 3) for k, v in model.timing_summary().items()}, file=sys.stderr)
-        model.timing = None
+    # back to device-resident parameters for the later windows
+    model.rebind_data(hdata, data)
+    job.theta = {k: (torch.as_tensor(v, device=device) if isinstance(v, np.ndarray) and v.ndim >= 1 else v)
+                 for k, v in th_host.items()}
+    del Yh, hdata
+
+    # ---- converged window: the E-step gets dearer as the states densify ----------
+    at_density = None
+    if args.density_iters > 0:
+        while job.iters_done < args.density_iters:
+            job.step()
+        k2 = max(3, min(args.steps, 5))
+        win2 = timed_window(job, k2, barrier)
+        at_density = {"after_iterations": job.iters_done - k2, "steps": k2, "ms_per_step": win2["ms"] / k2,
+                      "value": win2["lpj"] / (win2["ms"] * 1e-3), "mean_active_latents_per_state": job.mean_active()[0],
+                      "free_energy": win2["F"], "kernels": kernels_record(win2)}
+
+    # ---- short sub-records of the other single-GPU workloads (N = 1 only) -------------------------------------
+    also = {}
+    if world == 1 and not args.no_also:
+        for other in [x for x in ("cfg2", "cfg3", "cfg4", "cfg1") if x != name]:
+            j2 = Job(other, WORKLOADS[other]["N"], args, rank, world, device, comm)
+            for _ in range(3):
+                j2.step()
+            w2 = timed_window(j2, 3, barrier)
+            also[other] = {"config": workload_config(other, j2.w, j2.N_total, world, args), "steps": 3, "warmup": 3,
+                           "ms_per_step": w2["ms"] / 3, "value": w2["lpj"] / (w2["ms"] * 1e-3), "unit": UNIT,
+                           "em_iters_per_sec": 3 / (w2["ms"] * 1e-3), "free_energy": w2["F"],
+                           "dtype": dtype_string(j2.w, args), "kernels": kernels_record(w2),
+                           "roofline": roofline_of(j2, w2, peak, peak_src, fma), "gpu_launches": w2["launches"]}
+            del j2
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    U_mean = U_sum / args.steps
-    alg = algorithmic_bytes(w, N, U_mean)
-    peak, peak_src = measured_peaks()
-    tot_t = sum(c * t for c, t in kern.values())
-    dom = max(kern, key=lambda k: kern[k][0] * kern[k][1])
-    roof = None
-    if dom in alg:
-        ach = alg[dom] / (kern[dom][1] * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": NCU_TRAFFIC.get((args.workload, N), {}).get(dom), "peak_source": peak_src, "launch_ms": kern[dom][1],
-                "algorithmic_bytes_per_launch": alg[dom]}
     line = {
         "metric": METRIC, "value": lpj_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "%s: %s" % (args.workload, DESCR[args.workload]), "N_per_gpu": N,
-                   "ea": "%s/%s parents=%d children=%d generations=%d" % tuple(w["ea"]),
-                   "l2": "inputs larger than L2 (K sets + tables > 126 MB)" if N * w["K"] * 4 * ((w["H"] + 31) // 32) > 126e6
-                   else "working set fits L2 (small reference config)",
-                   "tables": ("B = Y W by tcgen05 fp16 hi+lo split GEMM (lpj within 1e-5 of f64)" if args.tables == "tc"
-                              else "f64 SIMT GEMM") if w["model"] == "bsc" else "f64",
-                   "statistics": ("Wp = <S>'Y by split-K tcgen05 fp16 hi+lo GEMM (within 1e-5 of max|Wp|), Wq/pi/sigma f64"
-                                  if args.stats in ("tc", "auto")
-                                  else "f64") if w["model"] == "bsc" else "f64",
-                   "parallelism": "dp%d over N" % world},
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": dtype_string(w, args), "data": "synthetic",
+        "config": workload_config(name, w, N_total, world, args),
         "em_iters_per_sec": args.steps / (ms * 1e-3),
-        "lpj_per_step": lpj_total / args.steps, "new_unique_per_datapoint": U_mean, "free_energy": F,
+        "lpj_per_step": lpj_total / args.steps, "new_unique_per_datapoint": win["U_mean"], "free_energy": F,
+        "mean_active_latents_per_state": act_timed,
         "e2e": {"value": e2e_lpj / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms / args.steps},
-        "gpu_launches": int(launches),
-        "kernels": {k: {"launches": c, "mean_ms": t, "share": c * t / tot_t} for k, (c, t) in kern.items()},
-        "roofline": roof, "clocks": clocks,
+        "gpu_launches": win["launches"],
+        "kernels": kernels_record(win),
+        "roofline": roof, "comm": comm_rec, "clocks": clocks, "at_density": at_density,
+        "fma_peak_TFLOPs": fma, "also": also,
     }
     if not args.no_cpu:
-        line["cpu_baseline"] = cpu_port(args.workload, steps=1, warmup=1)
+        line["cpu_baseline"] = cpu_arm(name, steps=1, warmup=1)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
 # ---------------------------------------------------------------------------------------------
-# CPU arm: the NumPy oracle (a restatement of the reference's per-datapoint NumPy path, pinned
-# against the unmodified reference -- kind "port") on the host cores, one process per core like
-# the reference's MPI ranks, each on its own bounded sample of the same workload.
+# CPU arm: the UNMODIFIED reference (baseline/_ref/evo, copied from /root/reference by tools/install_reference.py
+# -- git-ignored, travels to the GPU box like the built .so) on the host cores, imported with the committed
+# single-rank mpi4py stand-in (tests/golden/_standin), one process per core like the reference's MPI ranks, each
+# on its own bounded slice of the SAME dataset rows the GPU arm holds (kind "reference").  If the copy is
+# absent the pinned NumPy oracle port runs instead (kind "port").
 # ---------------------------------------------------------------------------------------------
 CPU_SAMPLE = {"cfg1": 1000, "cfg2": 1000, "cfg5": 64, "cfg3": 64, "cfg4": 64}  # datapoints per core per step
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")
+
+
+def reference_available():
+    return os.path.isdir(os.path.join(REF_DIR, "evo", "models"))
 
 
 def cpu_worker(args):
@@ -514,45 +649,67 @@ def cpu_worker(args):
     import warnings
 
     warnings.simplefilter("ignore")
-    from oracle import bsc as OB
-    from oracle import sssc as OS
-    from oracle import variational as OV
-
     w = WORKLOADS[args.workload]
     n = args.n
     D, H, K = w["D"], w["H"], w["K"]
-    Y, X = synth_host(w, n, 1000 + args.cpu_worker)
-    Y = Y.astype(np.float64)
-    np.random.seed(1 + args.cpu_worker)
+    rows = np.arange(args.cpu_worker * n, (args.cpu_worker + 1) * n, dtype=np.int64)
+    Y, X = host_rows(w, rows)
     obs = np.ones_like(Y, dtype=bool) if X is None else X
-    mean = (Y * obs).sum(0) / np.maximum(obs.sum(0), 1)
-    sigma = float(np.sqrt((((Y - mean) * obs) ** 2).sum() / obs.sum()))
-    W0 = mean[:, None] + np.random.normal(scale=sigma / 4.0, size=(D, H))
     sel, mut, P, C, G = w["ea"]
-    cont = OV.init_states(n, K, H, sel, mut, P, C, G)
-    if w["model"] == "bsc":
-        theta = {"W": W0, "pi": 1.0 / H, "sigma": sigma}
-        data = {"y": Y, "x_infr": obs}
-        step = lambda th: OB.step(th, cont, data, D, H, K)
-    else:
-        learn = ("W", "pies", "sigma2") if X is not None else ("W", "pies", "mus", "sigma2", "Psi")
-        theta = {"W": W0, "pies": np.random.uniform(0.1, 0.5, size=H),
-                 "mus": np.ones(H) if X is not None else np.random.normal(0, 1, H),
-                 "Psi": np.eye(H), "sigma2": np.float64(sigma ** 2)}
+    np.random.seed(1 + args.cpu_worker)
+    use_ref = reference_available() and not os.environ.get("EVO_BENCH_PORT")
+    if use_ref:
+        sys.path.insert(0, os.path.join(ROOT, "tests", "golden", "_standin"))
+        sys.path.insert(0, REF_DIR)
+        from evo.models import BSC as RBSC, SSSC as RSSSC
+        from evo.variational.utils import init_states as ref_init_states
+
         Yn = np.where(obs, Y, np.nan)
-        data = {"y": Yn, "x_infr": obs, "x": obs if X is not None else np.zeros_like(obs)}
-        step = lambda th: OS.em_step(th, cont, data, D, H, K, to_learn=learn, do_reconstruction=True)
+        data = {"y": Yn, "x_infr": obs.copy()}
+        if w["model"] == "bsc":
+            model = RBSC(D, H, K)
+            recon = False
+        else:
+            learn = ["W", "pies", "sigma2"] if X is not None else ["W", "pies", "mus", "sigma2", "Psi"]
+            model = RSSSC(D, H, K, to_learn=learn)
+            data["x"] = obs.copy() if X is not None else np.zeros_like(obs)
+            recon = True
+        theta = model.check_params(model.standard_init(data))
+        cont = ref_init_states(n, K, H, sel, mut, P, C, G)
+        step = lambda th: model.step(th, cont, data, do_reconstruction=recon)
+    else:
+        from oracle import bsc as OB
+        from oracle import sssc as OS
+        from oracle import variational as OV
+
+        mean = (Y * obs).sum(0) / np.maximum(obs.sum(0), 1)
+        sigma = float(np.sqrt((((Y - mean) * obs) ** 2).sum() / obs.sum()))
+        W0 = mean[:, None] + np.random.normal(scale=sigma / 4.0, size=(D, H))
+        cont = OV.init_states(n, K, H, sel, mut, P, C, G)
+        if w["model"] == "bsc":
+            theta = {"W": W0, "pi": 1.0 / H, "sigma": sigma}
+            data = {"y": Y, "x_infr": obs}
+            step = lambda th: OB.step(th, cont, data, D, H, K)
+        else:
+            learn = ("W", "pies", "sigma2") if X is not None else ("W", "pies", "mus", "sigma2", "Psi")
+            theta = {"W": W0, "pies": np.random.uniform(0.1, 0.5, size=H),
+                     "mus": np.ones(H) if X is not None else np.random.normal(0, 1, H),
+                     "Psi": np.eye(H), "sigma2": np.float64(sigma ** 2)}
+            Yn = np.where(obs, Y, np.nan)
+            data = {"y": Yn, "x_infr": obs, "x": obs if X is not None else np.zeros_like(obs)}
+            step = lambda th: OS.em_step(th, cont, data, D, H, K, to_learn=learn, do_reconstruction=True)
     for _ in range(args.warmup):
-        step(theta)
+        F, nu, nsub, theta = step(theta)
     t0 = time.perf_counter()
     lpj = 0.0
     for _ in range(args.steps):
         F, nu, nsub, theta = step(theta)
         lpj += n * K + nu * n
-    print(json.dumps({"lpj": lpj, "sec": time.perf_counter() - t0, "F": F}), flush=True)
+    print(json.dumps({"lpj": lpj, "sec": time.perf_counter() - t0, "F": float(F), "kind": "reference" if use_ref else "port"}),
+          flush=True)
 
 
-def cpu_port(workload, steps, warmup, n_sub=None, cores=None):
+def cpu_arm(workload, steps, warmup, n_sub=None, cores=None):
     cores = cores or len(os.sched_getaffinity(0))
     n_sub = n_sub or CPU_SAMPLE[workload]
     env = dict(os.environ, OMP_NUM_THREADS="1", OPENBLAS_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
@@ -564,9 +721,13 @@ def cpu_port(workload, steps, warmup, n_sub=None, cores=None):
     wall = time.perf_counter() - t0
     sec = max(o["sec"] for o in outs)
     lpj = sum(o["lpj"] for o in outs)
-    return {"value": lpj / sec, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d datapoints per core x %d cores, %d timed EM iteration(s) after %d warm-up, NumPy oracle "
-                      "(oracle/bsc.py), 1 BLAS thread per process; whole call %.1f s" % (n_sub, cores, steps, warmup, wall),
+    kind = outs[0]["kind"]
+    what = ("the unmodified reference (baseline/_ref/evo, mpi4py stand-in, one process per core)" if kind == "reference"
+            else "NumPy oracle port (oracle/), one process per core")
+    return {"value": lpj / sec, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": "rows [0, %d) of the GPU arm's dataset: %d datapoints per core x %d cores, %d timed EM iteration(s) "
+                      "after %d warm-up, %s, 1 BLAS thread per process; whole call %.1f s"
+                      % (n_sub * cores, n_sub, cores, steps, warmup, what, wall),
             "ms_per_step": sec / steps * 1e3, "em_iters_per_sec_on_sample": steps / sec}
 
 
@@ -577,15 +738,16 @@ def run_reference(args):
         return
     w = WORKLOADS[args.workload]
     total = max(1, args.steps + args.warmup)
-    n_sub = max(16, int(CPU_SAMPLE[args.workload] * 2 / total))
-    cb = cpu_port(args.workload, steps=args.steps, warmup=args.warmup, n_sub=n_sub)
+    n_sub = max(8, int(CPU_SAMPLE[args.workload] * 2 / total))
+    cb = cpu_arm(args.workload, steps=args.steps, warmup=args.warmup, n_sub=n_sub)
+    cfg = workload_config(args.workload, w, args.n if args.n else w["N"], world, args)
+    cfg.pop("tables"), cfg.pop("statistics")
+    cfg["parallelism"] = "%d host processes over a bounded sample of N" % cb["cores"]
+    cfg["N_per_step"] = n_sub * cb["cores"]
     line = {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "%s: %s" % (args.workload, DESCR[args.workload]), "N_per_step": n_sub * cb["cores"],
-                   "ea": "%s/%s parents=%d children=%d generations=%d" % tuple(w["ea"]),
-                   "parallelism": "%d host processes over N" % cb["cores"]},
+        "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
         "cpu_baseline": cb,
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -599,9 +761,12 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--n", type=int, default=0, help="datapoints per GPU (default: the workload's N)")
+    ap.add_argument("--workload", default="cfg5", choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=0, help="datapoints IN TOTAL over all GPUs (default: the workload's N)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-also", action="store_true", help="skip the short sub-records of the other workloads")
+    ap.add_argument("--density-iters", type=int, default=40,
+                    help="also time a window after this many EM iterations (0 = off): states are denser by then")
     ap.add_argument("--tables", default="tc", choices=["tc", "f64"],
                     help="BSC table B = Y W: tcgen05 split-precision GEMM (default) or the f64 SIMT GEMM")
     ap.add_argument("--stats", default="auto", choices=["auto", "tc", "f64"],

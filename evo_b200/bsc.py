@@ -270,11 +270,16 @@ class BSC(Model):
             self.reconstruct(my_data, my_suff_stat, model_params)
         stats = self._stats_enqueue(model_params, my_suff_stat, dd)
         stats[-ACC_LEN:] = acc
+        ev = self._tick()
         self.comm.allreduce_(stats)
+        self._tock("allreduce", ev)
         # the solve is enqueued before anything is read back: ONE device->host read per EM iteration
+        ev = self._tick()
         pend = self._solve_enqueue(model_params, my_suff_stat, dd, stats)
+        self._tock("solve", ev)
         host = torch.cat([stats[-ACC_LEN:], pend["scal"]]).cpu().numpy()
         F, S_nunique, S_sub = self._estep_finish(host[:ACC_LEN], model_params, my_suff_stat, dd)
+        self.last_counts["stats_bytes"] = stats.numel() * 8
         return F, S_nunique, S_sub, self._solve_finish(model_params, my_suff_stat, dd, pend, host[ACC_LEN:])
 
     def _stats_enqueue(self, model_params, my_suff_stat, dd):

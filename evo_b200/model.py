@@ -50,6 +50,7 @@ class DeviceData:
         self.N_total, self.n_obs_total = int(round(tot[0])), int(round(tot[1]))
         self.Yrec = None
         self.cache = {}
+        self.y_ref = None
 
 
 class Model:
@@ -75,12 +76,30 @@ class Model:
 
     # ---- plumbing ---------------------------------------------------------------------------
     def device_data(self, my_data):
-        key = id(my_data["y"])
-        dd = self._data.get(key)
-        if dd is None or dd.N != my_data["y"].shape[0]:
+        """Resident device shard of `my_data` (uploaded once).  Keyed by the identity of `my_data["y"]`; the entry
+        holds a reference to that object, so its id cannot be recycled by another array while it is cached."""
+        y = my_data["y"]
+        dd = self._data.get(id(y))
+        if dd is None or dd.y_ref is not y or dd.N != y.shape[0]:
             dd = DeviceData(my_data, self.device, self.comm)
-            self._data = {key: dd}  # one resident dataset per model
+            dd.y_ref = y
+            self._data = {id(y): dd}  # one resident dataset per model
         return dd
+
+    def rebind_data(self, my_data, my_data_new):
+        """The resident shard of `my_data` now answers to `my_data_new["y"]` (same rows arriving from another buffer,
+        e.g. pinned host memory): nothing is copied."""
+        dd = self.device_data(my_data)
+        dd.y_ref = my_data_new["y"]
+        self._data = {id(dd.y_ref): dd}
+        return dd
+
+    @staticmethod
+    def _values_changed(dd):
+        """The shard's VALUES were replaced: drop everything derived from them (|y|^2, the transposed fp16 planes of
+        the tensor-core statistics, ES3C's sum of y^2); buffers that only depend on the shape stay."""
+        for k in ("ynorm2", "wp_tc_valid", "ysq"):
+            dd.cache.pop(k, None)
 
     def refresh_data(self, my_data):
         """Copy `my_data["y"]` (host buffer, ideally pinned) into the resident device shard again --
@@ -95,8 +114,7 @@ class Model:
             dd.Y.copy_(src.to(dd.Y.dtype))
         if dd.incomplete:
             dd.Y.copy_(torch.where(dd.mask.bool(), dd.Y, torch.zeros_like(dd.Y)))
-        dd.cache.pop("ynorm2", None)
-        dd.cache.pop("wp_tc_valid", None)
+        self._values_changed(dd)
         return dd
 
     def stage_data(self, my_data):
@@ -134,8 +152,7 @@ class Model:
         dd.spare_free = torch.cuda.Event()
         dd.spare_free.record(cur)
         dd.Y, dd.Y_spare = dd.Y_spare, dd.Y
-        dd.cache.pop("ynorm2", None)
-        dd.cache.pop("wp_tc_valid", None)
+        self._values_changed(dd)
         return dd
 
     def _call(self, name, *args):
@@ -312,12 +329,49 @@ class Model:
         self._call("evo_free_energy", _lib.ptr(lpj), lpj.shape[0], lpj.shape[1], lpj.stride(0), _lib.ptr(out))
         return out
 
-    # ---- data generation (_models.py:73-99) -- cold path, host NumPy like the reference ---------
-    def generate_data(self, model_params, my_N):
+    # ---- data generation (_models.py:73-99) on the device ------------------------------------------------
+    def generate_data(self, model_params, my_N, seed=None, n_offset=0, device_only=False):
+        """`Model.generate_data(model_params, my_N)` of the reference (_models.py:73-99): draws the hidden states
+        s ~ Bernoulli(pies) and the observations of the model (`generate_from_hidden`, bsc.py:27-57 /
+        sssc.py:66-102) -- here by ONE kernel (`evo_generate_data`), row n a pure function of
+        (seed, n_offset + n), so every rank can generate its own shard of one dataset.  `seed=None` takes a
+        seed from NumPy's global generator (the reference draws from it directly).  Returns the reference's dict
+        {"y", "s", "y_mean"[, "z"]} as NumPy arrays; with `device_only` {"y_dev" f32, "s_dev" packed} only."""
         assert "pies" in model_params or "pi" in model_params
-        W = np.asarray(model_params["W"].cpu() if isinstance(model_params["W"], torch.Tensor) else model_params["W"])
-        D, H_gen = W.shape
+        H, D = self.H, self.D
+        dev = self.device
+        W = _dev(model_params["W"], dev, torch.float64)
+        assert tuple(W.shape) == (D, H)
+        Wt = W.T.contiguous()
         pies = model_params["pies"] if "pies" in model_params else model_params["pi"]
-        p = np.random.random(size=(my_N, H_gen))
-        s = p <= pies
-        return self.generate_from_hidden(model_params, {"s": s})
+        pies_d, pi = None, 0.0
+        if np.ndim(pies) == 0:
+            pi = float(pies)
+        else:
+            pies_d = _dev(pies, dev, torch.float64)
+        mus = Psi = None
+        diag = 1
+        if "Psi" in model_params:  # ES3C
+            mus = _dev(model_params["mus"], dev, torch.float64)
+            Psi = _dev(model_params["Psi"], dev, torch.float64)
+            diag = int(bool((Psi == torch.diag(torch.diagonal(Psi))).all().item()))
+            sigma = float(np.sqrt(float(model_params["sigma2"])))
+        else:
+            sigma = float(model_params["sigma"])
+        if seed is None:
+            seed = int(np.random.randint(0, 2 ** 31 - 1))
+        my_N = int(my_N)
+        Y = torch.empty((my_N, D), dtype=torch.float32, device=dev)
+        S = torch.empty((my_N, V.words_for(H)), dtype=torch.int32, device=dev)
+        Z = torch.empty((my_N, H), dtype=torch.float32, device=dev) if (mus is not None and not device_only) else None
+        Ym = torch.empty((my_N, D), dtype=torch.float32, device=dev) if not device_only else None
+        ovf = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._call("evo_generate_data", _lib.ptr(Wt), _lib.ptr(pies_d), pi, _lib.ptr(mus), _lib.ptr(Psi), diag, sigma,
+                   my_N, int(n_offset), D, H, int(seed), _lib.ptr(Y), _lib.ptr(S), _lib.ptr(Z), _lib.ptr(Ym), _lib.ptr(ovf))
+        if device_only:
+            return {"y_dev": Y, "s_dev": S}
+        out = {"y": Y.double().cpu().numpy(), "s": V.unpack_states(S, H).cpu().numpy(), "y_mean": Ym.double().cpu().numpy(),
+               "y_dev": Y, "s_dev": S}
+        if Z is not None:
+            out["z"] = Z.double().cpu().numpy()
+        return out

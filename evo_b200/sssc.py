@@ -218,9 +218,14 @@ class SSSC(Model):
                 my_data["y_reconstructed"] = dd.Yrec.double().cpu().numpy()
         # ---- ONE all-reduce: statistics + free-energy / diagnostic scalars in the tail ------------------
         stats[-ACC_LEN:] = acc
+        ev = self._tick()
         self.comm.allreduce_(stats)
+        self._tock("allreduce", ev)
         F, S_nunique, S_sub = self._finish_acc(stats[-ACC_LEN:], model_params, ss, dd)
+        self.last_counts["stats_bytes"] = stats.numel() * 8
+        ev = self._tick()
         self._update(model_params, ss, dd, stats)
+        self._tock("solve", ev)
         return F, S_nunique, S_sub, model_params
 
     # ---- parameter updates (sssc.py:688-770), replicated on every rank ----------------------------------------

@@ -261,6 +261,22 @@ typedef struct evo_es3c_stats_args {
 } evo_es3c_stats_args;
 int evo_es3c_suffstats(const evo_es3c_stats_args *args, void *stream);
 
+/* ---- device-side setup ----------------------------------------------------------------
+ * Model.generate_data (evo/models/_models.py:73-99) -> BSC.generate_from_hidden (bsc.py:27-57) /
+ * SSSC.generate_from_hidden (sssc.py:66-102): s_h ~ Bernoulli(pies[h]) (pies NULL: the scalar `pi`),
+ * BSC (mus == Psi == NULL): y = W s + sigma N(0, I);  ES3C: z_A ~ N(mus_A, Psi_AA), y = W_A z_A + sigma N(0, I)
+ * with sigma = sqrt(sigma2); psi_diag != 0 uses the diagonal of Psi only, otherwise the Cholesky factor of
+ * Psi_AA (supports of more than 32 latents fall back to the diagonal and are counted in *overflow).
+ * Row n is a pure function of (seed, n_offset + n): Philox-4x32-10 counter streams documented in
+ * csrc/datagen.cu and restated in oracle/datagen.py -- shards of one dataset do not depend on the rank count.
+ * Wt = W' [H][D] f64.  Outputs: Y f32 [N][D]; optional S_out packed [N][Hw], Z_out f32 [N][H], Ymean f32 [N][D]. */
+int evo_generate_data(const double *Wt, const double *pies, double pi, const double *mus, const double *Psi,
+                      int psi_diag, double sigma, int64_t N, int64_t n_offset, int D, int H, uint64_t seed,
+                      float *Y, uint32_t *S_out, float *Z_out, float *Ymean, int32_t *overflow, void *stream);
+/* FMA throughput of the SIMT pipes in TFLOP/s (dtype 32 or 64; 8 independent chains per thread, best of 3,
+ * synchronous, default stream): the measured denominator of the ES3C roofline (bench.py). */
+int evo_fma_peak(int dtype, int iters, double *tflops_out);
+
 /* ---- overlapping-patch pipeline of the image drivers (tvutil.prepost OverlappingPatches /
  *      MultiDimOverlappingPatches .get / .set_and_merge with mean_merger / median_merger; call sites
  *      examples/image-denoising/main.py:85-88,169-177, examples/image-inpainting/main.py:86-88,174-182) ----
