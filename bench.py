@@ -80,7 +80,8 @@ def _hash_u32(x):
 
 def observed_mask(rows, D, p_missing, xp):
     """Entry (n, d) is missing with probability p: a hash of the GLOBAL entry index (sharding independent)."""
-    idx = rows[:, None] * D + xp.arange(D)[None, :]
+    cols = xp.arange(D) if xp is np else xp.arange(D, device=rows.device)
+    idx = rows[:, None] * D + cols[None, :]
     return _hash_u32(idx + 0x9E3779B9) >= int(p_missing * 4294967296.0)
 
 

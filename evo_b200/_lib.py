@@ -67,6 +67,20 @@ class Es3cStatsArgs(C.Structure):
     ]
 
 
+class Es3cUpdateArgs(C.Structure):
+    """Mirror of `evo_es3c_update_args` (include/evo_b200.h)."""
+
+    _fields_ = [
+        ("D", C.c_int32), ("H", C.c_int32),
+        ("learn_W", C.c_int32), ("learn_pies", C.c_int32), ("learn_mus", C.c_int32), ("learn_Psi", C.c_int32),
+        ("learn_sigma2", C.c_int32), ("background", C.c_int32), ("incomplete", C.c_int32), ("_pad", C.c_int32),
+        ("N_total", C.c_double), ("n_obs_total", C.c_double), ("ysq", C.c_double), ("sigma2_old", C.c_double),
+        ("eps_pies", C.c_double), ("eps_mus", C.c_double), ("eps_Psi", C.c_double), ("eps_sigma2", C.c_double),
+        ("stats", C.c_void_p), ("W", C.c_void_p), ("pies", C.c_void_p), ("mus", C.c_void_p), ("Psi", C.c_void_p),
+        ("scal", C.c_void_p), ("workspace", C.c_void_p),
+    ]
+
+
 _vp, _i, _i64, _d, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_uint64
 
 SIGNATURES = {
@@ -95,6 +109,10 @@ SIGNATURES = {
     "evo_bsc_wp_tc_workspace_bytes": (_i64, [_i64, _i, _i]),
     "evo_bsc_wp_tc_set_data": (_i, [_vp, _i64, _i, _i, _vp, _vp]),
     "evo_bsc_suffstats_tc": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp]),
+    "evo_bsc_solve_workspace_bytes": (_i64, [_i, _i]),
+    "evo_bsc_solve": (_i, [_vp, _d, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp, _vp]),
+    "evo_es3c_update_workspace_bytes": (_i64, [_i, _i]),
+    "evo_es3c_update": (_i, [C.POINTER(Es3cUpdateArgs), _vp]),
     "evo_es3c_set_scratch": (_i, [_vp, _i]),
     "evo_es3c_lpj": (_i, [_vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _vp, _i64, _vp, _vp]),
     "evo_es3c_suffstats": (_i, [C.POINTER(Es3cStatsArgs), _vp]),

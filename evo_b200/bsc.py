@@ -333,46 +333,44 @@ class BSC(Model):
         return self._solve_finish(model_params, my_suff_stat, dd, pend, pend["scal"].cpu().numpy())
 
     def _solve_enqueue(self, model_params, my_suff_stat, dd, stats):
-        """Parameter update from the reduced statistics (bsc.py:226-262), enqueued without a host read;
-        `scal` = (cholesky info, solution finite, sum of pies / N, sigma statistic) is read once by the caller."""
+        """Parameter update from the reduced statistics (bsc.py:226-275) by `evo_bsc_solve` (block Gaussian
+        elimination of [Wq | Wp] on the device), enqueued without a host read; `scal` = (info, pi, sigma, W finite) is
+        read once by the caller together with the E-step scalars."""
         D, H = self.D, self.H
-        Wp = stats[: H * D].view(H, D)
-        Wq = stats[H * D: H * D + H * H].view(H, H)
-        Wq = torch.tril(Wq) + torch.tril(Wq, -1).T
-        p = stats[H * D + H * H: H * D + H * H + H] / dd.N_total
-        if my_suff_stat["permanent"]["background"]:
-            p[-1] = 1.0 - 1.1e-5
-        pend = {"Wq": Wq, "Wp": Wp, "p": p, "sol": None}
-        flags = torch.ones(2, dtype=torch.float64, device=self.device)
-        if "W" in self.to_learn:
-            # Wq is symmetric PSD: Cholesky on the device; the host falls back to the reference's
-            # minimum-norm lstsq when it is not positive definite (checked in _solve_finish)
-            L, info = torch.linalg.cholesky_ex(Wq)
-            sol = torch.cholesky_solve(Wp, L)
-            pend["sol"] = sol
-            flags = torch.stack([info.to(torch.float64), torch.isfinite(sol).all().to(torch.float64)])
-        pend["scal"] = torch.cat([flags, p.sum().reshape(1), stats[H * D + H * H + H].reshape(1)])
-        return pend
+        ws = getattr(self, "_solve_ws", None)
+        if ws is None:
+            nb = int(self.lib.evo_bsc_solve_workspace_bytes(D, H))
+            ws = self._solve_ws = torch.empty(nb, dtype=torch.uint8, device=self.device)
+        learn_W = "W" in self.to_learn
+        W_out = torch.empty((D, H), dtype=torch.float64, device=self.device) if learn_W else None
+        pies = torch.empty(H, dtype=torch.float64, device=self.device)
+        scal = torch.empty(4, dtype=torch.float64, device=self.device)
+        self._call("evo_bsc_solve", _lib.ptr(stats), float(dd.N_total), D, H, int(learn_W),
+                   int(bool(my_suff_stat["permanent"]["background"])), float(dd.n_obs_total) if dd.incomplete else -1.0,
+                   float(model_params["sigma"]), _lib.ptr(W_out), _lib.ptr(pies), _lib.ptr(scal), _lib.ptr(ws))
+        return {"W": W_out, "p": pies, "scal": scal, "stats": stats}
 
     def _solve_finish(self, model_params, my_suff_stat, dd, pend, scal):
         D, H = self.D, self.H
-        N = dd.N_total
         as_numpy = not isinstance(model_params["W"], torch.Tensor)
-        sigma_old = float(model_params["sigma"])
         if "W" in self.to_learn:
-            if int(scal[0]) == 0 and scal[1] > 0.5:
-                Wn = pend["sol"]
+            if int(scal[0]) == 0 and scal[3] > 0.5:
+                Wn = pend["W"]
             else:
-                Wn = torch.as_tensor(np.linalg.lstsq(pend["Wq"].cpu().numpy(), pend["Wp"].cpu().numpy(), rcond=-1)[0],
-                                     device=self.device)
-            model_params["W"] = Wn.T.contiguous().cpu().numpy() if as_numpy else Wn.T.contiguous()
+                # Wq is (numerically) singular -- e.g. a latent that carries no posterior mass.  The reference's
+                # lstsq(rcond=-1) returns the minimum-norm solution (bsc.py:233-235): eigenvalues below eps x the
+                # largest are dropped.  Same thing on the device through the Hermitian pseudo-inverse (rare path).
+                stats = pend["stats"]
+                Wp = stats[: H * D].view(H, D)
+                Wq = stats[H * D: H * D + H * H].view(H, H)
+                Wq = torch.tril(Wq) + torch.tril(Wq, -1).T
+                Wn = (torch.linalg.pinv(Wq, hermitian=True, rtol=float(np.finfo(np.float64).eps)) @ Wp).T.contiguous()
+                self.last_counts["solve_fallback"] = self.last_counts.get("solve_fallback", 0) + 1
+            model_params["W"] = Wn.cpu().numpy() if as_numpy else Wn
         if "pi" in self.to_learn:
-            model_params["pi"] = float(scal[2] / H)
+            model_params["pi"] = float(scal[1])
             model_params["pies"] = pend["p"].cpu().numpy() if as_numpy else pend["p"]
         if "sigma" in self.to_learn:
-            sig = float(scal[3])
-            if dd.incomplete:
-                model_params["sigma"] = float(np.sqrt((sig + dd.n_obs_total * sigma_old ** 2) / N / D))
-            else:
-                model_params["sigma"] = float(np.sqrt(sig / N / D))
+            sig = float(scal[2])
+            model_params["sigma"] = sig if sig == sig else 0.0  # a negative statistic (NaN root) is clamped by check_params
         return model_params

@@ -172,7 +172,7 @@ class SSSC(Model):
         return acc
 
     def _finish_acc(self, acc, model_params, my_suff_stat, dd):
-        r = acc.cpu().numpy()
+        r = acc.cpu().numpy() if isinstance(acc, torch.Tensor) else acc
         for i, k in enumerate(("reset_lpj_isnan", "reset_lpj_smaller_eps_lpj", "reset_lpj_isinf")):
             dict.__setitem__(my_suff_stat, k, int(r[3 + i]))
         self.last_counts = {"lpj_evaluated": float(r[6])}
@@ -221,66 +221,82 @@ class SSSC(Model):
         ev = self._tick()
         self.comm.allreduce_(stats)
         self._tock("allreduce", ev)
-        F, S_nunique, S_sub = self._finish_acc(stats[-ACC_LEN:], model_params, ss, dd)
-        self.last_counts["stats_bytes"] = stats.numel() * 8
+        # the parameter updates are enqueued before anything is read back: ONE device->host read per EM iteration
         ev = self._tick()
-        self._update(model_params, ss, dd, stats)
+        pend = self._update_enqueue(model_params, ss, dd, stats)
         self._tock("solve", ev)
+        host = torch.cat([stats[-ACC_LEN:], pend["scal"]]).cpu().numpy()
+        F, S_nunique, S_sub = self._finish_acc(host[:ACC_LEN], model_params, ss, dd)
+        self.last_counts["stats_bytes"] = stats.numel() * 8
+        self._update_finish(model_params, ss, dd, stats, pend, host[ACC_LEN:])
         return F, S_nunique, S_sub, model_params
 
     # ---- parameter updates (sssc.py:688-770), replicated on every rank ----------------------------------------
-    def _update(self, th, ss, dd, stats):
+    def _update_enqueue(self, th, ss, dd, stats):
+        """`evo_es3c_update`: every learned parameter from the reduced statistics, on the device, no host read."""
+        D, H = self.D, self.H
+        c = dd.cache
+        ws = getattr(self, "_update_ws", None)
+        if ws is None:
+            nb = int(self.lib.evo_es3c_update_workspace_bytes(D, H))
+            ws = self._update_ws = torch.empty(nb, dtype=torch.uint8, device=self.device)
+        if "sigma2" in self.to_learn and "ysq" not in c:
+            ysq = (dd.Y.double() ** 2).sum().reshape(1)  # once per dataset; Y is 0 where masked
+            self.comm.allreduce_(ysq)
+            c["ysq"] = float(ysq.item())
+        new = {"W": c["W"].clone(), "pies": _dev(th["pies"], self.device, torch.float64).clone(), "mus": c["mus"].clone(),
+               "Psi": c["Psi"].clone(), "scal": torch.empty(4, dtype=torch.float64, device=self.device)}
+        a = _lib.Es3cUpdateArgs()
+        a.D, a.H = D, H
+        L = self.to_learn
+        a.learn_W, a.learn_pies, a.learn_mus = int("W" in L), int("pies" in L), int("mus" in L)
+        a.learn_Psi, a.learn_sigma2 = int("Psi" in L), int("sigma2" in L)
+        a.background, a.incomplete = int(bool(ss["permanent"]["background"])), int(dd.incomplete)
+        a.N_total, a.n_obs_total = float(dd.N_total), float(dd.n_obs_total)
+        a.ysq, a.sigma2_old = float(c.get("ysq", 0.0)), float(th["sigma2"])
+        a.eps_pies, a.eps_mus, a.eps_Psi, a.eps_sigma2 = self.eps_pies, self.eps_mus, self.eps_Psi, self.eps_sigma2
+        a.stats = stats.data_ptr()
+        a.W, a.pies, a.mus, a.Psi = new["W"].data_ptr(), new["pies"].data_ptr(), new["mus"].data_ptr(), new["Psi"].data_ptr()
+        a.scal, a.workspace = new["scal"].data_ptr(), ws.data_ptr()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.evo_es3c_update(C.byref(a), _lib.stream()), "evo_es3c_update")
+        return new
+
+    def _update_finish(self, th, ss, dd, stats, new, scal):
         D, H = self.D, self.H
         H2 = H * H
-        N = dd.N_total
-        o = 0
-        sum_s = stats[o:o + H]; o += H
-        sum_sz = stats[o:o + H]; o += H
-        sum_ss = stats[o:o + H2].view(H, H); o += H2
-        sum_szsz = stats[o:o + H2].view(H, H); o += H2
-        sum_s_sz = stats[o:o + H2].view(H, H); o += H2
-        sum_outer = stats[o:o + H2].view(H, H); o += H2
-        WpT = stats[o:o + H * D].view(H, D); o += H * D
-        trace = stats[o]
         as_numpy = not isinstance(th["W"], torch.Tensor)
         out = (lambda t: t.cpu().numpy()) if as_numpy else (lambda t: t)
-        sigma2_old = float(th["sigma2"])
-        W_new = dd.cache["W"]
-        if "W" in self.to_learn:
-            try:
-                inv = torch.linalg.inv(sum_szsz)
-                if not bool(torch.isfinite(inv).all().item()):
-                    raise RuntimeError("singular")
-                W_new = WpT.T @ inv
-            except RuntimeError:
-                # sssc.py:696-709: second moments not invertible -> pinv with rank-one noise
-                noise = torch.as_tensor(np.random.normal(0, self.eps_W, H), device=self.device)
-                W_new = WpT.T @ torch.linalg.pinv(sum_szsz + torch.outer(noise, noise))
-            th["W"] = out(W_new.contiguous())
-        if "pies" in self.to_learn:
-            p = (sum_s / N).clamp(self.eps_pies, 1 - self.eps_pies)
-            if ss["permanent"]["background"]:
-                p[H - 1] = 1.0 - 1.1e-5
-            th["pies"] = out(p)
-        mus_new = dd.cache["mus"]
-        if "mus" in self.to_learn:
-            mus_new = sum_sz / (sum_s + self.eps_mus)
-            th["mus"] = out(mus_new)
-        if "Psi" in self.to_learn:
-            Psi = torch.outer(mus_new, mus_new) * sum_ss + sum_szsz - 2 * mus_new[:, None] * sum_s_sz
-            # element-wise product with the inverse -- reference behaviour (sssc.py:738)
-            th["Psi"] = out(Psi * torch.linalg.inv(sum_ss + self.eps_Psi * torch.eye(H, dtype=torch.float64, device=self.device)))
+        singular_W = "W" in self.to_learn and (int(scal[0]) != 0 or scal[3] < 0.5)
+        singular_P = "Psi" in self.to_learn and (int(scal[1]) != 0 or scal[3] < 0.5)
+        if singular_W or singular_P:
+            # (numerically) singular second moments: the reference's route (sssc.py:695-709) -- pseudo-inverse of the
+            # moments plus rank-one noise.  The noise is drawn on rank 0 and broadcast, so that every rank keeps
+            # bit-identical parameters (there is no per-iteration Bcast of theta here).  Rare path, device library calls.
+            sum_s, sum_sz = stats[:H], stats[H:2 * H]
+            sum_ss = stats[2 * H:2 * H + H2].view(H, H)
+            sum_szsz = stats[2 * H + H2:2 * H + 2 * H2].view(H, H)
+            sum_s_sz = stats[2 * H + 2 * H2:2 * H + 3 * H2].view(H, H)
+            sum_outer = stats[2 * H + 3 * H2:2 * H + 4 * H2].view(H, H)
+            WpT = stats[2 * H + 4 * H2:2 * H + 4 * H2 + H * D].view(H, D)
+            if singular_W:
+                noise = torch.as_tensor(self.comm.bcast(np.random.normal(0, self.eps_W, H)), device=self.device)
+                new["W"] = (WpT.T @ torch.linalg.pinv(sum_szsz + torch.outer(noise, noise))).contiguous()
+                if "sigma2" in self.to_learn and not dd.incomplete:
+                    WtW = new["W"].T @ new["W"]
+                    scal = scal.copy()
+                    scal[2] = (dd.cache["ysq"] - float((sum_outer * WtW.T).sum().item())) / dd.N_total / D + self.eps_sigma2
+            if singular_P:
+                mu = new["mus"]
+                Psi = torch.outer(mu, mu) * sum_ss + sum_szsz - 2 * mu[:, None] * sum_s_sz
+                eye = torch.eye(H, dtype=torch.float64, device=self.device)
+                new["Psi"] = Psi * torch.linalg.inv(sum_ss + self.eps_Psi * eye)
+            self.last_counts["solve_fallback"] = self.last_counts.get("solve_fallback", 0) + 1
+        for k in ("W", "pies", "mus", "Psi"):
+            if k in self.to_learn:
+                th[k] = out(new[k])
         if "sigma2" in self.to_learn:
-            if "ysq" not in dd.cache:
-                ysq = (dd.Y.double() ** 2).sum().reshape(1)  # Y is 0 where masked
-                self.comm.allreduce_(ysq)
-                dd.cache["ysq"] = float(ysq.item())
-            if dd.incomplete:
-                s2 = ((dd.cache["ysq"] - float(trace.item())) + dd.n_obs_total * sigma2_old) / N / D + self.eps_sigma2
-            else:
-                WtW = W_new.T @ W_new
-                s2 = (dd.cache["ysq"] - float((sum_outer * WtW.T).sum().item())) / N / D + self.eps_sigma2
-            th["sigma2"] = np.float64(s2)
+            th["sigma2"] = np.float64(scal[2])
         return th
 
     def M_step(self, model_params, my_suff_stat, my_data):

@@ -221,6 +221,40 @@ int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double 
                         const uint8_t *recon_keep, const uint8_t *infer_mask, int64_t N, int D, int H,
                         int S, int S_perm, float *Yrec, void *stream);
 
+/* ---- replicated parameter updates on the device (no library solver, no host fallback) ----------------------------
+ * Both solve A X = B by block Gaussian elimination of [A | B] with explicitly inverted 32 x 32 diagonal blocks
+ * (csrc/solve.cu).  `info` (scal[0]; for ES3C also scal[1]) is 0 when every pivot exceeded 1e-13 x the largest
+ * diagonal entry, else 1 + the index of the first failing block: the statistics are (numerically) singular and the
+ * caller takes the reference's minimum-norm route (bsc.py:233-250 lstsq / pinv; sssc.py:695-709).
+ *
+ * evo_bsc_solve -- BSC.M_step after the all-reduce (evo/models/bsc.py:226-275).  stats = the reduced buffer of
+ * evo_bsc_suffstats [Wp H*D | Wq H*H (lower triangle) | pies H | sigma 1].  Writes W [D][H] = (Wq^-1 Wp)' (only if
+ * learn_W and info == 0), pies [H] = sum / N_total (background: last = 1 - 1.1e-5), scal[4] = {info, pi = mean pies,
+ * sigma = sqrt(sig / (N D)) or sqrt((sig + n_obs_total sigma_old^2) / (N D)) for incomplete data (n_obs_total >= 0),
+ * 1 if W is finite}.  The caller keeps the parameters it does not learn. */
+int64_t evo_bsc_solve_workspace_bytes(int D, int H);
+int evo_bsc_solve(const double *stats, double N_total, int D, int H, int learn_W, int background, double n_obs_total,
+                  double sigma_old, double *W, double *pies, double *scal, void *workspace, void *stream);
+/* evo_es3c_update -- SSSC.EM_step parameter updates (evo/models/sssc.py:688-770) from the reduced buffer of
+ * evo_es3c_suffstats.  W / pies / mus / Psi hold the current parameters and are overwritten where learned:
+ *   W = Wp inv(sum_szsz) (:692-694), pies = clip(sum_s / N, eps, 1 - eps) (:712-721), mus = sum_sz / (sum_s + eps_mus)
+ *   (:724-727), Psi = (mu mu' o sum_ss + sum_szsz - 2 mu[:,None] o sum_s_sz) o inv(sum_ss + eps_Psi I) -- the reference's
+ *   ELEMENT-WISE product (:729-741) --, sigma2 (:744-770): complete data (ysq - trace(sum_outer W'W)) / (N D) + eps with
+ *   the NEW W, incomplete data ((ysq - trace statistic) + n_obs_total sigma2_old) / (N D) + eps.
+ * scal[4] = {info of the W solve, info of the Psi solve, sigma2_new, 1 if all outputs are finite}. */
+typedef struct evo_es3c_update_args {
+  int32_t D, H;
+  int32_t learn_W, learn_pies, learn_mus, learn_Psi, learn_sigma2, background, incomplete, _pad;
+  double N_total, n_obs_total, ysq, sigma2_old;
+  double eps_pies, eps_mus, eps_Psi, eps_sigma2;
+  const double *stats;
+  double *W, *pies, *mus, *Psi; /* [D][H], [H], [H], [H][H] */
+  double *scal;                 /* [4] */
+  void *workspace;              /* evo_es3c_update_workspace_bytes(D, H), 16-byte aligned */
+} evo_es3c_update_args;
+int64_t evo_es3c_update_workspace_bytes(int D, int H);
+int evo_es3c_update(const evo_es3c_update_args *args, void *stream);
+
 /* ---- ES3C (class SSSC) ------------------------------------------------------------------------
  * The E-step is evo_estep with eval = EVO_EVAL_ES3C: complete data uses (G, B, ynorm2) from
  * evo_bsc_prepare, incomplete data uses Wt = W' [H][D] passed in `W`, plus pil_bar_h, mus, Psi, sigma2
