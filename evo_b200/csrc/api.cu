@@ -3,6 +3,7 @@
 
 #include "common.cuh"
 #include "estep.cuh"
+#include "estep_flip.cuh"
 #include "es3c.cuh"
 
 namespace evo {
@@ -202,6 +203,7 @@ static int estep_dims(const evo_estep_args *x, EstepDev &dv) {
     if (x->mutation == EVO_MUT_RANDFLIP || x->mutation == EVO_MUT_SPARSEFLIP) {
       EVO_REQUIRE(x->n_generations == 0 || x->n_children >= 1, "n_children must be >= 1");
       Cg = P * x->n_children;
+      EVO_REQUIRE(Cg <= 1024, "at most 1024 children per generation");
     } else {
       Cg = P * (P - 1);
     }

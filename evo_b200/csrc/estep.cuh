@@ -286,6 +286,36 @@ __device__ __forceinline__ int count_less(const double *keys, int n, double k) {
 // ---- mutation helpers -----------------------------------------------------------------------
 __device__ __forceinline__ void flip_bit(uint32_t *st, int pos) { st[pos >> 5] ^= 1u << (pos & 31); }
 
+// randflip positions (eas.py:27-42): C distinct uniformly drawn positions per parent; child c = p * C + j flips slot[c].
+// Every child draws its own position (Philox draw index c * 64 + round); in rounds, a child that collides with a LOWER
+// sibling's current position redraws, until no collision is left.  Relabelling the positions maps trajectories of this
+// process onto equally likely ones, so the final tuple is uniform over the ordered C-tuples of distinct positions --
+// the distribution of the reference's sequential draw -- while all children of all parents draw in parallel.
+// Shared by every kernel variant (same streams => same children).  Ends with a group barrier.
+template <int T>
+__device__ __forceinline__ void draw_flip_positions(const RngCtx &rng, uint32_t gr, int take, int C, int Hm, int *slot, int *red_i) {
+  const int tid = threadIdx.x, nc = take * C;
+  _Pragma("unroll 1") for (int c = tid; c < nc; c += T)
+    slot[c] = (int)urange(rng.draw(RNG_MUTATE, gr, (uint32_t)c * 64u).x, (uint32_t)Hm);
+  gsync<T>();
+  if (C > Hm) return;  // cannot be distinct (degenerate input): keep the first draw
+  for (uint32_t round = 1; round < 64u; ++round) {
+    unsigned need = 0;
+    int it = 0;
+    _Pragma("unroll 1") for (int c = tid; c < nc; c += T, ++it) {
+      const int j = c % C, b0 = c - j, pos = slot[c];
+      bool dup = false;
+      for (int q = 0; q < j; ++q) dup |= (slot[b0 + q] == pos);
+      if (dup) need |= 1u << (it & 31);
+    }
+    if (!group_or<T>(need, red_i)) break;  // (barriers inside: every read of this round is done)
+    it = 0;
+    _Pragma("unroll 1") for (int c = tid; c < nc; c += T, ++it)
+      if ((need >> (it & 31)) & 1u) slot[c] = (int)urange(rng.draw(RNG_MUTATE, gr, (uint32_t)c * 64u + round).x, (uint32_t)Hm);
+    gsync<T>();
+  }
+}
+
 // sparseflip (eas.py:46-100): independent flips, p1 on on-bits, p0 on off-bits, over the first Hm
 // latents.  Sampled by thinning a Bernoulli(pmax) process visited with geometric jumps -- same
 // distribution, O(#candidates) draws instead of O(H).
@@ -439,25 +469,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
         if (FAST || mut == EVO_MUT_RANDFLIP || mut == EVO_MUT_SPARSEFLIP) {
           const int C = a.n_children;
           nc = take * C;
-          if (FAST || mut == EVO_MUT_RANDFLIP) {
-            // C distinct uniformly drawn positions per parent; child j flips position j
-            _Pragma("unroll 1") for (int p = tid; p < take; p += T) {
-              uint32_t di = (uint32_t)p * 64u * (uint32_t)(C + 1);
-              for (int j = 0; j < C; ++j) {
-                int pos;
-                bool dup;
-                do {
-                  uint4 r = rng.draw(RNG_MUTATE, gr, di++);
-                  pos = (int)urange(r.x, (uint32_t)Hm);
-                  dup = false;
-                  for (int q = 0; q < j; ++q) dup |= (s.slot[p * C + q] == pos);
-                  if (dup && C >= Hm) { dup = false; }  // cannot be distinct: give up (degenerate input)
-                } while (dup);
-                s.slot[p * C + j] = pos;
-              }
-            }
-            gsync<T>();
-          }
+          if (FAST || mut == EVO_MUT_RANDFLIP) draw_flip_positions<T>(rng, gr, take, C, Hm, s.slot, s.red_i);
           _Pragma("unroll 1") for (int c = tid; c < nc; c += T) {
             int p = c / C;
             const uint32_t *src = s.st_uniq + (size_t)s.parents[p] * Hs;
@@ -750,15 +762,19 @@ static int launch_estep_variant(const EstepDev &dv, Eval ev, int64_t items, cuda
   return EVO_OK;
 }
 
+// randflip fast path over index lists with implicit children (estep_flip.cuh)
+struct BscGramEval;
+template <int TT>
+static int launch_estep_flip(const EstepDev &dv, BscGramEval ev, cudaStream_t st);
+
 template <class Eval, int TT>
 static int launch_estep_T(const EstepDev &dv, Eval ev, bool fast, cudaStream_t st) {
   if constexpr (Eval::kList) {
-    if (fast && dv.ovf_list && dv.H < 65535 && dv.N < 2147483647LL && !getenv("EVO_ESTEP_BITS")) {
+    const int PB = dv.n_parents * (dv.n_generations > 1 ? dv.n_generations - 1 : 0);
+    if (fast && dv.ovf_list && dv.H < 65535 && dv.S + PB < 65535 && dv.N < 2147483647LL && dv.n_children <= dv.H &&
+        !getenv("EVO_ESTEP_BITS")) {
       EVO_CUDA(cudaMemsetAsync(dv.ovf_list, 0, sizeof(int32_t), st));
-      EstepDev dl = dv;
-      dl.Hr = LIST_WORDS;
-      dl.Hs = LIST_WORDS + 1;
-      int rc = launch_estep_variant<Eval, TT, true, true>(dl, ev, dv.N, st);
+      int rc = launch_estep_flip<TT>(dv, ev, st);
       if (rc) return rc;
       EstepDev db = dv;
       db.n_list = dv.ovf_list;
