@@ -29,6 +29,11 @@ def _run_both(D, H, K, N, act, ea, iters=3):
         th = m.check_params(m.standard_init(data))
         cont = init_states(N, K, H, "fit", "randflip", *ea, p_init_Kn=act / H, device=m.device, seed=11)
         _, _, _, th = m.step(th, cont, data)  # one M-step so that the parameters carry structure
+        # With H > N the M-step leaves latents without posterior mass an all-zero column of W (minimum-norm solve): states
+        # that differ only in such latents have EXACTLY equal log-joints in exact arithmetic, and which of them survives
+        # is decided by rounding (the reference's own order there is unspecified -- SURVEY App. A.6(i)).  A tiny
+        # perturbation removes the exact ties, so that the two kernels can be compared state for state.
+        th["W"] = np.asarray(th["W"]) + 1e-6 * rng.normal(size=(D, H))
         out = {}
         # E-steps under the SAME fixed parameters (the M-step's f64 atomics are unordered, so two
         # trajectories through M-steps differ in the last bits whichever kernel ran)
