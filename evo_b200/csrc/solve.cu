@@ -84,21 +84,26 @@ static int gemm(const GemmArgs &g, cudaStream_t st) {
 }
 
 // Inverse of the 32 x 32 diagonal block M[r0.., r0..] (leading dimension ld) by Gauss-Jordan with partial
-// pivoting, one warp, lane = row.  inv (32 x 32, row-major) <- block^-1; *info = blk + 1 (smallest failing
-// block) when a pivot is <= tol * scale[0] in magnitude or not finite.
+// pivoting, one warp, lane = row, the row of [A | R] in REGISTERS (both loops fully unrolled).  Rows are not swapped:
+// the lane chosen as pivot for column k ends up holding row k of the inverse.  inv (32 x 32, row-major) <- block^-1;
+// *info = blk + 1 (first failing block) when a pivot is <= tol * scale[0] in magnitude or not finite.
 __global__ void __launch_bounds__(32) diag_inv_kernel(const double *__restrict__ Mx, int64_t ld, int r0, double *__restrict__ inv,
                                                       const double *__restrict__ scale, double tol, int blk, int *info) {
-  __shared__ double A[SB][SB + 1], R[SB][SB + 1];
+  __shared__ double prow[2 * SB];
   const int lane = threadIdx.x;
+  double a[SB], r[SB];
+#pragma unroll
   for (int c = 0; c < SB; ++c) {
-    A[lane][c] = Mx[(int64_t)(r0 + lane) * ld + r0 + c];
-    R[lane][c] = (lane == c) ? 1.0 : 0.0;
+    a[c] = Mx[(int64_t)(r0 + lane) * ld + r0 + c];
+    r[c] = (lane == c) ? 1.0 : 0.0;
   }
-  __syncwarp();
   const double thr = tol * fabs(scale[0]);
-  bool bad = false;
+  bool bad = false, used = false;
+  int mycol = 0;
+  double mypiv = 1.0;
+#pragma unroll
   for (int k = 0; k < SB; ++k) {
-    double mag = lane >= k ? fabs(A[lane][k]) : -1.0;
+    double mag = used ? -1.0 : fabs(a[k]);
     int p = lane;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -106,22 +111,26 @@ __global__ void __launch_bounds__(32) diag_inv_kernel(const double *__restrict__
       const int op = __shfl_xor_sync(0xffffffffu, p, o);
       if (om > mag || (om == mag && op < p)) { mag = om; p = op; }
     }
-    if (p != k) {
-      double t = A[k][lane]; A[k][lane] = A[p][lane]; A[p][lane] = t;
-      t = R[k][lane]; R[k][lane] = R[p][lane]; R[p][lane] = t;
+    if (lane == p) {
+#pragma unroll
+      for (int c = 0; c < SB; ++c) { prow[c] = a[c]; prow[SB + c] = r[c]; }
+      used = true; mycol = k; mypiv = a[k];
     }
     __syncwarp();
-    const double piv = A[k][k];
+    const double piv = prow[k];
     if (!(fabs(piv) > thr) || !isfinite(piv)) bad = true;
-    if (lane != k) {
-      const double f = A[lane][k] / piv;
-      for (int c = k + 1; c < SB; ++c) A[lane][c] -= f * A[k][c];
-      for (int c = 0; c < SB; ++c) R[lane][c] -= f * R[k][c];
+    if (lane != p) {
+      const double f = a[k] / piv;
+#pragma unroll
+      for (int c = k + 1; c < SB; ++c) a[c] -= f * prow[c];
+#pragma unroll
+      for (int c = 0; c < SB; ++c) r[c] -= f * prow[SB + c];
     }
     __syncwarp();
   }
-  const double d = 1.0 / A[lane][lane];
-  for (int c = 0; c < SB; ++c) inv[lane * SB + c] = R[lane][c] * d;
+  const double d = 1.0 / mypiv;
+#pragma unroll
+  for (int c = 0; c < SB; ++c) inv[mycol * SB + c] = r[c] * d;
   if (bad && lane == 0) atomicCAS(info, 0, blk + 1);
 }
 
@@ -147,20 +156,20 @@ static int block_solve(double *Mx, int Hp, int Wd, double *invs, const double *s
     rc = gemm(t, st);
     if (rc) return rc;
   }
-  // back substitution: X_k = inv_k (R_k - sum_{j>k} M_kj X_j)
+  // back substitution, right-looking: X_k = inv_k R_k, then R_i -= M_ik X_k for every block row i above (wide, short
+  // GEMMs instead of 32-row dot products with a long k loop)
   const int nrhs = Wd - Hp;
   for (int k = nb - 1; k >= 0; --k) {
     const int r0 = k * SB;
     double *Rk = Mx + (int64_t)r0 * ld + Hp;
-    const int right = Hp - r0 - SB;
-    if (right > 0) {
-      GemmArgs s{Mx + (int64_t)r0 * ld + r0 + SB, ld, 1, Mx + (int64_t)(r0 + SB) * ld + Hp, ld, 1, Rk, ld, SB, nrhs, right, -1.0, 1.0};
-      int rc = gemm(s, st);
-      if (rc) return rc;
-    }
     GemmArgs x{invs + (size_t)k * SB * SB, SB, 1, Rk, ld, 1, Rk, ld, SB, nrhs, SB, 1.0, 0.0};
     int rc = gemm(x, st);
     if (rc) return rc;
+    if (r0 > 0) {
+      GemmArgs u{Mx + r0, ld, 1, Rk, ld, 1, Mx + Hp, ld, r0, nrhs, SB, -1.0, 1.0};
+      rc = gemm(u, st);
+      if (rc) return rc;
+    }
   }
   return EVO_OK;
 }
