@@ -479,6 +479,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # the version banner goes to stdout, which carries ONE JSON line
         dist.init_process_group("nccl", device_id=device)
     from evo_b200 import _lib
     from evo_b200.comm import Comm

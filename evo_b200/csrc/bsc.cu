@@ -149,7 +149,7 @@ __device__ __forceinline__ double warp_max_d(double v) {
 // 32: it lists the state's active latents once (SS_LS entries; longer states take the bit-scan path)
 // and issues one global f64 atomic per pair.  <s>_n is gathered latent by latent over the union of the
 // states' active latents (lane per latent, fixed summation order k = 0..S-1), so no shared-memory atomics.
-constexpr int SS_LS = 16, SS_LD = 18;  // list capacity / row stride in uint16 (9 words: conflict-free rows)
+constexpr int SS_LS = 32, SS_LD = 34;  // list capacity / row stride in uint16 (17 words: conflict-free rows)
 __host__ __device__ inline size_t suffstats_warp_bytes(int H, int Hw, int cols) {
   size_t b = (size_t)8 * H + (size_t)8 * cols;       // es, q
   b += ((size_t)4 * Hw + 7) & ~(size_t)7;             // union words

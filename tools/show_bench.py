@@ -4,7 +4,7 @@ import sys
 
 for f in sys.argv[1:]:
     try:
-        d = json.load(open(f))
+        d = json.loads([l for l in open(f) if l.startswith('{')][-1])
     except Exception as e:
         print(f, e)
         continue
