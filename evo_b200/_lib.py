@@ -119,6 +119,13 @@ SIGNATURES = {
     "evo_bsc_reconstruct": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp]),
     "evo_generate_data": (_i, [_vp, _vp, _d, _vp, _vp, _i, _d, _i64, _i64, _i, _i, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "evo_fma_peak": (_i, [_i, _i, C.POINTER(C.c_double)]),
+    "evo_bsc_full_logsumexp": (_i, [_i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _d, _d, _vp, _vp]),
+    "evo_es3c_full_logsumexp": (_i, [_i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _vp, _vp]),
+    "evo_comm_load": (_i, [C.c_char_p]),
+    "evo_comm_unique_id": (_i, [_vp]),
+    "evo_comm_init": (_i, [_i, _i, _vp, C.POINTER(C.c_void_p)]),
+    "evo_comm_allreduce": (_i, [_vp, _vp, _i64, _vp]),
+    "evo_comm_destroy": (_i, [_vp]),
     "evo_patches_count": (_i64, [_i, _i, _i, _i, _i]),
     "evo_patches_extract": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "evo_patches_merge": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),

@@ -229,10 +229,17 @@ class BSC(Model):
         dd = self.device_data(my_data)
         self.E_step_precompute(model_params, my_suff_stat, my_data)
         if full:
-            sm = my_suff_stat["sm"]
-            assert sm is not None, "full free energy needs the table of all states (H < 12)"
-            tab = pack_states(sm, self.device)  # includes the all-zero row: same value as the permanent state
-            lpj = self.lpj_all(model_params, my_data, tab, shared=True)
+            # all 2^H states enumerated on the device from their index (the reference tabulates them and stops at
+            # H < 12, utils.py:58-69); H <= 24 here
+            self._tables(model_params, dd)
+            c = dd.cache
+            Fs = torch.zeros(1, dtype=torch.float64, device=self.device)
+            ev = _lib.EVAL_BSC_DIRECT if dd.incomplete else _lib.EVAL_BSC_GRAM
+            self._call("evo_bsc_full_logsumexp", ev, dd.N, self.D, self.H, int(bool(my_suff_stat["permanent"]["background"])),
+                       _lib.ptr(c["W"]), _lib.ptr(dd.Y), _lib.ptr(dd.mask), _lib.ptr(c.get("G")), _lib.ptr(c.get("B")),
+                       _lib.ptr(c.get("ynorm2")), float(model_params["pre1"]), float(model_params["pil_bar"]), _lib.ptr(Fs))
+            self.comm.allreduce_(Fs)
+            return float(model_params["ljc"] + Fs.item() / dd.N_total)
         elif compute_lpj:
             lpj = self.lpj_all(model_params, my_data, my_suff_stat["ss_dev"])
             if my_suff_stat["S_perm"] > 0:

@@ -28,12 +28,49 @@ class Comm:
         self._on = dist.is_available() and dist.is_initialized() and not single
         self.rank = dist.get_rank(group) if self._on else 0
         self.size = dist.get_world_size(group) if self._on else 1
+        self._nccl = {}
 
     # ---- device / tensor path (one fused allreduce per EM iteration) -------------------------
+    def _native(self, device):
+        """NCCL communicator behind the library's own C-ABI (`evo_comm_*`, include/evo_b200.h), created lazily per
+        device: rank 0 makes the unique id, torch.distributed ships the 128 bytes (host plumbing), every rank joins.
+        EVO_COMM=torch keeps torch.distributed's all_reduce as the data plane."""
+        import ctypes as C
+        import os
+
+        if os.environ.get("EVO_COMM", "") == "torch" or dist.get_backend(self.group) != "nccl":
+            return None
+        key = str(device)
+        if key not in self._nccl:
+            from . import _lib
+
+            lib = _lib.load()
+            buf = (C.c_ubyte * 128)()
+            if self.rank == 0:
+                _lib.check(lib.evo_comm_unique_id(buf), "evo_comm_unique_id")
+            box = [bytes(buf)]
+            dist.broadcast_object_list(box, src=dist.get_global_rank(self.group, 0) if self.group is not None else 0,
+                                       group=self.group)
+            raw = (C.c_ubyte * 128).from_buffer_copy(box[0])
+            h = C.c_void_p()
+            with torch.cuda.device(device):
+                _lib.check(lib.evo_comm_init(self.rank, self.size, raw, C.byref(h)), "evo_comm_init")
+            self._nccl[key] = (lib, h)
+        return self._nccl[key]
+
     def allreduce_(self, t):
-        """In-place SUM all-reduce of a torch tensor (NCCL for CUDA tensors, gloo for CPU)."""
+        """In-place SUM all-reduce of a torch tensor: float64 CUDA tensors (the packed statistics) through
+        `evo_comm_allreduce` (NCCL via the C-ABI) on the current stream; anything else through torch.distributed."""
         if self.size > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            nat = self._native(t.device) if (t.is_cuda and t.dtype == torch.float64 and t.is_contiguous()) else None
+            if nat is not None:
+                from . import _lib
+
+                lib, h = nat
+                with torch.cuda.device(t.device):
+                    _lib.check(lib.evo_comm_allreduce(h, _lib.ptr(t), t.numel(), _lib.stream()), "evo_comm_allreduce")
+            else:
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return t
 
     # ---- mpi4py-shaped surface ---------------------------------------------------------------

@@ -562,6 +562,39 @@ extern "C" int evo_bsc_lpj(int eval, const uint32_t *states, int shared_states, 
   return EVO_ERR_ARG;
 }
 
+template <class Eval>
+static int launch_full(Eval ev, int64_t N, int Hm, uint32_t or_mask, double *out, cudaStream_t st) {
+  constexpr int T = 128;
+  const size_t smem = (sizeof(uint32_t) + sizeof(double)) * FULL_B + ev.smem_bytes(T);
+  auto k = full_logsumexp_kernel<Eval, T>;
+  if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k<<<grid_for((const void *)k, T, smem, N), T, smem, st>>>(ev, N, Hm, or_mask, out);
+  EVO_LAUNCH_CHECK("full_logsumexp");
+  return EVO_OK;
+}
+
+extern "C" int evo_bsc_full_logsumexp(int eval, int64_t N, int D, int H, int background, const double *W, const float *Y,
+                                      const uint8_t *mask, const double *G, const double *B, const double *ynorm2,
+                                      double pre1, double pil_bar, double *out, void *stream) {
+  EVO_REQUIRE(N >= 0 && D > 0 && H > 0 && out, "bad arguments");
+  const int Hm = background ? H - 1 : H;
+  EVO_REQUIRE(H <= 32 && Hm <= 24, "exact likelihood: at most 24 enumerated latents (2^24 states per datapoint)");
+  if (N == 0) return EVO_OK;
+  const uint32_t or_mask = background ? (1u << (H - 1)) : 0u;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (eval == EVO_EVAL_BSC_GRAM) {
+    EVO_REQUIRE(G && B && ynorm2 && !mask, "gram evaluator needs G, B, ynorm2 and complete data");
+    BscGramEval ev{G, B, ynorm2, pre1, pil_bar, H, 1, nullptr, nullptr, 0.0};
+    return launch_full(ev, N, Hm, or_mask, out, st);
+  } else if (eval == EVO_EVAL_BSC_DIRECT) {
+    EVO_REQUIRE(W && Y, "direct evaluator needs W, Y");
+    BscDirectEval ev{W, Y, mask, pre1, pil_bar, D, H, 1, nullptr, nullptr, 0.0};
+    return launch_full(ev, N, Hm, or_mask, out, st);
+  }
+  set_error("evo_bsc_full_logsumexp: unknown evaluator %d", eval);
+  return EVO_ERR_ARG;
+}
+
 extern "C" int evo_free_energy(const double *lpj, int64_t N, int cols, int64_t ld, double *out, void *stream) {
   EVO_REQUIRE(N >= 0 && cols > 0 && ld >= cols, "bad sizes");
   if (N == 0) return EVO_OK;

@@ -301,3 +301,41 @@ extern "C" int evo_es3c_lpj(const uint32_t *states, int shared_states, int64_t N
   EVO_LAUNCH_CHECK("es3c_lpj");
   return EVO_OK;
 }
+
+extern "C" int evo_es3c_full_logsumexp(int64_t N, int D, int H, int background, const double *Wt, const float *Y,
+                                       const uint8_t *mask, const double *G, const double *B, const double *ynorm2,
+                                       const double *Psi, const double *mus, const double *pil_bar_h, double sigma2,
+                                       double *out, void *stream) {
+  EVO_REQUIRE(N >= 0 && D > 0 && H > 0 && out, "bad arguments");
+  EVO_REQUIRE(Psi && mus && pil_bar_h && sigma2 > 0.0, "model tables");
+  const int Hm = background ? H - 1 : H;
+  EVO_REQUIRE(H <= 32 && Hm <= 24, "exact likelihood: at most 24 enumerated latents (2^24 states per datapoint)");
+  if (N == 0) return EVO_OK;
+  Es3cEval ev;
+  memset(&ev, 0, sizeof(ev));
+  ev.Psi = Psi; ev.mus = mus; ev.pil_bar = pil_bar_h;
+  ev.s2i = (double)(1.0L / (long double)sigma2);
+  ev.D = D; ev.H = H; ev.Hw = 1;
+  current_scratch(ev.scratch, ev.scratch_warps);
+  if (mask) {
+    EVO_REQUIRE(Wt && Y, "incomplete data needs Wt and Y");
+    ev.masked = 1; ev.Wt = Wt; ev.Y = Y; ev.mask = mask;
+  } else {
+    EVO_REQUIRE(G && B && ynorm2, "complete data needs G, B, ynorm2");
+    ev.masked = 0; ev.G = G; ev.B = B; ev.ynorm2 = ynorm2;
+  }
+  ev.max_batch = FULL_B;
+  constexpr int T = 128;
+  const size_t smem = (sizeof(uint32_t) + sizeof(double)) * FULL_B + ev.smem_bytes(T);
+  auto k = full_logsumexp_kernel<Es3cEval, T>;
+  if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 1;
+  EVO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, T, smem));
+  if (per_sm < 1) per_sm = 1;
+  int64_t g = (int64_t)sm_count() * per_sm;
+  if (g > N) g = N;
+  const uint32_t or_mask = background ? (1u << (H - 1)) : 0u;
+  k<<<(int)g, T, smem, (cudaStream_t)stream>>>(ev, N, Hm, or_mask, out);
+  EVO_LAUNCH_CHECK("es3c_full_logsumexp");
+  return EVO_OK;
+}

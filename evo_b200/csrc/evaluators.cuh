@@ -222,5 +222,46 @@ __global__ void __launch_bounds__(T) lpj_kernel(Eval ev, const uint32_t *__restr
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Exact log-likelihood term (free_energy(full=True), _models.py:334-451 over the state table of
+// variational/utils.py:58-69): sum_n logsumexp over ALL 2^Hm states, enumerated on the fly from the state index
+// (one packed word, Hm <= 24; or_mask = the always-on background bit) instead of materialising the table
+// ((2^H, H) bools in the reference, which caps it at H < 12).  One CTA per datapoint, batches of FULL_B states
+// through the evaluator's own eval_batch, running (max, sum) per thread.
+// ------------------------------------------------------------------------------------------
+constexpr int FULL_B = 1024;
+template <class Eval, int T>
+__global__ void __launch_bounds__(T) full_logsumexp_kernel(Eval ev, int64_t N, int Hm, uint32_t or_mask, double *out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ double red_d[8];
+  uint32_t *st = reinterpret_cast<uint32_t *>(smem_raw);
+  double *val = reinterpret_cast<double *>(smem_raw + sizeof(uint32_t) * FULL_B);
+  unsigned char *ev_smem = smem_raw + (sizeof(uint32_t) + sizeof(double)) * FULL_B;
+  const uint32_t total = 1u << Hm;
+  double acc = 0.0;
+  for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
+    __syncthreads();
+    ev.template setup<T>(n, ev_smem);
+    __syncthreads();
+    double m = -DBL_MAX, ssum = 0.0;
+    for (uint32_t base = 0; base < total; base += FULL_B) {
+      const int cnt = (int)(total - base < (uint32_t)FULL_B ? total - base : (uint32_t)FULL_B);
+      for (int i = threadIdx.x; i < cnt; i += T) st[i] = (base + (uint32_t)i) | or_mask;
+      __syncthreads();
+      unsigned fl = 0;
+      ev.template eval_batch<T>(st, 1, cnt, val, fl);
+      __syncthreads();
+      for (int i = threadIdx.x; i < cnt; i += T) {
+        const double v = val[i];
+        if (v > m) { ssum = ssum * exp(m - v) + 1.0; m = v; } else { ssum += exp(v - m); }
+      }
+      __syncthreads();
+    }
+    const double gm = group_max<T>(m, red_d);
+    const double gs = group_sum<T>(ssum > 0.0 ? ssum * exp(m - gm) : 0.0, red_d);
+    if (threadIdx.x == 0) acc += gm + log(gs);
+  }
+  if (threadIdx.x == 0 && acc != 0.0) atomicAdd(out, acc);
+}
 
 }  // namespace evo

@@ -347,9 +347,16 @@ class SSSC(Model):
         dd = self.device_data(my_data)
         self.E_step_precompute(model_params, my_suff_stat, my_data)
         if full:
-            sm = my_suff_stat["sm"]
-            assert sm is not None, "full free energy needs the table of all states (H < 12)"
-            lpj = self.lpj_all(model_params, my_data, pack_states(sm, self.device), shared=True)
+            # all 2^H states enumerated on the device from their index (H <= 24; the reference stops at H < 12)
+            self._tables(model_params, dd)
+            c = dd.cache
+            Fs = torch.zeros(1, dtype=torch.float64, device=self.device)
+            self._call("evo_es3c_full_logsumexp", dd.N, self.D, self.H, int(bool(my_suff_stat["permanent"]["background"])),
+                       _lib.ptr(c["Wt"]), _lib.ptr(dd.Y), _lib.ptr(dd.mask), _lib.ptr(c.get("G")), _lib.ptr(c.get("B")),
+                       _lib.ptr(c.get("ynorm2")), _lib.ptr(c["Psi"]), _lib.ptr(c["mus"]), _lib.ptr(c["pil"]),
+                       float(model_params["sigma2"]), _lib.ptr(Fs))
+            self.comm.allreduce_(Fs)
+            return float(model_params["ljc"] + Fs.item() / dd.N_total)
         elif compute_lpj:
             lpj = self.lpj_all(model_params, my_data, my_suff_stat["ss_dev"])
             if my_suff_stat["S_perm"] > 0:

@@ -295,6 +295,29 @@ typedef struct evo_es3c_stats_args {
 } evo_es3c_stats_args;
 int evo_es3c_suffstats(const evo_es3c_stats_args *args, void *stream);
 
+/* ---- exact log-likelihood (Model.free_energy(full=True), evo/models/_models.py:334-451; state table
+ * evo/variational/utils.py:58-69) -- *out += sum_n logsumexp over ALL 2^Hm states of the model's log-pseudo-joint, the
+ * states enumerated on the fly from their index (no table: the reference materialises (2^H, H) bools and stops at
+ * H < 12).  Hm = H (or H - 1 with a background unit, whose bit is forced on) <= 24, H <= 32.  Arguments as for
+ * evo_bsc_lpj / evo_es3c_lpj. */
+int evo_bsc_full_logsumexp(int eval, int64_t N, int D, int H, int background, const double *W, const float *Y,
+                           const uint8_t *mask, const double *G, const double *B, const double *ynorm2, double pre1,
+                           double pil_bar, double *out, void *stream);
+int evo_es3c_full_logsumexp(int64_t N, int D, int H, int background, const double *Wt, const float *Y, const uint8_t *mask,
+                            const double *G, const double *B, const double *ynorm2, const double *Psi, const double *mus,
+                            const double *pil_bar_h, double sigma2, double *out, void *stream);
+
+/* ---- communicator: the one collective of an EM iteration (replaces evo/utils/parallel.py:45-67 and the ~15
+ * Allreduce / Bcast calls per iteration of bsc.py:230-274, sssc.py:671-690, _models.py:139,156) -----------------------
+ * NCCL resolved at run time (the copy already loaded by the process, else libnccl.so.2, else evo_comm_load(path)).
+ * evo_comm_unique_id fills 128 bytes on one rank; the caller ships them to every rank (any host channel); each rank
+ * calls evo_comm_init on its own device (collective).  evo_comm_allreduce: in-place SUM of `count` float64 on `stream`. */
+int evo_comm_load(const char *libnccl_path);
+int evo_comm_unique_id(void *id128);
+int evo_comm_init(int rank, int world, const void *id128, void **comm_out);
+int evo_comm_allreduce(void *comm, double *buf, int64_t count, void *stream);
+int evo_comm_destroy(void *comm);
+
 /* ---- device-side setup ----------------------------------------------------------------
  * Model.generate_data (evo/models/_models.py:73-99) -> BSC.generate_from_hidden (bsc.py:27-57) /
  * SSSC.generate_from_hidden (sssc.py:66-102): s_h ~ Bernoulli(pies[h]) (pies NULL: the scalar `pi`),

@@ -181,3 +181,35 @@ def test_pack_unpack_roundtrip_and_init_states():
                 assert ss[n][:, -1].all()
         mean_on = ss[:, :, : (H - 1 if perm and perm["background"] else H)].mean()
         assert mean_on < 6.0 / H
+
+
+@pytest.mark.parametrize("model", ["bsc", "bsc_missing", "es3c", "es3c_missing"])
+def test_free_energy_full_enumerated_equals_table_path(model):
+    """free_energy(full=True) enumerates the 2^H states on the device (evo_*_full_logsumexp); for H = 13 -- beyond the
+    reference's H < 12 cap -- it must equal the log-likelihood computed from an explicit state table through the
+    stand-alone lpj kernels (the route validated against the reference at H = 10 above)."""
+    import torch
+
+    from evo_b200.bsc import BSC
+    from evo_b200.sssc import SSSC
+    from evo_b200.variational import all_states, init_states, pack_states
+
+    D, H, N = 9, 13, 40
+    rng = np.random.RandomState(5)
+    Y = (rng.normal(size=(N, D)) * 2).astype(np.float32).astype(np.float64)
+    X = rng.random_sample((N, D)) > 0.25 if "missing" in model else None
+    data = {"y": np.where(X, Y, np.nan) if X is not None else Y, "x_infr": X}
+    if model.startswith("bsc"):
+        m = BSC(D, H, 8)
+        th = m.check_params({"W": rng.normal(size=(D, H)), "pi": 0.15, "sigma": 1.1})
+    else:
+        m = SSSC(D, H, 8)
+        A = rng.normal(size=(H, H)) * 0.2
+        th = m.check_params({"W": rng.normal(size=(D, H)), "pies": rng.uniform(0.05, 0.3, size=H), "mus": rng.normal(size=H) + 1,
+                             "Psi": np.eye(H) + A @ A.T, "sigma2": np.float64(1.2)})
+    cont = init_states(N, 8, H, "fit", "randflip", 2, 1, 1)
+    L = m.free_energy(data, th, cont, full=True)
+    tab = pack_states(all_states(H), m.device)
+    lpj = m.lpj_all(th, data, tab, shared=True)
+    want = float(th["ljc"] + m._sum_logsumexp(lpj).item() / N)
+    assert abs(L - want) < 1e-11 * abs(want), (L, want)
