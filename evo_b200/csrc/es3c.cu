@@ -29,6 +29,7 @@ int es3c_launch_estep(const EstepDev &dv, const evo_estep_args *x, cudaStream_t 
   if (x->mask) {
     EVO_REQUIRE(x->W && x->Y, "es3c with incomplete data needs Wt (in W) and Y");
     ev.masked = 1; ev.Wt = x->W; ev.Y = x->Y; ev.mask = x->mask;
+    if (x->G && x->B && x->ynorm2 && dv.D <= 65535) { ev.masked = 2; ev.G = x->G; ev.B = x->B; ev.ynorm2 = x->ynorm2; }
   } else {
     EVO_REQUIRE(x->G && x->B && x->ynorm2, "es3c with complete data needs G, B, ynorm2");
     ev.masked = 0; ev.G = x->G; ev.B = x->B; ev.ynorm2 = x->ynorm2;
@@ -116,7 +117,7 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
       for (int i = threadIdx.x; i < cols; i += T) q[i] *= inv;
     }
     __syncthreads();
-    if (ev.masked) ev.yn2 = ev.masked_yn2();
+    if (ev.masked == 1) ev.yn2 = ev.masked_yn2();
     // ---- per-state moments, one warp per state -------------------------------------------------
     const uint32_t *stn = a.states + n * (int64_t)S * Hw;
     for (int k = warp; k < S; k += T / 32) {
@@ -243,6 +244,7 @@ extern "C" int evo_es3c_suffstats(const evo_es3c_stats_args *x, void *stream) {
   ev.Wt = x->Wt; ev.Y = x->Y;
   if (x->mask) {
     ev.masked = 1; ev.mask = x->mask;
+    if (x->G && x->B && x->ynorm2 && x->D <= 65535) { ev.masked = 2; ev.G = x->G; ev.B = x->B; ev.ynorm2 = x->ynorm2; }
   } else {
     EVO_REQUIRE(x->G && x->B && x->ynorm2, "complete data needs G, B, ynorm2");
     ev.masked = 0; ev.G = x->G; ev.B = x->B; ev.ynorm2 = x->ynorm2;
@@ -283,6 +285,7 @@ extern "C" int evo_es3c_lpj(const uint32_t *states, int shared_states, int64_t N
   if (mask) {
     EVO_REQUIRE(Wt && Y, "incomplete data needs Wt and Y");
     ev.masked = 1; ev.Wt = Wt; ev.Y = Y; ev.mask = mask;
+    if (G && B && ynorm2 && D <= 65535) { ev.masked = 2; ev.G = G; ev.B = B; ev.ynorm2 = ynorm2; }
   } else {
     EVO_REQUIRE(G && B && ynorm2, "complete data needs G, B, ynorm2");
     ev.masked = 0; ev.G = G; ev.B = B; ev.ynorm2 = ynorm2;
@@ -320,6 +323,7 @@ extern "C" int evo_es3c_full_logsumexp(int64_t N, int D, int H, int background, 
   if (mask) {
     EVO_REQUIRE(Wt && Y, "incomplete data needs Wt and Y");
     ev.masked = 1; ev.Wt = Wt; ev.Y = Y; ev.mask = mask;
+    if (G && B && ynorm2 && D <= 65535) { ev.masked = 2; ev.G = G; ev.B = B; ev.ynorm2 = ynorm2; }
   } else {
     EVO_REQUIRE(G && B && ynorm2, "complete data needs G, B, ynorm2");
     ev.masked = 0; ev.G = G; ev.B = B; ev.ynorm2 = ynorm2;

@@ -26,7 +26,9 @@ struct Es3cEval {
   // model
   const double *Psi, *mus, *pil_bar;  // [H][H], [H], [H]
   double s2i;
-  int D, H, Hw, masked;
+  int D, H, Hw, masked;  // masked: 0 complete data; 1 incomplete, Gram accumulated from W' rows under the mask per state;
+                         // 2 incomplete with tables: G_AA = (W'W)_AA - sum_{d missing} W_dA' W_dA, b = (Y W)_A (Y is 0 where
+                         // missing) -- |missing| instead of |observed| terms per pair, and no per-state reductions over D
   double *scratch;       // global per-warp workspaces for 16 < a <= 32 (or NULL)
   int scratch_warps;     // capacity of `scratch` in warps
   int max_batch;         // largest cnt eval_batch will see (index lists of the small / large systems); 0 = no lists
@@ -36,6 +38,17 @@ struct Es3cEval {
   unsigned char *wsm;    // smem per-warp area base
   unsigned char *lsm;    // smem: int counters[2] + uint16 small[max_batch] + uint16 big[max_batch]
   double yn2;
+  uint16_t *miss;        // smem (masked == 2): missing observables of this datapoint, ascending
+  const int *nmiss_ptr;  // smem: their number
+
+  // sum over the missing observables of W_dh W_dh' (the part of (W'W)_hh' this datapoint must not count)
+  __device__ __forceinline__ double miss_corr(int h, int h2) const {
+    const int nm = *nmiss_ptr;
+    const double *wa = Wt + (int64_t)h * D, *wb = Wt + (int64_t)h2 * D;
+    double c = 0.0;
+    for (int q = 0; q < nm; ++q) { const int d = miss[q]; c += __ldg(wa + d) * __ldg(wb + d); }
+    return c;
+  }
 
   static constexpr int AS = 16, LDS = 17;   // shared-memory path
   static constexpr int AG = 32, LDGL = 33;  // global-scratch path
@@ -45,19 +58,20 @@ struct Es3cEval {
   static constexpr size_t WARP_SCRATCH = 3 * AG * LDGL;  // doubles
 
   __host__ __device__ size_t head_bytes() const {
-    return masked ? align8((size_t)D * sizeof(double)) + align8((size_t)D) : align8((size_t)H * sizeof(double));
+    if (masked == 1) return align8((size_t)D * sizeof(double)) + align8((size_t)D);
+    return align8((size_t)H * sizeof(double)) + (masked == 2 ? align8(48 + (size_t)2 * D) : 0);
   }
   __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(8 + (size_t)4 * max_batch) : 0; }
   static constexpr bool kList = false;
   __host__ __device__ size_t smem_bytes(int T, bool = false) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM + list_bytes(); }
   // measured (cfg3/cfg4, 64 states + 64 children): complete data is fastest with 4 warps and more resident
   // CTAs, masked data (a D-long Gram gather per system) with 8 warps per datapoint
-  __host__ int threads_hint(int work) const { return work < 64 ? 64 : (masked ? 256 : 128); }
+  __host__ int threads_hint(int work) const { return work < 64 ? 64 : (masked == 1 ? 256 : 128); }
 
   template <int T>
   __device__ void setup(int64_t n, unsigned char *smem) {
     vec = reinterpret_cast<double *>(smem);
-    if (masked) {
+    if (masked == 1) {
       m = smem + align8((size_t)D * sizeof(double));
       for (int d = threadIdx.x; d < D; d += T) {
         uint8_t ok = mask[n * (int64_t)D + d];
@@ -68,6 +82,22 @@ struct Es3cEval {
       const double *src = B + n * (int64_t)H;
       for (int i = threadIdx.x; i < H; i += T) vec[i] = __ldg(src + i);
       yn2 = __ldg(ynorm2 + n);
+      if (masked == 2) {  // ordered list of this datapoint's missing observables: [8 ints scratch | count | uint16 list]
+        int *scr = reinterpret_cast<int *>(smem + align8((size_t)H * sizeof(double)));
+        miss = reinterpret_cast<uint16_t *>(scr + 12);
+        int cnt = 0;
+        for (int d0 = 0; d0 < D; d0 += T) {
+          const int d = d0 + threadIdx.x;
+          const bool f = d < D && !mask[n * (int64_t)D + d];
+          int tot;
+          const int off = group_scan_flag<T>(f, tot, scr);
+          if (f) miss[cnt + off] = (uint16_t)d;
+          cnt += tot;
+          gsync<T>();
+        }
+        if (threadIdx.x == 0) scr[8] = cnt;
+        nmiss_ptr = scr + 8;
+      }
     }
     wsm = smem + head_bytes();
     lsm = wsm + (size_t)(T / 32) * WARP_SMEM;
@@ -128,11 +158,19 @@ struct Es3cEval {
   __device__ __forceinline__ double gather(int a, const uint16_t *idx, double *A1, double *A2, int ld, double &ynorm) const {
     const int lane = threadIdx.x & 31;
     double bi = 0.0;
-    if (!masked) {
+    if (masked != 1) {
       if (lane < a) {
         int h = idx[lane];
         const double *Gr = G + (int64_t)h * H;
-        for (int l = 0; l < a; ++l) A1[lane * ld + l] = __ldg(Gr + idx[l]);
+        if (masked == 2) {
+          for (int l = 0; l <= lane; ++l) {
+            const double v = __ldg(Gr + idx[l]) - miss_corr(h, idx[l]);
+            A1[lane * ld + l] = v;
+            A1[l * ld + lane] = v;
+          }
+        } else {
+          for (int l = 0; l < a; ++l) A1[lane * ld + l] = __ldg(Gr + idx[l]);
+        }
         bi = vec[h];
       }
       ynorm = yn2;
@@ -302,11 +340,19 @@ struct Es3cEval {
     const bool act = sl < a;
     // gather G_AA -> A1, Psi_AA -> A2, b_i
     double bi = 0.0;
-    if (!masked) {
+    if (masked != 1) {
       if (act) {
         const int h = idx[sl];
         const double *Gr = G + (int64_t)h * H;
-        for (int l = 0; l < a; ++l) A1[sl * LD8 + l] = __ldg(Gr + idx[l]);
+        if (masked == 2) {
+          for (int l = 0; l <= sl; ++l) {
+            const double v = __ldg(Gr + idx[l]) - miss_corr(h, idx[l]);
+            A1[sl * LD8 + l] = v;
+            A1[l * LD8 + sl] = v;
+          }
+        } else {
+          for (int l = 0; l < a; ++l) A1[sl * LD8 + l] = __ldg(Gr + idx[l]);
+        }
         bi = vec[h];
       }
     } else {
@@ -402,7 +448,7 @@ struct Es3cEval {
 
   template <int T, bool LIST = false>
   __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) {
-    if (masked) yn2 = masked_yn2();
+    if (masked == 1) yn2 = masked_yn2();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // split the batch by |s|: systems with a <= 8 are packed four per warp (without list space every
     // state goes to the warp-per-state solver)
@@ -443,7 +489,7 @@ struct Es3cEval {
     }
   }
   __device__ double eval_zero(unsigned &flags) {
-    if (masked) yn2 = masked_yn2();
+    if (masked == 1) yn2 = masked_yn2();
     return lpj_sanitise(-0.5 * s2i * yn2, flags);
   }
 };

@@ -137,8 +137,8 @@ class SSSC(Model):
         c["Psi"] = _dev(model_params["Psi"], self.device, torch.float64)
         c["mus"] = _dev(model_params["mus"], self.device, torch.float64)
         c["pil"] = _dev(pil if pil is not None else model_params["pil_bar"], self.device, torch.float64)
-        if dd.incomplete:
-            return
+        # incomplete data use the same tables (Y is 0 where missing, so B = Y W sums over the observed entries) plus a
+        # per-datapoint correction of G over the MISSING observables inside the evaluator (es3c.cuh, masked == 2)
         if "G" not in c:
             c["G"] = torch.empty((H, H), dtype=torch.float64, device=self.device)
             c["B"] = torch.empty((dd.N, H), dtype=torch.float64, device=self.device)
@@ -158,8 +158,7 @@ class SSSC(Model):
         a.Y = dd.Y.data_ptr()
         if dd.incomplete:
             a.W, a.mask = c["Wt"].data_ptr(), dd.mask.data_ptr()
-        else:
-            a.G, a.B, a.ynorm2 = c["G"].data_ptr(), c["B"].data_ptr(), c["ynorm2"].data_ptr()
+        a.G, a.B, a.ynorm2 = c["G"].data_ptr(), c["B"].data_ptr(), c["ynorm2"].data_ptr()
 
     # ---- E-step: fused kernel over the shard (sssc.py:510-548) -------------------------------------------
     def E_step(self, model_params, my_suff_stat, my_data):
@@ -201,8 +200,7 @@ class SSSC(Model):
         a.states, a.lpj, a.Y = ss["ss_dev"].data_ptr(), ss["lpj_dev"].data_ptr(), dd.Y.data_ptr()
         a.mask = dd.mask.data_ptr() if dd.incomplete else None
         a.recon_keep = dd.keep.data_ptr() if dd.keep is not None else None
-        if not dd.incomplete:
-            a.G, a.B, a.ynorm2 = c["G"].data_ptr(), c["B"].data_ptr(), c["ynorm2"].data_ptr()
+        a.G, a.B, a.ynorm2 = c["G"].data_ptr(), c["B"].data_ptr(), c["ynorm2"].data_ptr()
         a.Wt, a.Psi, a.mus = c["Wt"].data_ptr(), c["Psi"].data_ptr(), c["mus"].data_ptr()
         a.sigma2 = float(model_params["sigma2"])
         a.stats = stats.data_ptr()
