@@ -118,6 +118,8 @@ SIGNATURES = {
     "evo_es3c_suffstats": (_i, [C.POINTER(Es3cStatsArgs), _vp]),
     "evo_bsc_reconstruct": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp]),
     "evo_generate_data": (_i, [_vp, _vp, _d, _vp, _vp, _i, _d, _i64, _i64, _i, _i, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "evo_column_moments": (_i, [_vp, _vp, _i64, _i, _vp, _vp]),
+    "evo_normal_fill": (_i, [_vp, _i64, _i, _vp, _d, _u64, _vp]),
     "evo_fma_peak": (_i, [_i, _i, C.POINTER(C.c_double)]),
     "evo_bsc_full_logsumexp": (_i, [_i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _d, _d, _vp, _vp]),
     "evo_es3c_full_logsumexp": (_i, [_i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _vp, _vp]),

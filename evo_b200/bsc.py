@@ -35,35 +35,27 @@ class BSC(Model):
     def standard_init(self, my_data, W_init=None, pi_init=None, sigma_init=None):
         dd = self.device_data(my_data)
         D, H = self.D, self.H
-        Y = dd.Y.double()
+        ssum, ssq, cnt = self._column_moments(dd)
         if not dd.incomplete:
-            tot = torch.cat([Y.sum(0), (Y * Y).sum(0)])
-            self.comm.allreduce_(tot)
-            y_mean = tot[:D] / dd.N_total
-            var = tot[D:] / dd.N_total - y_mean * y_mean
+            y_mean = ssum / dd.N_total
+            var = ssq / dd.N_total - y_mean * y_mean
             sig = float(torch.sqrt(var.clamp_min(0).sum() / D).item())
         else:
-            m = dd.mask.double()
-            tot = torch.cat([(Y * m).sum(0), m.sum(0)])
-            self.comm.allreduce_(tot)
-            y_mean = tot[:D] / tot[D:].clamp_min(1.0)
-            r = (((Y - y_mean) * m) ** 2).sum().reshape(1)
-            self.comm.allreduce_(r)
-            sig = float(torch.sqrt(r / dd.n_obs_total).item())
+            y_mean = ssum / cnt.clamp_min(1.0)
+            r = (ssq - 2.0 * y_mean * ssum + cnt * y_mean * y_mean).sum()  # sum over observed entries of (y - mean_d)^2
+            sig = float(torch.sqrt(r.clamp_min(0) / dd.n_obs_total).item())
         if sigma_init is None:
             sigma_init = sig
             assert sigma_init > 0.0
-        y_mean = y_mean.cpu().numpy()
         if not isinstance(W_init, np.ndarray):
             if W_init == "random_uniform":
                 W_init = self.comm.bcast(np.random.random((D, H)))
             elif W_init == "normal":
-                W_init = self.comm.bcast(np.random.normal(0, 5, [D, H]))
+                W_init = self._noisy_init(None, 5.0).cpu().numpy()
             elif W_init == "data_mean":
-                W_init = np.tile(y_mean[:, None], (1, H))
+                W_init = np.tile(y_mean.cpu().numpy()[:, None], (1, H))
             else:
-                noise = self.comm.bcast(np.random.normal(scale=sigma_init / 4.0, size=[D, H]))
-                W_init = y_mean[:, None] + noise
+                W_init = self._noisy_init(y_mean, sigma_init / 4.0).cpu().numpy()
         if pi_init is None:
             pi_init = 1.0 / H
         return {"W": W_init, "pi": pi_init, "sigma": sigma_init}

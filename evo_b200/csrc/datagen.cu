@@ -144,6 +144,38 @@ __global__ void __launch_bounds__(32 * GEN_WARPS) generate_kernel(GenArgs a) {
   }
 }
 
+// ---- standard_init on the device (_models.py:206-283, sssc.py:104-197) ---------------------------------------------
+// column moments of the (masked) data: out[0..D) = sum_n m y, out[D..2D) = sum_n m y^2, out[2D..3D) = sum_n m
+__global__ void __launch_bounds__(256) column_moments_kernel(const float *__restrict__ Y, const uint8_t *__restrict__ mask,
+                                                             int64_t N, int D, double *__restrict__ out) {
+  // thread = column (coalesced rows), CTA = slab of rows
+  const int64_t rows_per = (N + gridDim.y - 1) / gridDim.y;
+  const int64_t lo = blockIdx.y * rows_per, hi = lo + rows_per < N ? lo + rows_per : N;
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= D) return;
+  double s = 0.0, s2 = 0.0, c = 0.0;
+  for (int64_t n = lo; n < hi; ++n) {
+    const bool ok = !mask || mask[n * D + d];
+    if (ok) { const double v = (double)Y[n * D + d]; s += v; s2 += v * v; c += 1.0; }
+  }
+  atomicAdd(out + d, s);
+  atomicAdd(out + D + d, s2);
+  atomicAdd(out + 2 * D + d, c);
+}
+// out[i][j] = (row_mean ? row_mean[i] : 0) + scale * N(0,1)   (rows x cols), Philox keyed by (seed, element index)
+__global__ void __launch_bounds__(256) normal_fill_kernel(double *__restrict__ out, int64_t rows, int cols,
+                                                          const double *__restrict__ row_mean, double scale, uint64_t seed) {
+  const Philox ph(seed);
+  const int64_t tot = rows * cols, pairs = (tot + 1) / 2;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < pairs; t += (int64_t)gridDim.x * blockDim.x) {
+    double c, s;
+    box_muller(ph((uint32_t)t, (uint32_t)(t >> 32), 0x1A17u, 0u), c, s);
+    const int64_t i0 = 2 * t, i1 = 2 * t + 1;
+    out[i0] = (row_mean ? row_mean[i0 / cols] : 0.0) + scale * c;
+    if (i1 < tot) out[i1] = (row_mean ? row_mean[i1 / cols] : 0.0) + scale * s;
+  }
+}
+
 // ---- FMA throughput: 8 independent accumulator chains per thread, `iters` x 8 FMAs ---------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) fma_peak_kernel(T *out, int iters, T x0) {
@@ -222,5 +254,28 @@ extern "C" int evo_fma_peak(int dtype, int iters, double *tflops_out) {
   cudaFree(buf);
   const double flop = 2.0 * 64.0 * (double)iters * (double)blocks * threads;
   *tflops_out = flop / (best * 1e-3) / 1e12;
+  return EVO_OK;
+}
+
+extern "C" int evo_column_moments(const float *Y, const uint8_t *mask, int64_t N, int D, double *out, void *stream) {
+  EVO_REQUIRE(Y && out && N >= 0 && D > 0, "bad arguments");
+  if (N == 0) return EVO_OK;
+  int slabs = (int)((N + 511) / 512);
+  const int cap = sm_count() * 8;
+  if (slabs > cap) slabs = cap;
+  dim3 grid((D + 255) / 256, slabs);
+  column_moments_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(Y, mask, N, D, out);
+  EVO_LAUNCH_CHECK("column_moments");
+  return EVO_OK;
+}
+
+extern "C" int evo_normal_fill(double *out, int64_t rows, int cols, const double *row_mean, double scale, uint64_t seed,
+                               void *stream) {
+  EVO_REQUIRE(out && rows >= 0 && cols > 0, "bad arguments");
+  if (rows == 0) return EVO_OK;
+  const int64_t pairs = (rows * cols + 1) / 2;
+  int64_t b = (pairs + 255) / 256, cap = (int64_t)sm_count() * 8;
+  normal_fill_kernel<<<(int)(b < cap ? b : cap), 256, 0, (cudaStream_t)stream>>>(out, rows, cols, row_mean, scale, seed);
+  EVO_LAUNCH_CHECK("normal_fill");
   return EVO_OK;
 }

@@ -329,6 +329,24 @@ class Model:
         self._call("evo_free_energy", _lib.ptr(lpj), lpj.shape[0], lpj.shape[1], lpj.stride(0), _lib.ptr(out))
         return out
 
+    # ---- standard_init helpers (_models.py:206-283, sssc.py:104-197): statistics and noise on the device ----------
+    def _column_moments(self, dd):
+        """(sum_n m y, sum_n m y^2, sum_n m) per observable over ALL ranks: one kernel, one all-reduce."""
+        D = self.D
+        tot = torch.zeros(3 * D, dtype=torch.float64, device=self.device)
+        self._call("evo_column_moments", _lib.ptr(dd.Y), _lib.ptr(dd.mask), dd.N, D, _lib.ptr(tot))
+        self.comm.allreduce_(tot)
+        return tot[:D], tot[D:2 * D], tot[2 * D:]
+
+    def _noisy_init(self, row_mean, scale):
+        """[D][H] = row_mean[:, None] + scale N(0,1), filled on every rank from one Philox seed (taken from NumPy's
+        global generator on rank 0, so `np.random.seed` keeps runs reproducible; the reference broadcasts the noise)."""
+        seed = int(self.comm.bcast(int(np.random.randint(0, 2 ** 31 - 1))))
+        W = torch.empty((self.D, self.H), dtype=torch.float64, device=self.device)
+        self._call("evo_normal_fill", _lib.ptr(W), self.D, self.H, _lib.ptr(row_mean.contiguous()) if row_mean is not None else None,
+                   float(scale), seed)
+        return W
+
     # ---- data generation (_models.py:73-99) on the device ------------------------------------------------
     def generate_data(self, model_params, my_N, seed=None, n_offset=0, device_only=False):
         """`Model.generate_data(model_params, my_N)` of the reference (_models.py:73-99): draws the hidden states

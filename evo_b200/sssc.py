@@ -74,29 +74,21 @@ class SSSC(Model):
         th["pies"] = self.comm.bcast(np.random.uniform(low=0.1, high=0.5, size=[H]))
         th["mus"] = self.comm.bcast(np.random.normal(0, 1, [H])) if "mus" in self.to_learn else np.ones(H)
         th["Psi"] = np.diag(np.ones(H))
-        Y = dd.Y.double()
-        m = dd.mask.double() if dd.incomplete else torch.ones_like(Y)
-        tot = torch.cat([(Y * m).sum(0), m.sum(0)])
-        self.comm.allreduce_(tot)
-        if dd.incomplete:
-            y_mean = tot[:D] / dd.N_total  # the reference divides the masked sums by N (sssc.py:150)
-        else:
-            y_mean = tot[:D] / dd.N_total
+        ssum, ssq, cnt = self._column_moments(dd)
+        y_mean = ssum / dd.N_total  # the reference divides the masked sums by N in both cases (sssc.py:150)
         if sigma_init is None:
-            r = (((Y - y_mean) * m) ** 2).sum().reshape(1)
-            self.comm.allreduce_(r)
+            r = float((ssq - 2.0 * y_mean * ssum + cnt * y_mean * y_mean).sum().item())  # sum_obs (y - y_mean_d)^2
             if dd.incomplete:
-                th["sigma2"] = np.float64(r.item() / dd.n_obs_total + 0.001)
+                th["sigma2"] = np.float64(r / dd.n_obs_total + 0.001)
             else:  # mean of the diagonal of the unbiased covariance (np.cov), sssc.py:172
-                th["sigma2"] = np.float64(r.item() / D / max(dd.N_total - 1, 1) + 0.001)
+                th["sigma2"] = np.float64(r / D / max(dd.N_total - 1, 1) + 0.001)
         else:
             th["sigma2"] = np.float64(sigma_init)
-        y_mean = y_mean.cpu().numpy()
         if not isinstance(W_init, np.ndarray):
             if W_init == "normal":
-                th["W"] = self.comm.bcast(np.random.normal(0, 5, [D, H]))
+                th["W"] = self._noisy_init(None, 5.0).cpu().numpy()
             else:
-                th["W"] = self.comm.bcast(y_mean[:, None] + np.random.normal(scale=np.sqrt(th["sigma2"]) / 4.0, size=[D, H]))
+                th["W"] = self._noisy_init(y_mean, float(np.sqrt(th["sigma2"])) / 4.0).cpu().numpy()
         else:
             th["W"] = W_init
         return th

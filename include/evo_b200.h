@@ -330,6 +330,12 @@ int evo_comm_destroy(void *comm);
 int evo_generate_data(const double *Wt, const double *pies, double pi, const double *mus, const double *Psi,
                       int psi_diag, double sigma, int64_t N, int64_t n_offset, int D, int H, uint64_t seed,
                       float *Y, uint32_t *S_out, float *Z_out, float *Ymean, int32_t *overflow, void *stream);
+/* standard_init on the device (evo/models/_models.py:206-283, sssc.py:104-197): column moments of the (masked) data,
+ * out[3 D] += {sum m y, sum m y^2, sum m} (accumulated: the caller zeroes and all-reduces), and the initial dictionary
+ * out[i][j] = row_mean[i] + scale N(0,1) ([rows][cols] f64; row_mean may be NULL) from a Philox stream keyed by
+ * (seed, element) -- every rank fills the same values from the same seed, no broadcast. */
+int evo_column_moments(const float *Y, const uint8_t *mask, int64_t N, int D, double *out, void *stream);
+int evo_normal_fill(double *out, int64_t rows, int cols, const double *row_mean, double scale, uint64_t seed, void *stream);
 /* FMA throughput of the SIMT pipes in TFLOP/s (dtype 32 or 64; 8 independent chains per thread, best of 3,
  * synchronous, default stream): the measured denominator of the ES3C roofline (bench.py). */
 int evo_fma_peak(int dtype, int iters, double *tflops_out);

@@ -114,3 +114,42 @@ def test_device_generator_has_the_reference_moments():
     th["sigma2"] = np.float64(Z["es3c_sigma2"])
     gen = SSSC(D, H, 4).generate_data(th, n, seed=4)
     _check_moments("es3c_", gen, n, True)
+
+
+@pytest.mark.gpu
+def test_standard_init_statistics_and_noise_on_device():
+    """standard_init (_models.py:206-283, sssc.py:104-197): data mean / spread from `evo_column_moments`, dictionary
+    = data mean + N(0, (sigma/4)^2) from `evo_normal_fill` -- against the reference's formulas in NumPy."""
+    from evo_b200.bsc import BSC
+    from evo_b200.sssc import SSSC
+
+    rng = np.random.RandomState(4)
+    N, D, H = 3000, 20, 50
+    Y = (rng.normal(size=(N, D)) * rng.uniform(0.5, 3, size=D) + rng.normal(size=D) * 4).astype(np.float32).astype(np.float64)
+    X = rng.random_sample((N, D)) > 0.3
+    # BSC, complete data (_models.py:225-240): mean over n, sigma = sqrt(mean_d var_d)
+    np.random.seed(3)
+    th = BSC(D, H, 8).standard_init({"y": Y, "x_infr": None})
+    mean = Y.mean(0)
+    sig = np.sqrt(Y.var(0).mean())
+    assert abs(th["sigma"] - sig) < 1e-9 * sig and th["pi"] == 1.0 / H
+    noise = th["W"] - mean[:, None]
+    assert abs(noise.mean()) < 5 * (sig / 4) / np.sqrt(D * H) and abs(noise.std() - sig / 4) < 0.1 * sig / 4
+    np.random.seed(3)
+    th2 = BSC(D, H, 8).standard_init({"y": Y, "x_infr": None})
+    assert np.array_equal(th["W"], th2["W"]), "np.random.seed makes the device initialisation reproducible"
+    # BSC, incomplete data (_models.py:241-262): masked mean, sigma over the observed entries
+    Yn = np.where(X, Y, np.nan)
+    th = BSC(D, H, 8).standard_init({"y": Yn, "x_infr": X})
+    mean = np.nanmean(Yn, 0)
+    sig = np.sqrt(np.nansum((Yn - mean) ** 2) / X.sum())
+    assert abs(th["sigma"] - sig) < 1e-9 * sig
+    assert np.abs((th["W"] - mean[:, None]).mean(1)).max() < 6 * (sig / 4) / np.sqrt(H)
+    # ES3C (sssc.py:143-181): complete -> mean diagonal of the unbiased covariance + 1e-3
+    th = SSSC(D, H, 8).standard_init({"y": Y, "x_infr": None})
+    want = np.diag(np.cov(Y.T)).mean() + 0.001
+    assert abs(float(th["sigma2"]) - want) < 1e-9 * want
+    th = SSSC(D, H, 8).standard_init({"y": Yn, "x_infr": X})
+    ym = np.nansum(Yn, 0) / N
+    want = np.nansum((Yn - ym) ** 2) / X.sum() + 0.001
+    assert abs(float(th["sigma2"]) - want) < 1e-9 * want
