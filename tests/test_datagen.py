@@ -137,7 +137,8 @@ def test_standard_init_statistics_and_noise_on_device():
     assert abs(noise.mean()) < 5 * (sig / 4) / np.sqrt(D * H) and abs(noise.std() - sig / 4) < 0.1 * sig / 4
     np.random.seed(3)
     th2 = BSC(D, H, 8).standard_init({"y": Y, "x_infr": None})
-    assert np.array_equal(th["W"], th2["W"]), "np.random.seed makes the device initialisation reproducible"
+    # same Philox seed from np.random -> same noise; the data mean is summed with unordered f64 atomics (last bits)
+    assert np.abs(th["W"] - th2["W"]).max() < 1e-12 * np.abs(th["W"]).max(), "np.random.seed makes the initialisation reproducible"
     # BSC, incomplete data (_models.py:241-262): masked mean, sigma over the observed entries
     Yn = np.where(X, Y, np.nan)
     th = BSC(D, H, 8).standard_init({"y": Yn, "x_infr": X})
