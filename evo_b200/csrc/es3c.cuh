@@ -61,7 +61,7 @@ struct Es3cEval {
     if (masked == 1) return align8((size_t)D * sizeof(double)) + align8((size_t)D);
     return align8((size_t)H * sizeof(double)) + (masked == 2 ? align8(48 + (size_t)2 * D) : 0);
   }
-  __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(8 + (size_t)4 * max_batch) : 0; }
+  __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(16 + (size_t)6 * max_batch) : 0; }
   static constexpr bool kList = false;
   __host__ __device__ size_t smem_bytes(int T, bool = false) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM + list_bytes(); }
   // measured (cfg3/cfg4, 64 states + 64 children): complete data is fastest with 4 warps and more resident
@@ -158,19 +158,30 @@ struct Es3cEval {
   __device__ __forceinline__ double gather(int a, const uint16_t *idx, double *A1, double *A2, int ld, double &ynorm) const {
     const int lane = threadIdx.x & 31;
     double bi = 0.0;
-    if (masked != 1) {
+    if (masked == 2) {
+      // (W'W)_AA minus the missing observables' share, the warp striding over the missing list for every pair
+      const int nm = *nmiss_ptr;
+      for (int i = 0; i < a; ++i) {
+        const double *wa = Wt + (int64_t)idx[i] * D;
+        for (int j = 0; j <= i; ++j) {
+          const double *wb = Wt + (int64_t)idx[j] * D;
+          double c = 0.0;
+          for (int q = lane; q < nm; q += 32) { const int d = miss[q]; c += __ldg(wa + d) * __ldg(wb + d); }
+          c = warp_sum(c);
+          if (lane == 0) {
+            const double v = __ldg(G + (int64_t)idx[i] * H + idx[j]) - c;
+            A1[i * ld + j] = v;
+            A1[j * ld + i] = v;
+          }
+        }
+      }
+      if (lane < a) bi = vec[idx[lane]];
+      ynorm = yn2;
+    } else if (masked == 0) {
       if (lane < a) {
         int h = idx[lane];
         const double *Gr = G + (int64_t)h * H;
-        if (masked == 2) {
-          for (int l = 0; l <= lane; ++l) {
-            const double v = __ldg(Gr + idx[l]) - miss_corr(h, idx[l]);
-            A1[lane * ld + l] = v;
-            A1[l * ld + lane] = v;
-          }
-        } else {
-          for (int l = 0; l < a; ++l) A1[lane * ld + l] = __ldg(Gr + idx[l]);
-        }
+        for (int l = 0; l < a; ++l) A1[lane * ld + l] = __ldg(Gr + idx[l]);
         bi = vec[h];
       }
       ynorm = yn2;
@@ -446,6 +457,114 @@ struct Es3cEval {
     return -0.5 * (logdet + quad) + prior;
   }
 
+  // ---- states with at most SMALL_A active latents: one THREAD per state, everything in registers -------------------
+  // Same quantities as build() / lu_solve() -- N = I + s2i G_AA Psi_A, v = s2i (b - G mu), |r|^2, w = Psi_A' v,
+  // lpj = -1/2 (log|det N| + s2i |r|^2 - w' N^-1 v) + sum pil -- on a fixed SMALL_A x SMALL_A system padded with the
+  // identity (fully unrolled LU with partial pivoting, no divergence between states of different size).  Most states
+  // of a sparse model are this small, and a warp (or 8 lanes) per such state is mostly idle.
+  static constexpr int SMALL_A = 2;
+  __device__ __forceinline__ double small_lpj(const uint32_t *st) const {
+    constexpr int MA = SMALL_A;
+    int hs[MA];
+    int a = 0;
+#pragma unroll
+    for (int i = 0; i < MA; ++i) hs[i] = 0;
+    for (int w = 0; w < Hw; ++w) {
+      uint32_t m = st[w];
+      while (m) {
+        const int h = (w << 5) + __ffs(m) - 1;
+        m &= m - 1;
+#pragma unroll
+        for (int i = 0; i < MA; ++i) if (i == a) hs[i] = h;
+        ++a;
+      }
+    }
+    if (a == 0) return -0.5 * s2i * yn2;
+    double g[MA][MA], ps[MA][MA], mu[MA], b[MA];
+    double prior = 0.0;
+#pragma unroll
+    for (int i = 0; i < MA; ++i) {
+      const bool oi = i < a;
+      mu[i] = oi ? __ldg(mus + hs[i]) : 0.0;
+      b[i] = oi ? vec[hs[i]] : 0.0;
+      prior += oi ? __ldg(pil_bar + hs[i]) : 0.0;
+#pragma unroll
+      for (int j = 0; j < MA; ++j) {
+        const bool on = oi && j < a;
+        ps[i][j] = on ? __ldg(Psi + (int64_t)hs[i] * H + hs[j]) : 0.0;
+        if (j <= i) {
+          double v = on ? __ldg(G + (int64_t)hs[i] * H + hs[j]) : 0.0;
+          if (on && masked == 2) v -= miss_corr(hs[i], hs[j]);
+          g[i][j] = v;
+          g[j][i] = v;
+        }
+      }
+    }
+    double t[MA], v[MA], w[MA], n[MA][MA];
+    double rn2 = yn2;
+#pragma unroll
+    for (int i = 0; i < MA; ++i) {
+      double ti = 0.0;
+#pragma unroll
+      for (int l = 0; l < MA; ++l) ti += g[i][l] * mu[l];
+      t[i] = ti;
+      v[i] = s2i * (b[i] - ti);
+      rn2 += mu[i] * (ti - 2.0 * b[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < MA; ++i) {
+      double wi = 0.0;
+#pragma unroll
+      for (int l = 0; l < MA; ++l) wi += ps[l][i] * v[l];  // (Psi_A' v)_i: Psi need not be symmetric
+      w[i] = wi;
+#pragma unroll
+      for (int j = 0; j < MA; ++j) {
+        double acc = 0.0;
+#pragma unroll
+        for (int l = 0; l < MA; ++l) acc += g[i][l] * ps[l][j];
+        n[i][j] = (i == j ? 1.0 : 0.0) + s2i * acc;
+      }
+    }
+    // LU with partial pivoting, right-hand side v (in place); padded rows are unit rows and never chosen over a
+    // larger pivot of the live block except by exact ties, which is harmless
+    double logdet = 0.0;
+#pragma unroll
+    for (int k = 0; k < MA; ++k) {
+      int p = k;
+      double best = fabs(n[k][k]);
+#pragma unroll
+      for (int i = k + 1; i < MA; ++i) { const double m2 = fabs(n[i][k]); if (m2 > best) { best = m2; p = i; } }
+#pragma unroll
+      for (int i = k + 1; i < MA; ++i) {
+        if (i == p) {
+#pragma unroll
+          for (int c = 0; c < MA; ++c) { const double x = n[k][c]; n[k][c] = n[i][c]; n[i][c] = x; }
+          const double x = v[k]; v[k] = v[i]; v[i] = x;
+        }
+      }
+      const double piv = n[k][k];
+      logdet += log(fabs(piv));
+#pragma unroll
+      for (int i = k + 1; i < MA; ++i) {
+        const double f = n[i][k] / piv;
+#pragma unroll
+        for (int c = k + 1; c < MA; ++c) n[i][c] -= f * n[k][c];
+        v[i] -= f * v[k];
+      }
+    }
+#pragma unroll
+    for (int k = MA - 1; k >= 0; --k) {
+      double x = v[k];
+#pragma unroll
+      for (int c = k + 1; c < MA; ++c) x -= n[k][c] * v[c];
+      v[k] = x / n[k][k];
+    }
+    double wx = 0.0;
+#pragma unroll
+    for (int i = 0; i < MA; ++i) wx += w[i] * v[i];
+    return -0.5 * (logdet + s2i * rn2 - wx) + prior;
+  }
+
   template <int T, bool LIST = false>
   __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) {
     if (masked == 1) yn2 = masked_yn2();
@@ -454,20 +573,27 @@ struct Es3cEval {
     // state goes to the warp-per-state solver)
     const bool listed = max_batch > 0 && cnt <= max_batch;
     int *cn = reinterpret_cast<int *>(lsm);
-    uint16_t *small = reinterpret_cast<uint16_t *>(lsm + 8), *big = small + max_batch;
-    int ns = 0, nb = cnt;
+    uint16_t *small = reinterpret_cast<uint16_t *>(lsm + 16), *big = small + max_batch, *tiny = big + max_batch;
+    int ns = 0, nb = cnt, nt = 0;
     if (listed) {
+      const int tiny_max = masked == 1 ? -1 : SMALL_A;  // the register path reads the Gram tables
       gsync<T>();
-      if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; }
+      if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; cn[2] = 0; }
       gsync<T>();
 #pragma unroll 1
       for (int i = threadIdx.x; i < cnt; i += T) {
         const int a = popc_state(st + (size_t)i * ld, Hw);
-        if (a <= G8) small[atomicAdd(&cn[0], 1)] = (uint16_t)i;
+        if (a <= tiny_max) tiny[atomicAdd(&cn[2], 1)] = (uint16_t)i;
+        else if (a <= G8) small[atomicAdd(&cn[0], 1)] = (uint16_t)i;
         else big[atomicAdd(&cn[1], 1)] = (uint16_t)i;
       }
       gsync<T>();
-      ns = cn[0], nb = cn[1];
+      ns = cn[0], nb = cn[1], nt = cn[2];
+    }
+#pragma unroll 1
+    for (int j = threadIdx.x; j < nt; j += T) {
+      const int i = tiny[j];
+      out[i] = lpj_sanitise(small_lpj(st + (size_t)i * ld), flags);
     }
 #pragma unroll 1
     for (int q = warp; q * 4 < ns; q += T / 32) {
