@@ -436,6 +436,16 @@ def roofline_of(job, win, peak, peak_src, fma=None):
     roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
             "traffic": (NCU_TRAFFIC.get("%s:%d" % (job.name, job.N), {}) or {}).get(dom), "peak_source": peak_src,
             "launch_ms": kern[dom][1], "algorithmic_bytes_per_launch": alg[dom]}
+    wi = ((NCU_TRAFFIC.get("%s:%d" % (job.name, job.N), {}) or {}).get("warp_inst") or {}).get(dom)
+    if wi:
+        # the kernel is bound by instruction issue, not by HBM: warp instructions per launch (ncu, same command) against
+        # 4 issue slots x SMs x clock -- the time the launch would take at 100 % issue-slot utilisation
+        import torch
+        sms = torch.cuda.get_device_properties(job.device).multi_processor_count
+        ceil_ms = wi / (4.0 * sms * 1.965e9) * 1e3
+        roof["issue"] = {"warp_instructions_per_launch": wi, "issue_slots_per_s": 4.0 * sms * 1.965e9,
+                         "launch_ms_at_full_issue": ceil_ms, "frac_of_issue_ceiling": ceil_ms / kern[dom][1],
+                         "hbm_frac_at_full_issue": alg[dom] / (ceil_ms * 1e-3) / 1e9 / peak}
     if w["model"] == "es3c" and fma:
         a1, a2, a3 = job.mean_active()
         d_obs = w["D"] * (1.0 - w.get("missing", 0.0))
