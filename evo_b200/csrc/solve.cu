@@ -10,12 +10,15 @@
 // ACROSS blocks: stable for (near-)SPD matrices, whose Schur complements stay (near-)SPD.  A pivot below
 // 1e-13 x the largest diagonal entry raises `info` (block index + 1): the caller then takes the minimum-norm /
 // pseudo-inverse route the reference takes for singular statistics (bsc.py:236-250, sssc.py:695-709).
+#include <cooperative_groups.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace evo {
 
 constexpr int SB = 32;           // elimination block
-constexpr int GT = 64, GK = 16;  // GEMM tile
+constexpr int GT = 64, GK = 32;  // GEMM tile (k chunk = the elimination block: one load phase per panel / update tile)
 
 struct GemmArgs {
   const double *A; int64_t ar, ac;  // A(i,k) = A[i*ar + k*ac]
@@ -25,12 +28,11 @@ struct GemmArgs {
   double alpha, beta;               // C = beta C + alpha A B   (beta == 0: C is not read)
 };
 
-// 64 x 64 tile per CTA, 256 threads x (4 x 4), k in steps of 16.  A tile whose C aliases A (N <= 64) or B
-// (M <= 64) is safe: every CTA finishes reading its operands before it writes.
-__global__ void __launch_bounds__(256) gemm_f64_kernel(GemmArgs g) {
-  __shared__ double sa[GK][GT + 1], sb[GK][GT + 1];
+// 64 x 64 tile of C per call, 256 threads x (4 x 4), k in steps of 16.  A tile whose C aliases A (N <= 64) or B
+// (M <= 64) is safe: every operand read of the tile is done before it is written.
+__device__ __forceinline__ void gemm_tile(const GemmArgs &g, int ti, int tj, double (*sa)[GT + 1], double (*sb)[GT + 1]) {
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  const int i0 = blockIdx.y * GT, j0 = blockIdx.x * GT;
+  const int i0 = ti * GT, j0 = tj * GT;
   double acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -40,12 +42,12 @@ __global__ void __launch_bounds__(256) gemm_f64_kernel(GemmArgs g) {
     __syncthreads();
     for (int t = threadIdx.x; t < GT * GK; t += 256) {
       int r, k;
-      if (g.ac == 1) { k = t & (GK - 1); r = t >> 4; } else { r = t & (GT - 1); k = t >> 6; }
+      if (g.ac == 1) { k = t % GK; r = t / GK; } else { r = t % GT; k = t / GT; }
       sa[k][r] = (i0 + r < g.M && k0 + k < g.K) ? g.A[(int64_t)(i0 + r) * g.ar + (int64_t)(k0 + k) * g.ac] : 0.0;
     }
     for (int t = threadIdx.x; t < GT * GK; t += 256) {
       int c, k;
-      if (g.bc == 1) { c = t & (GT - 1); k = t >> 6; } else { k = t & (GK - 1); c = t >> 4; }
+      if (g.bc == 1) { c = t % GT; k = t / GT; } else { k = t % GK; c = t / GK; }
       sb[k][c] = (j0 + c < g.N && k0 + k < g.K) ? g.B[(int64_t)(k0 + k) * g.br + (int64_t)(j0 + c) * g.bc] : 0.0;
     }
     __syncthreads();
@@ -62,7 +64,7 @@ __global__ void __launch_bounds__(256) gemm_f64_kernel(GemmArgs g) {
         for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
     }
   }
-  __syncthreads();  // in-place products: all operand reads of this CTA are done
+  __syncthreads();  // in-place products: all operand reads of this tile are done
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -73,6 +75,10 @@ __global__ void __launch_bounds__(256) gemm_f64_kernel(GemmArgs g) {
         *p = (g.beta == 0.0 ? 0.0 : g.beta * *p) + g.alpha * acc[i][j];
       }
     }
+}
+__global__ void __launch_bounds__(256) gemm_f64_kernel(GemmArgs g) {
+  __shared__ double sa[GK][GT + 1], sb[GK][GT + 1];
+  gemm_tile(g, blockIdx.y, blockIdx.x, sa, sb);
 }
 
 static int gemm(const GemmArgs &g, cudaStream_t st) {
@@ -87,18 +93,16 @@ static int gemm(const GemmArgs &g, cudaStream_t st) {
 // pivoting, one warp, lane = row, the row of [A | R] in REGISTERS (both loops fully unrolled).  Rows are not swapped:
 // the lane chosen as pivot for column k ends up holding row k of the inverse.  inv (32 x 32, row-major) <- block^-1;
 // *info = blk + 1 (first failing block) when a pivot is <= tol * scale[0] in magnitude or not finite.
-__global__ void __launch_bounds__(32) diag_inv_kernel(const double *__restrict__ Mx, int64_t ld, int r0, double *__restrict__ inv,
-                                                      const double *__restrict__ scale, double tol, int blk, int *info) {
-  __shared__ double prow[2 * SB];
-  const int lane = threadIdx.x;
+__device__ __forceinline__ void diag_inv_warp(const double *__restrict__ Mx, int64_t ld, int r0, double *inv, double *prow,
+                                              double thr, bool &bad) {
+  const int lane = threadIdx.x & 31;
   double a[SB], r[SB];
 #pragma unroll
   for (int c = 0; c < SB; ++c) {
     a[c] = Mx[(int64_t)(r0 + lane) * ld + r0 + c];
     r[c] = (lane == c) ? 1.0 : 0.0;
   }
-  const double thr = tol * fabs(scale[0]);
-  bool bad = false, used = false;
+  bool used = false;
   int mycol = 0;
   double mypiv = 1.0;
 #pragma unroll
@@ -131,7 +135,88 @@ __global__ void __launch_bounds__(32) diag_inv_kernel(const double *__restrict__
   const double d = 1.0 / mypiv;
 #pragma unroll
   for (int c = 0; c < SB; ++c) inv[mycol * SB + c] = r[c] * d;
-  if (bad && lane == 0) atomicCAS(info, 0, blk + 1);
+}
+__global__ void __launch_bounds__(32) diag_inv_kernel(const double *__restrict__ Mx, int64_t ld, int r0, double *__restrict__ inv,
+                                                      const double *__restrict__ scale, double tol, int blk, int *info) {
+  __shared__ double prow[2 * SB];
+  bool bad = false;
+  diag_inv_warp(Mx, ld, r0, inv, prow, tol * fabs(scale[0]), bad);
+  if (bad && threadIdx.x == 0) atomicCAS(info, 0, blk + 1);
+}
+
+// The whole elimination as ONE persistent cooperative kernel: grid barriers (~ 2 us) instead of ~ 5 dependent
+// launches per block step.  Every CTA inverts the diagonal block itself (redundantly, into shared memory), so the
+// panel scaling needs no barrier after the inversion; CTA 0 publishes the inverse for the back substitution.
+__global__ void __launch_bounds__(256, 1) block_solve_kernel(double *Mx, int Hp, int Wd, double *invs, const double *scale,
+                                                            double tol, int *info) {
+  __shared__ double sa[GK][GT + 1], sb[GK][GT + 1];
+  __shared__ double prow[2 * SB];
+  __shared__ double sinv[SB * SB];
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  const int nb = Hp / SB, nrhs = Wd - Hp, G = gridDim.x, me = blockIdx.x;
+  const int64_t ld = Wd;
+  const double thr = tol * fabs(scale[0]);
+  for (int k = 0; k < nb; ++k) {
+    const int r0 = k * SB;
+    __syncthreads();
+    if (k == 0) {  // first block: everybody inverts it (nothing to overlap with)
+      if (threadIdx.x < 32) {
+        bool bad = false;
+        diag_inv_warp(Mx, ld, r0, sinv, prow, thr, bad);
+        if (bad && me == 0 && threadIdx.x == 0) atomicCAS(info, 0, k + 1);
+      }
+      __syncthreads();
+      if (me == 0)
+        for (int t = threadIdx.x; t < SB * SB; t += 256) invs[t] = sinv[t];
+    } else {  // look-ahead: CTA 0 inverted this block during the previous trailing update and published it
+      for (int t = threadIdx.x; t < SB * SB; t += 256) sinv[t] = invs[(size_t)k * SB * SB + t];
+      __syncthreads();
+    }
+    const int below = Hp - r0 - SB;
+    if (below > 0) {
+      // panel: L_ik = M_ik inv (in place); each CTA scales the row tiles it will also use... (any split works)
+      GemmArgs p{Mx + (int64_t)(r0 + SB) * ld + r0, ld, 1, sinv, SB, 1, Mx + (int64_t)(r0 + SB) * ld + r0, ld, below, SB, SB, 1.0, 0.0};
+      const int pt = (below + GT - 1) / GT;
+      for (int t = me; t < pt; t += G) gemm_tile(p, t, 0, sa, sb);
+    }
+    grid.sync();
+    if (below > 0) {
+      GemmArgs u{Mx + (int64_t)(r0 + SB) * ld + r0, ld, 1, Mx + (int64_t)r0 * ld + r0 + SB, ld, 1,
+                 Mx + (int64_t)(r0 + SB) * ld + r0 + SB, ld, below, Wd - r0 - SB, SB, -1.0, 1.0};
+      const int ti = (u.M + GT - 1) / GT, tj = (u.N + GT - 1) / GT;
+      if (me == 0) {
+        // the tile holding the next diagonal block first, then its inverse -- while the other CTAs finish the update
+        gemm_tile(u, 0, 0, sa, sb);
+        __syncthreads();
+        if (threadIdx.x < 32) {
+          bool bad = false;
+          diag_inv_warp(Mx, ld, r0 + SB, invs + (size_t)(k + 1) * SB * SB, prow, thr, bad);
+          if (bad && threadIdx.x == 0) atomicCAS(info, 0, k + 2);
+        }
+        __threadfence();
+        for (int t = G; t < ti * tj; t += G) gemm_tile(u, t / tj, t % tj, sa, sb);
+      } else {
+        for (int t = me; t < ti * tj; t += G) gemm_tile(u, t / tj, t % tj, sa, sb);
+      }
+      grid.sync();
+    }
+  }
+  __threadfence();
+  grid.sync();  // the last block's inverse (published by CTA 0 without a barrier behind it) is visible to everyone
+  for (int k = nb - 1; k >= 0; --k) {
+    const int r0 = k * SB;
+    double *Rk = Mx + (int64_t)r0 * ld + Hp;
+    GemmArgs x{invs + (size_t)k * SB * SB, SB, 1, Rk, ld, 1, Rk, ld, SB, nrhs, SB, 1.0, 0.0};
+    const int xt = (nrhs + GT - 1) / GT;
+    for (int t = me; t < xt; t += G) gemm_tile(x, 0, t, sa, sb);
+    grid.sync();
+    if (r0 > 0) {
+      GemmArgs u{Mx + r0, ld, 1, Rk, ld, 1, Mx + Hp, ld, r0, nrhs, SB, -1.0, 1.0};
+      const int ti = (u.M + GT - 1) / GT, tj = (u.N + GT - 1) / GT;
+      for (int t = me; t < ti * tj; t += G) gemm_tile(u, t / tj, t % tj, sa, sb);
+      grid.sync();
+    }
+  }
 }
 
 // Block Gaussian elimination of [A | B] in place (Mx: Hp x Wd row-major, Hp a multiple of 32, A = the first Hp
@@ -139,6 +224,22 @@ __global__ void __launch_bounds__(32) diag_inv_kernel(const double *__restrict__
 static int block_solve(double *Mx, int Hp, int Wd, double *invs, const double *scale, int *info, cudaStream_t st) {
   const int nb = Hp / SB;
   const int64_t ld = Wd;
+  if (!getenv("EVO_SOLVE_MULTI")) {  // one persistent cooperative kernel when the device supports it
+    int dev = 0, coop = 0, per_sm = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess &&
+        coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, block_solve_kernel, 256, 0) == cudaSuccess && per_sm >= 1) {
+      const int tiles = ((Hp + GT - 1) / GT) * ((Wd + GT - 1) / GT);
+      int grid = sm_count() * per_sm;
+      if (grid > tiles) grid = tiles;
+      if (grid < 1) grid = 1;
+      double tol = 1e-13;
+      void *args[] = {&Mx, &Hp, &Wd, &invs, (void *)&scale, &tol, &info};
+      EVO_CUDA(cudaLaunchCooperativeKernel((const void *)block_solve_kernel, dim3(grid), dim3(256), args, 0, st));
+      count_launch();
+      return EVO_OK;
+    }
+    cudaGetLastError();
+  }
   for (int k = 0; k < nb; ++k) {
     const int r0 = k * SB;
     double *inv = invs + (size_t)k * SB * SB;
