@@ -145,3 +145,28 @@ def test_es3c_update_matches_numpy(D, H, incomplete, learn):
         assert abs(sc[2] - s2) <= 1e-9 * abs(s2)
     else:
         assert sc[2] == s2old
+
+
+def test_es3c_singular_moments_take_the_reference_fallback():
+    """A latent that is active in no state leaves a zero row / column in sum <sz sz'>: `evo_es3c_update` flags it and
+    SSSC takes the reference's route (sssc.py:695-709: pseudo-inverse plus rank-one noise, drawn on rank 0 and
+    broadcast) on the device -- finite parameters, the dead latent's column of W stays at the noise level."""
+    from evo_b200.sssc import SSSC
+    from evo_b200.variational import init_states
+
+    rng = np.random.RandomState(0)
+    D, H, N, S = 8, 6, 200, 4
+    Y = rng.normal(size=(N, D)).astype(np.float32).astype(np.float64)
+    m = SSSC(D, H, S)
+    cont = init_states(N, S, H, "fit", "randflip", 2, 1, 0)  # no generations: the K sets stay as given
+    ss = np.zeros((N, S, H), dtype=bool)
+    for k in range(S):
+        ss[:, k, k] = True  # states use latents 0..3 only; 4 and 5 never appear
+    ss[:, 0, 1] = True
+    cont["ss"] = ss
+    th = {"W": rng.normal(size=(D, H)), "pies": np.full(H, 0.2), "mus": np.ones(H), "Psi": np.eye(H), "sigma2": np.float64(1.0)}
+    np.random.seed(0)
+    F, _, _, th = m.step(th, cont, {"y": Y, "x_infr": None, "x": np.zeros((N, D), bool)}, do_reconstruction=True)
+    assert m.last_counts.get("solve_fallback", 0) == 1
+    assert np.isfinite(F) and all(np.isfinite(np.asarray(th[k])).all() for k in ("W", "pies", "mus", "Psi", "sigma2"))
+    assert np.abs(th["pies"][4:] - 5e-5).max() < 1e-12  # clipped at eps
