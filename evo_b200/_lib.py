@@ -111,6 +111,7 @@ SIGNATURES = {
     "evo_bsc_suffstats_tc": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp]),
     "evo_bsc_solve_workspace_bytes": (_i64, [_i, _i]),
     "evo_bsc_solve": (_i, [_vp, _d, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp, _vp]),
+    "evo_bsc_solve_static": (_i, [_vp, _d, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp]),
     "evo_es3c_update_workspace_bytes": (_i64, [_i, _i]),
     "evo_es3c_update": (_i, [C.POINTER(Es3cUpdateArgs), _vp]),
     "evo_es3c_set_scratch": (_i, [_vp, _i]),

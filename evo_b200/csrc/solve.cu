@@ -564,3 +564,42 @@ extern "C" int evo_es3c_update(const evo_es3c_update_args *x, void *stream) {
   EVO_LAUNCH_CHECK("es3c_scal");
   return EVO_OK;
 }
+
+// ---- evo_bsc_solve_static: the BSC solve for callers that may not allocate -----------------------------------------------------
+// No counterpart in the reference; added (CUDA-graph capture, serving loops and
+// harnesses that forbid cudaMalloc).  Same computation as evo_bsc_solve, with the elimination workspace in a file-scope
+// device array instead of a caller buffer.  Every GPU that loads the library holds the array until the process exits.
+// All calls on a device SHARE it: calls that overlap on the GPU (two streams) race; serialise them.  It keeps the last
+// call's contents; the solve clears its 64-byte header (scale, info, finite) itself and overwrites [A | B] and the
+// block inverses in full before reading them, so nothing else needs to start at zero.
+static __device__ __align__(256) unsigned char g_solve_static[EVO_BSC_SOLVE_STATIC_BYTES];
+
+namespace {
+constexpr int kMaxDev = 64;
+void *g_static_ptr[kMaxDev];  // device address of g_solve_static, per device (host code must not pass the symbol itself)
+bool g_static_set[kMaxDev];
+}  // namespace
+
+extern "C" int evo_bsc_solve_static(const double *stats, double N_total, int D, int H, int learn_W, int background,
+                                    double n_obs_total, double sigma_old, double *W, double *pies, double *scal, void *stream) {
+  EVO_REQUIRE(D > 0 && H > 0, "bad sizes");
+  const int64_t need = evo_bsc_solve_workspace_bytes(D, H);
+  if (need > (int64_t)EVO_BSC_SOLVE_STATIC_BYTES) {
+    set_error("evo_bsc_solve_static: D=%d H=%d needs %lld workspace bytes, the static scratch holds %lld "
+              "(EVO_BSC_SOLVE_STATIC_BYTES); use evo_bsc_solve with a caller workspace",
+              D, H, (long long)need, (long long)EVO_BSC_SOLVE_STATIC_BYTES);
+    return EVO_ERR_ARG;
+  }
+  int dev = -1;
+  EVO_CUDA(cudaGetDevice(&dev));
+  EVO_REQUIRE(dev >= 0 && dev < kMaxDev, "device ordinal out of range");
+  if (!g_static_set[dev]) {  // once per device, with that device current
+    void *p = nullptr;
+    EVO_CUDA(cudaGetSymbolAddress(&p, g_solve_static));
+    EVO_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    g_static_ptr[dev] = p;
+    g_static_set[dev] = true;
+  }
+  return evo_bsc_solve(stats, N_total, D, H, learn_W, background, n_obs_total, sigma_old, W, pies, scal, g_static_ptr[dev],
+                       stream);
+}

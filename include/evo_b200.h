@@ -235,6 +235,16 @@ int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double 
 int64_t evo_bsc_solve_workspace_bytes(int D, int H);
 int evo_bsc_solve(const double *stats, double N_total, int D, int H, int learn_W, int background, double n_obs_total,
                   double sigma_old, double *W, double *pies, double *scal, void *workspace, void *stream);
+/* evo_bsc_solve_static -- NO counterpart in the reference: added for callers
+ * that cannot allocate device memory (CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same arguments, outputs and error behaviour as evo_bsc_solve without the workspace: the elimination scratch is a
+ * file-scope device array of EVO_BSC_SOLVE_STATIC_BYTES that every GPU loading the library holds until exit.  Sizes
+ * with evo_bsc_solve_workspace_bytes(D, H) > EVO_BSC_SOLVE_STATIC_BYTES (e.g. beyond D = H = 512) are rejected with
+ * EVO_ERR_ARG.  The call performs no cudaMalloc / cudaFree.  All calls on a device share the array: calls that overlap
+ * on the GPU race -- keep them on one stream or order them with events. */
+#define EVO_BSC_SOLVE_STATIC_BYTES (6 * 1024 * 1024)
+int evo_bsc_solve_static(const double *stats, double N_total, int D, int H, int learn_W, int background,
+                         double n_obs_total, double sigma_old, double *W, double *pies, double *scal, void *stream);
 /* evo_es3c_update -- SSSC.EM_step parameter updates (evo/models/sssc.py:688-770) from the reduced buffer of
  * evo_es3c_suffstats.  W / pies / mus / Psi hold the current parameters and are overwritten where learned:
  *   W = Wp inv(sum_szsz) (:692-694), pies = clip(sum_s / N, eps, 1 - eps) (:712-721), mus = sum_sz / (sum_s + eps_mus)
