@@ -189,6 +189,7 @@ def algorithmic_bytes(w, N, U_mean):
         # (d): read K^n + lpj + y_n, one pass over the outputs
         "evo_bsc_suffstats": N * (K * (4 * Hw + 4) + 4 * D) + 8 * (H * D + H * H),
         "evo_bsc_suffstats_tc": N * (K * (4 * Hw + 4) + 4 * D) + 8 * (H * D + H * H),
+        "evo_bsc_suffstats_tc_finish": N * (K * (4 * Hw + 4) + 4 * D) + 8 * (H * D + H * H),
         # transposed fp16 hi + lo planes of Y: read f32, write 2 x fp16
         "evo_bsc_wp_tc_set_data": N * D * 8,
         # ES3C (d): as above + mask bits + y_rec write, one pass over the four H x H + H x D outputs

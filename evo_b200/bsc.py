@@ -121,14 +121,48 @@ class BSC(Model):
         return None
 
     # ---- E-step (_models.py:454-565) -----------------------------------------------------------------
-    def _estep_enqueue(self, model_params, my_suff_stat, my_data):
+    def _estep_enqueue(self, model_params, my_suff_stat, my_data, fused=None):
         dd = self.device_data(my_data)
         self.E_step_precompute(model_params, my_suff_stat, my_data)
         self._tables(model_params, dd)
         acc = torch.zeros(ACC_LEN, dtype=torch.float64, device=self.device)
-        self._estep_launch(my_suff_stat, dd, acc, lambda a: self._fill_eval(a, model_params, dd))
+
+        def fill(a):
+            self._fill_eval(a, model_params, dd)
+            if fused is not None:  # statistics in the tail of the E-step kernel (evo_estep_args.fs_*)
+                a.fs_stats, a.fs_wp_workspace, a.fs_rest = fused["stats"].data_ptr(), fused["ws"].data_ptr(), fused["rest"].data_ptr()
+
+        self._estep_launch(my_suff_stat, dd, acc, fill)
         dd.cache["acc"] = acc
         return dd, acc
+
+    # fuse the statistics pass into the E-step kernel when Wp goes through the tensor-core GEMM and the data are complete
+    fuse_stats = True
+
+    def _fused_begin(self, dd):
+        """Statistics buffer, Wp workspace (Y planes valid, <s> planes cleared) and the rest list for a fused E-step."""
+        D, H = self.D, self.H
+        c = dd.cache
+        stats = torch.zeros(H * D + H * H + H + 1 + ACC_LEN, dtype=torch.float64, device=self.device)
+        if "wp_tc_ws" not in c:
+            nb = int(self.lib.evo_bsc_wp_tc_workspace_bytes(dd.N, D, H))
+            c["wp_tc_ws"] = torch.empty(nb, dtype=torch.uint8, device=self.device)
+            c.pop("wp_tc_valid", None)
+        if not c.get("wp_tc_valid"):
+            self._call("evo_bsc_wp_tc_set_data", _lib.ptr(dd.Y), dd.N, D, H, _lib.ptr(c["wp_tc_ws"]))
+            c["wp_tc_valid"] = True
+        rest = c.get("fs_rest")
+        if rest is None or rest.numel() < dd.N + 1:
+            rest = c["fs_rest"] = torch.empty(dd.N + 1, dtype=torch.int32, device=self.device)
+        self._call("evo_bsc_wp_tc_begin", dd.N, D, H, _lib.ptr(c["wp_tc_ws"]))
+        return {"stats": stats, "ws": c["wp_tc_ws"], "rest": rest}
+
+    def _fused_finish(self, model_params, my_suff_stat, dd, fused):
+        ss = my_suff_stat
+        self._call("evo_bsc_suffstats_tc_finish", _lib.ptr(ss["ss_dev"]), _lib.ptr(ss["lpj_dev"]), _lib.ptr(dd.Y), dd.N,
+                   self.D, self.H, int(ss["ss_dev"].shape[1]), int(ss["S_perm"]), float(model_params["pre1"]),
+                   float(model_params["pil_bar"]), _lib.ptr(fused["stats"]), _lib.ptr(fused["ws"]), _lib.ptr(fused["rest"]))
+        return fused["stats"]
 
     def E_step(self, model_params, my_suff_stat, my_data):
         dd, acc = self._estep_enqueue(model_params, my_suff_stat, my_data)
@@ -264,10 +298,17 @@ class BSC(Model):
         model_params = self.check_params(model_params)
         if len(self.to_learn) == 0:
             return Model.step(self, model_params, my_suff_stat, my_data, do_reconstruction)
-        dd, acc = self._estep_enqueue(model_params, my_suff_stat, my_data)
+        dd0 = self.device_data(my_data)
+        fused = None
+        if self.fuse_stats and self.stats in ("tc", "auto") and not dd0.incomplete:
+            fused = self._fused_begin(dd0)
+        dd, acc = self._estep_enqueue(model_params, my_suff_stat, my_data, fused)
         if do_reconstruction:
             self.reconstruct(my_data, my_suff_stat, model_params)
-        stats = self._stats_enqueue(model_params, my_suff_stat, dd)
+        if fused is not None:
+            stats = self._fused_finish(model_params, my_suff_stat, dd, fused)
+        else:
+            stats = self._stats_enqueue(model_params, my_suff_stat, dd)
         stats[-ACC_LEN:] = acc
         ev = self._tick()
         self.comm.allreduce_(stats)

@@ -160,6 +160,17 @@ static int estep_impl(const evo_estep_args *x, const evo_evolve_args *t, void *s
     int rc = estep_dims(x, dv);
     if (rc) return rc;
   }
+  if (x->fs_rest) {
+    EVO_REQUIRE(x->fs_stats && x->fs_wp_workspace, "fused statistics need fs_stats, fs_wp_workspace and fs_rest");
+    EVO_REQUIRE(x->N < 2147483647LL, "fused statistics: N must fit int32");
+    WpLists pl{};
+    wp_tc_planes(x->fs_wp_workspace, x->N, x->D, x->H, &pl);
+    dv.fs_Wq = x->fs_stats + (int64_t)x->H * x->D;
+    dv.fs_pies = dv.fs_Wq + (int64_t)x->H * x->H;
+    dv.fs_sig = dv.fs_pies + x->H;
+    dv.fs_hi = pl.et_hi; dv.fs_lo = pl.et_lo; dv.fs_ld = pl.et_ld;
+    dv.fs_rest = x->fs_rest;
+  }
   if (t) {
     dv.generic_only = 1;
     dv.evolve_only = t->evolve_only; dv.lpj_given = t->lpj_given; dv.skip_eval = t->skip_eval; dv.gen0 = t->gen0;

@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
                                                           const float *__restrict__ Ym, int64_t N, int D, int H, int Hw,
                                                           int S, int S_perm, double pre1, double pil_bar,
                                                           double *__restrict__ stats, float *__restrict__ Es_out,
-                                                          WpLists lists) {
+                                                          WpLists lists, const int32_t *__restrict__ n_list) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int cols = S + S_perm;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
@@ -180,7 +180,10 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
   double sig_acc = 0.0;
   for (int h = lane; h < H; h += 32) es[h] = 0.0;  // kept zero between datapoints (active entries reset below)
   __syncwarp();
-  for (int64_t n = (int64_t)blockIdx.x * wpc + warp; n < N; n += (int64_t)gridDim.x * wpc) {
+  // with n_list only the datapoints listed there ([0] = count, [1..]): the ones the fused E-step tail did not cover
+  const int64_t n_items = n_list ? (int64_t)n_list[0] : N;
+  for (int64_t it = (int64_t)blockIdx.x * wpc + warp; it < n_items; it += (int64_t)gridDim.x * wpc) {
+    const int64_t n = n_list ? (int64_t)n_list[1 + it] : it;
     // ---- posterior weights (bsc.py:176-177,219) ------------------------------------------------
     const double *row = lpj + n * cols;
     double mx = -DBL_MAX;
@@ -609,7 +612,7 @@ static bool wp_lists_applicable(int H) { return wp_smem(H) <= 227 * 1024 && H <=
 
 int evo::bsc_suffstats_pass1(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H, int S,
                              int S_perm, double pre1, double pil_bar, double *stats, float *Es_out, WpLists lists,
-                             cudaStream_t stream) {
+                             cudaStream_t stream, const int32_t *n_list) {
   const int Hw = words_for(H);
   EVO_REQUIRE(H <= 65535, "H > 65535 not supported by the statistics kernel");
   const size_t per_warp = suffstats_warp_bytes(H, Hw, S + S_perm);
@@ -623,7 +626,7 @@ int evo::bsc_suffstats_pass1(const uint32_t *states, const double *lpj, const fl
   auto k = bsc_suffstats_kernel;
   if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   k<<<grid_for((const void *)k, 32 * wpc, smem, (N + wpc - 1) / wpc), 32 * wpc, smem, stream>>>(
-      states, lpj, Ym, N, D, H, Hw, S, S_perm, pre1, pil_bar, stats, Es_out, lists);
+      states, lpj, Ym, N, D, H, Hw, S, S_perm, pre1, pil_bar, stats, Es_out, lists, n_list);
   EVO_LAUNCH_CHECK("bsc_suffstats");
   return EVO_OK;
 }

@@ -12,6 +12,7 @@
 
 #include "common.cuh"
 #include "evaluators.cuh"
+#include "stats.cuh"
 
 namespace evo {
 
@@ -42,6 +43,11 @@ struct EstepDev {
   uint32_t *ev_states;
   double *ev_lpj;
   int32_t *ev_count, *ev_pool, *ev_pool_n;
+  // ---- fused BSC statistics in the tail of the randflip fast path (estep_flip.cuh); fs_rest == NULL: off --------------
+  double *fs_Wq, *fs_pies, *fs_sig;
+  __half *fs_hi, *fs_lo;  // transposed fp16 planes of 2^14 <s>: [h][n], row stride fs_ld
+  int64_t fs_ld;
+  int32_t *fs_rest;       // [0] = count, [1..]: datapoints the tail did not cover
   // derived
   int Cg;    // children capacity per generation
   int Ctot;  // Cg * n_generations
@@ -762,6 +768,19 @@ static int launch_estep_variant(const EstepDev &dv, Eval ev, int64_t items, cuda
   return EVO_OK;
 }
 
+// fused statistics not covered by the kernel that runs: every datapoint goes to the separate statistics pass
+static __global__ void fs_rest_all_kernel(int32_t *rest, int64_t N) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i <= N; i += (int64_t)gridDim.x * blockDim.x)
+    rest[i] = i == 0 ? (int32_t)N : (int32_t)(i - 1);
+}
+static int fs_rest_all(const EstepDev &dv, cudaStream_t st) {
+  if (!dv.fs_rest) return EVO_OK;
+  int64_t b = (dv.N + 256) / 256, cap = (int64_t)sm_count() * 8;
+  fs_rest_all_kernel<<<(int)(b < cap ? b : cap), 256, 0, st>>>(dv.fs_rest, dv.N);
+  EVO_LAUNCH_CHECK("fs_rest_all");
+  return EVO_OK;
+}
+
 // randflip fast path over index lists with implicit children (estep_flip.cuh)
 struct BscGramEval;
 template <int TT>
@@ -774,6 +793,7 @@ static int launch_estep_T(const EstepDev &dv, Eval ev, bool fast, cudaStream_t s
     if (fast && dv.ovf_list && dv.H < 65535 && dv.S + PB < 65535 && dv.N < 2147483647LL && dv.n_children <= dv.H &&
         !getenv("EVO_ESTEP_BITS")) {
       EVO_CUDA(cudaMemsetAsync(dv.ovf_list, 0, sizeof(int32_t), st));
+      if (dv.fs_rest) EVO_CUDA(cudaMemsetAsync(dv.fs_rest, 0, sizeof(int32_t), st));
       int rc = launch_estep_flip<TT>(dv, ev, st);
       if (rc) return rc;
       EstepDev db = dv;
@@ -785,6 +805,10 @@ static int launch_estep_T(const EstepDev &dv, Eval ev, bool fast, cudaStream_t s
   }
   EstepDev db = dv;
   db.ovf_list = nullptr;
+  {
+    int rc = fs_rest_all(dv, st);
+    if (rc) return rc;
+  }
   if (fast) return launch_estep_variant<Eval, TT, true, false>(db, ev, dv.N, st);
   return launch_estep_variant<Eval, TT, false, false>(db, ev, dv.N, st);
 }

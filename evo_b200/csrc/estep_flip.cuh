@@ -223,6 +223,122 @@ __device__ __forceinline__ int flip_insert(const EstepDev &a, const FlipSmem &s,
   return -1;
 }
 
+// ---- fused BSC statistics (bsc.py:176-223) in the E-step tail ---------------------------------------------------------
+// K^n (lists) and its final log-joints are still in shared memory: posterior weights, sigma, <s>_n over the union of
+// the live states' latents, the Wq pair sums and the fp16 hi / lo planes of <s>_n for the tensor-core Wp GEMM are
+// formed here instead of by a second pass that re-reads lpj and the K sets from HBM.  Slots replaced in this E-step are
+// implicit (parent row, position): they are materialised into scratch rows carved from the dead sb / sg arrays first.
+// Returns this datapoint's sigma term (valid on thread 0); a datapoint that does not fit (scratch rows, union
+// capacity) is appended to fs_rest untouched.
+constexpr double FS_Q_SKIP = 1e-18;  // = Q_SKIP of the statistics pass (bsc.cu)
+template <int T>
+__device__ __forceinline__ double flip_fused_stats(const EstepDev &a, const FlipSmem &s, const BscGramEval &ev, int64_t n,
+                                                   double mx, double se, double lpj_perm) {
+  const int tid = threadIdx.x, S = a.S, Hw = a.Hw;
+  uint32_t *scr = reinterpret_cast<uint32_t *>(s.sb);  // sb, sg: dead after the generations
+  const int R = (int)((reinterpret_cast<unsigned char *>(s.keys) - reinterpret_cast<unsigned char *>(s.sb)) / (FL_STRIDE * 4));
+  uint32_t *ubm = reinterpret_cast<uint32_t *>(s.keys);                        // union bitmap [Hw]
+  const int keys_bytes = (a.PK + 2) * 8, bm_bytes = (4 * Hw + 7) & ~7;
+  uint16_t *act = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(s.keys) + bm_bytes);
+  double *es_u = reinterpret_cast<double *>(s.hash);                           // [S + Ctot] doubles, dead too
+  int capU = keys_bytes > bm_bytes ? (keys_bytes - bm_bytes) / 2 : 0;
+  if (capU > S + a.Ctot) capU = S + a.Ctot;
+  int *frow = s.old_by_rank;  // scratch row of a replaced slot, -1 = the slot's own row
+  bool ok = capU >= 32;
+  // ---- scratch rows for the replaced slots ----------------------------------------------------------------------------
+  int nrep = 0;
+  for (int base = 0; base < S; base += T) {
+    const int k = base + tid;
+    const bool f = k < S && s.pool[k] > 0;
+    int tot;
+    const int off = group_scan_flag<T>(f, tot, s.red_i);
+    if (k < S) frow[k] = f ? nrep + off : -1;
+    nrep += tot;
+    gsync<T>();
+  }
+  if (nrep > R) ok = false;
+  if (ok) {
+    _Pragma("unroll 1") for (int k = tid; k < S; k += T) {
+      if (frow[k] >= 0) {
+        const int i = s.pool[k] - 1;
+        flist_toggle_copy(s.rows + (size_t)s.nw_par[i] * FL_STRIDE, s.nw_pos[i], scr + (size_t)frow[k] * FL_STRIDE);
+      }
+    }
+    _Pragma("unroll 1") for (int w = tid; w < Hw; w += T) ubm[w] = 0u;
+  }
+  gsync<T>();
+  // ---- posterior weights, union bitmap, sigma ----------------------------------------------------------------------------
+  const double inv = 1.0 / se;
+  double sg = 0.0;
+  if (ok) {
+    _Pragma("unroll 1") for (int k = tid; k < S; k += T) {
+      const double qk = exp(s.lpj[k] - mx) * inv;
+      if (!(qk > FS_Q_SKIP)) continue;
+      const uint16_t *e = reinterpret_cast<const uint16_t *>(frow[k] >= 0 ? scr + (size_t)frow[k] * FL_STRIDE : s.rows + (size_t)k * FL_STRIDE);
+      const int na = e[31];
+      for (int x = 0; x < na; ++x) atomicOr(&ubm[e[x] >> 5], 1u << (e[x] & 31));
+      sg += qk * (s.lpj[k] - ev.pil_bar * (double)na) / ev.pre1;
+    }
+    if (a.S_perm > 0 && tid == 0) sg += exp(lpj_perm - mx) * inv * lpj_perm / ev.pre1;  // all-zero state: |y|^2
+  }
+  gsync<T>();
+  // ---- ascending list of the union (warp 0) -----------------------------------------------------------------------------------
+  if (ok && tid < 32) {
+    int nu = 0;
+    for (int w0 = 0; w0 < Hw; w0 += 32) {
+      uint32_t word = (w0 + tid < Hw) ? ubm[w0 + tid] : 0u;
+      const int c = __popc(word);
+      int pre = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, pre, o); if (tid >= o) pre += t; }
+      int pos = nu + pre - c;
+      while (word) {
+        const int bp = __ffs(word) - 1;
+        word &= word - 1;
+        if (pos < capU) act[pos] = (uint16_t)(((w0 + tid) << 5) + bp);
+        ++pos;
+      }
+      nu += __shfl_sync(0xffffffffu, pre, 31);
+    }
+    if (tid == 0) s.sh[1] = nu;
+  }
+  gsync<T>();
+  const int nu = ok ? s.sh[1] : 0;
+  if (nu > capU) ok = false;
+  if (!ok) {
+    if (tid == 0) a.fs_rest[1 + atomicAdd(a.fs_rest, 1)] = (int32_t)n;
+    return 0.0;
+  }
+  _Pragma("unroll 1") for (int i = tid; i < nu; i += T) es_u[i] = 0.0;
+  gsync<T>();
+  // ---- <s> over the union and the Wq pair sums ------------------------------------------------------------------------------------
+  _Pragma("unroll 1") for (int k = tid; k < S; k += T) {
+    const double qk = exp(s.lpj[k] - mx) * inv;
+    if (!(qk > FS_Q_SKIP)) continue;
+    const uint16_t *e = reinterpret_cast<const uint16_t *>(frow[k] >= 0 ? scr + (size_t)frow[k] * FL_STRIDE : s.rows + (size_t)k * FL_STRIDE);
+    const int na = e[31];
+    for (int x = 0; x < na; ++x) {
+      const int h = e[x];
+      int lo = 0, hi = nu;  // position of h in the union list
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (act[mid] < h) lo = mid + 1; else hi = mid; }
+      atomicAdd(&es_u[lo], qk);
+      double *wrow = a.fs_Wq + (int64_t)h * a.H;
+      for (int y = 0; y <= x; ++y) atomicAdd(wrow + e[y], qk);  // h' <= h
+    }
+  }
+  gsync<T>();
+  _Pragma("unroll 1") for (int i = tid; i < nu; i += T) {
+    const int h = act[i];
+    const double v = es_u[i];
+    atomicAdd(a.fs_pies + h, v);
+    const double sv = v * WP_TC_SCALE;
+    const __half hi = __double2half(sv);
+    a.fs_hi[(int64_t)h * a.fs_ld + n] = hi;
+    a.fs_lo[(int64_t)h * a.fs_ld + n] = __double2half(sv - (double)__half2float(hi));
+  }
+  return group_sum<T>(sg, s.red_d);
+}
+
 template <int T>
 __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval ev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -230,7 +346,7 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
   flip_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
   const int Hg = a.Hw, S = a.S, Hm = a.H, C = a.n_children;
-  double acc_F = 0.0, acc_U = 0.0, acc_sub = 0.0, acc_eval = 0.0;
+  double acc_F = 0.0, acc_U = 0.0, acc_sub = 0.0, acc_eval = 0.0, acc_sig = 0.0;
   unsigned long long cnt_nan = 0, cnt_small = 0, cnt_inf = 0;
 
   for (int64_t n = blockIdx.x; n < a.N; n += gridDim.x) {
@@ -255,7 +371,10 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
     }
     gsync<T>();
     if (s.sh[0]) {  // a state of K^n has more than FL_CAP active latents: not for this kernel
-      if (tid == 0) a.ovf_list[1 + atomicAdd(a.ovf_list, 1)] = (int32_t)n;
+      if (tid == 0) {
+        a.ovf_list[1 + atomicAdd(a.ovf_list, 1)] = (int32_t)n;
+        if (a.fs_rest) a.fs_rest[1 + atomicAdd(a.fs_rest, 1)] = (int32_t)n;
+      }
       continue;
     }
     unsigned fl0 = 0;
@@ -422,8 +541,14 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
       if (pool_n == 0) break;  // "No new and unique states" (eas.py:306-308)
     }
     if (s.sh[0]) {  // nothing of this datapoint has been written yet
-      if (tid == 0) a.ovf_list[1 + atomicAdd(a.ovf_list, 1)] = (int32_t)n;
+      if (tid == 0) {
+        a.ovf_list[1 + atomicAdd(a.ovf_list, 1)] = (int32_t)n;
+        if (a.fs_rest) a.fs_rest[1 + atomicAdd(a.fs_rest, 1)] = (int32_t)n;
+      }
       continue;
+    }
+    if (a.fs_rest) {  // slots replaced below are recorded here (the parent pool is no longer needed)
+      _Pragma("unroll 1") for (int k = tid; k < S; k += T) s.pool[k] = 0;
     }
 
     // ---- vary_Kn (utils.py:295-319): identical ranking to estep_kernel ---------------------------------------------------
@@ -465,6 +590,7 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
             if (!(ln[i] > s.lpj[k])) continue;
             flist_to_bits_toggled(s.rows + (size_t)s.nw_par[i] * FL_STRIDE, s.nw_pos[i], Hg, a.states + (n * (int64_t)S + k) * Hg);
             s.rnk[e] = -1 - k;  // lpj written after the barrier (other threads still compare against the old value)
+            if (a.fs_rest) s.pool[k] = i + 1;
             ++acc_local;
           }
           gsync<T>();
@@ -491,8 +617,10 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
         acc_sub += (double)n_sub;
         acc_eval += (double)(S + U);
       }
+      if (a.fs_rest) acc_sig += flip_fused_stats<T>(a, s, ev, n, mx, se, lpj_perm);
     }
   }
+  if (tid == 0 && a.fs_rest && acc_sig != 0.0) atomicAdd(a.fs_sig, acc_sig);
   if (tid == 0 && a.acc) {
     atomicAdd(a.acc + 0, acc_F);
     atomicAdd(a.acc + 1, acc_U);

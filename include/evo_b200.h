@@ -142,6 +142,16 @@ typedef struct evo_estep_args {
    * 4*Hw); datapoints that do not fit are collected here and redone by the packed-bits kernel in the same
    * call.  Results do not depend on which kernel handled a datapoint. */
   int32_t *overflow_list;
+  /* FUSED BSC STATISTICS (optional; all three NULL = off).  With them, the randflip fast path of the Gram evaluator
+   * adds each datapoint's share of Wq, pies and sigma (bsc.py:193-223) to `fs_stats` in the tail of the E-step --
+   * K^n and its log-joints are still in shared memory there -- and writes <s>_n into the fp16 planes of the
+   * tensor-core Wp workspace `fs_wp_workspace` (cleared beforehand by evo_bsc_wp_tc_begin).  Datapoints it does not
+   * cover (packed-bits overflow pass, unions of more than 384 latents, more substitutions than scratch rows; every
+   * datapoint if another kernel variant runs) are listed in `fs_rest` ([0] = count, N + 1 int32) for
+   * evo_bsc_suffstats_tc_finish, which adds their share and runs the Wp GEMM. */
+  double *fs_stats;
+  void *fs_wp_workspace;
+  int32_t *fs_rest;
 } evo_estep_args;
 int evo_estep(const evo_estep_args *args, void *stream);
 
@@ -215,6 +225,13 @@ int evo_bsc_wp_tc_set_data(const float *Ym, int64_t N, int D, int H, void *works
 int evo_bsc_suffstats_tc(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H,
                          int S, int S_perm, double pre1, double pil_bar, double *stats, float *Es_out,
                          void *workspace, void *stream);
+/* The two halves of evo_bsc_suffstats_tc around a fused E-step (evo_estep_args.fs_*): `begin` clears the <s> planes of
+ * the workspace BEFORE evo_estep; `finish` adds the statistics of the datapoints listed in `rest` ([0] = count; NULL =
+ * all N) and runs the split-K Wp GEMM. */
+int evo_bsc_wp_tc_begin(int64_t N, int D, int H, void *workspace, void *stream);
+int evo_bsc_suffstats_tc_finish(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H,
+                                int S, int S_perm, double pre1, double pil_bar, double *stats, void *workspace,
+                                const int32_t *rest, void *stream);
 /* y_rec[n][d] = sum_h <s_h>_n W[d][h] where recon_mask[n][d] == 0 (x false); other entries copy y;
  * rows whose infer_mask is all zero are left untouched (_models.py:646-648). */
 int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double *W, const float *Y,

@@ -283,3 +283,50 @@ def test_tc_statistics_with_missing_data_match_f64():
     assert np.max(np.abs(out["tc"][0] - out["f64"][0]) / np.abs(out["f64"][0])) < 1e-5, out
     assert np.max(np.abs(out["tc"][1] - out["f64"][1])) < 1e-4 * np.abs(out["f64"][1]).max()
     assert abs(out["tc"][2] - out["f64"][2]) < 1e-5 * out["f64"][2]
+
+
+@pytest.mark.parametrize("D,H,K,N,act,ea,perm", [
+    (64, 40, 32, 3000, 3.0, (6, 4, 2), False),    # everything through the fused tail
+    (32, 96, 24, 1500, 24.0, (6, 4, 2), False),   # states around the 31-latent list capacity: a mix of tail and rest list
+    (48, 300, 64, 2000, 5.0, (8, 8, 2), False),   # cfg2-like shape
+    (40, 1030, 32, 300, 4.0, (8, 4, 2), False),   # 33 words per packed state
+    (64, 40, 32, 1000, 3.0, (6, 4, 2), True),     # permanent all-zero state
+])
+def test_fused_statistics_equal_the_separate_pass(D, H, K, N, act, ea, perm):
+    """BSC.step with the statistics formed in the tail of the E-step kernel (evo_estep_args.fs_*, the bench's path)
+    against the same step with the separate statistics pass: same K sets and F, parameters equal up to the order of
+    the f64 atomics."""
+    import torch
+
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import init_states
+
+    rng = np.random.RandomState(D + H)
+    Wg = rng.normal(size=(D, H)) * 2.0
+    s = rng.random_sample((N, H)) < act / H
+    Y = (s @ Wg.T + rng.normal(size=(N, D))).astype(np.float32)
+    permanent = {"background": False, "allzero": True, "singletons": False} if perm else None
+    out = {}
+    for fuse in (True, False):
+        m = BSC(D, H, K)
+        m.tables = m.stats = "tc"
+        m.fuse_stats = fuse
+        data = {"y": torch.as_tensor(Y, device=m.device), "x_infr": None}
+        np.random.seed(1)
+        th = m.check_params(m.standard_init(data))
+        cont = init_states(N, K, H, "fit", "randflip", *ea, p_init_Kn=act / H, permanent=permanent, device=m.device, seed=11)
+        Fs = []
+        for _ in range(2):
+            F, _, _, th = m.step(th, cont, data)
+            Fs.append(F)
+        rest = int(data and m.device_data(data).cache["fs_rest"][0].item()) if fuse else None
+        out[fuse] = (np.array(Fs), np.asarray(th["W"]), th["pi"], th["sigma"], cont["ss_dev"].cpu().numpy(), rest)
+    a, b = out[True], out[False]
+    assert np.array_equal(a[4], b[4])
+    assert np.max(np.abs(a[0] - b[0]) / np.abs(b[0])) < 1e-12
+    assert np.abs(a[1] - b[1]).max() < 1e-9 * np.abs(b[1]).max()
+    assert abs(a[2] - b[2]) < 1e-12 * b[2] and abs(a[3] - b[3]) < 1e-12 * b[3]
+    if act == 24.0:
+        assert 0 < a[5] < N, a[5]  # both routes took part
+    elif act == 3.0:
+        assert a[5] < N // 10, a[5]  # a few datapoints replace more slots than there are scratch rows
