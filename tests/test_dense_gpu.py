@@ -289,7 +289,7 @@ def test_tc_statistics_with_missing_data_match_f64():
     (64, 40, 32, 3000, 3.0, (6, 4, 2), False),    # everything through the fused tail
     (32, 96, 24, 1500, 24.0, (6, 4, 2), False),   # states around the 31-latent list capacity: a mix of tail and rest list
     (48, 300, 64, 2000, 5.0, (8, 8, 2), False),   # cfg2-like shape
-    (40, 1030, 32, 300, 4.0, (8, 4, 2), False),   # 33 words per packed state
+    (40, 1030, 32, 8000, 4.0, (8, 4, 2), False),  # 33 words per packed state (N large enough for a regular Wq)
     (64, 40, 32, 1000, 3.0, (6, 4, 2), True),     # permanent all-zero state
 ])
 def test_fused_statistics_equal_the_separate_pass(D, H, K, N, act, ea, perm):
