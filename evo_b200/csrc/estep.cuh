@@ -48,6 +48,8 @@ struct EstepDev {
   __half *fs_hi, *fs_lo;  // transposed fp16 planes of 2^14 <s>: [h][n], row stride fs_ld
   int64_t fs_ld;
   int32_t *fs_rest;       // [0] = count, [1..]: datapoints the tail did not cover
+  // ---- CUDA-graph replay: per-iteration scalars from device memory (evo_bsc_em_advance); NULL = the fields above ----
+  const double *theta_dev;  // [0] pre1 [1] pil_bar [2] piH [3] iteration
   // derived
   int Cg;    // children capacity per generation
   int Ctot;  // Cg * n_generations
@@ -55,6 +57,20 @@ struct EstepDev {
   int PK;    // capacity of pool / key arrays = max(S, Cg)
   uint32_t mask_c, mask_s, mask_p;  // index-code masks (pow2 - 1) for Ctot, S, PK (order_key)
 };
+
+// theta_dev overrides the scalars that were kernel arguments (BSC evaluators; other evaluators have none)
+__device__ __forceinline__ void theta_set(BscGramEval &ev, const double *t) { ev.pre1 = t[0]; ev.pil_bar = t[1]; }
+__device__ __forceinline__ void theta_set(BscDirectEval &ev, const double *t) { ev.pre1 = t[0]; ev.pil_bar = t[1]; }
+template <class Eval>
+__device__ __forceinline__ void theta_set(Eval &, const double *) {}
+template <class Eval>
+__device__ __forceinline__ void theta_override(EstepDev &a, Eval &ev) {
+  if (a.theta_dev) {
+    theta_set(ev, a.theta_dev);
+    a.sparseness = a.theta_dev[2];
+    a.iteration = (uint32_t)a.theta_dev[3];
+  }
+}
 
 constexpr int TAG_EMPTY = -1;
 constexpr int TAG_CHILD = 1 << 24;
@@ -367,6 +383,7 @@ template <class Eval, int T, bool FAST = false, bool LIST = false>
 __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   EstepSmem s;
+  theta_override(a, ev);
   estep_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
   const int Hw = LIST ? LIST_WORDS : a.Hr, Hg = a.Hw, Hs = LIST ? LIST_WORDS + 1 : a.Hs, S = a.S;  // Hw: words of a shared-memory row, Hg: of a global row

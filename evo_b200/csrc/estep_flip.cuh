@@ -343,6 +343,7 @@ template <int T>
 __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval ev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FlipSmem s;
+  theta_override(a, ev);
   flip_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
   const int Hg = a.Hw, S = a.S, Hm = a.H, C = a.n_children;
