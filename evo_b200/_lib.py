@@ -37,6 +37,7 @@ class EstepArgs(C.Structure):
         ("acc", C.c_void_p),
         ("overflow_list", C.c_void_p),
         ("fs_stats", C.c_void_p), ("fs_wp_workspace", C.c_void_p), ("fs_rest", C.c_void_p),
+        ("theta_dev", C.c_void_p),
     ]
 
 
@@ -110,10 +111,11 @@ SIGNATURES = {
     "evo_bsc_wp_tc_workspace_bytes": (_i64, [_i64, _i, _i]),
     "evo_bsc_wp_tc_set_data": (_i, [_vp, _i64, _i, _i, _vp, _vp]),
     "evo_bsc_wp_tc_begin": (_i, [_i64, _i, _i, _vp, _vp]),
-    "evo_bsc_suffstats_tc_finish": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp]),
+    "evo_bsc_suffstats_tc_finish": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp, _vp]),
     "evo_bsc_suffstats_tc": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp]),
     "evo_bsc_solve_workspace_bytes": (_i64, [_i, _i]),
     "evo_bsc_solve": (_i, [_vp, _d, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp, _vp]),
+    "evo_bsc_em_advance": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _d, _d, _d, _d, _vp]),
     "evo_bsc_solve_static": (_i, [_vp, _d, _i, _i, _i, _i, _d, _d, _vp, _vp, _vp, _vp]),
     "evo_es3c_update_workspace_bytes": (_i64, [_i, _i]),
     "evo_es3c_update": (_i, [C.POINTER(Es3cUpdateArgs), _vp]),

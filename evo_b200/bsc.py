@@ -118,12 +118,17 @@ class BSC(Model):
         else:
             a.eval = _lib.EVAL_BSC_GRAM
             a.G, a.B, a.ynorm2 = c["G"].data_ptr(), c["B"].data_ptr(), c["ynorm2"].data_ptr()
+        if self._theta_dev is not None:  # CUDA-graph replay (emgraph.py): the scalars above come from device memory
+            a.theta_dev = self._theta_dev.data_ptr()
         return None
 
+    _theta_dev = None
+
     # ---- E-step (_models.py:454-565) -----------------------------------------------------------------
-    def _estep_enqueue(self, model_params, my_suff_stat, my_data, fused=None):
+    def _estep_enqueue(self, model_params, my_suff_stat, my_data, fused=None, precompute=True):
         dd = self.device_data(my_data)
-        self.E_step_precompute(model_params, my_suff_stat, my_data)
+        if precompute:
+            self.E_step_precompute(model_params, my_suff_stat, my_data)
         self._tables(model_params, dd)
         acc = torch.zeros(ACC_LEN, dtype=torch.float64, device=self.device)
 
@@ -161,7 +166,8 @@ class BSC(Model):
         ss = my_suff_stat
         self._call("evo_bsc_suffstats_tc_finish", _lib.ptr(ss["ss_dev"]), _lib.ptr(ss["lpj_dev"]), _lib.ptr(dd.Y), dd.N,
                    self.D, self.H, int(ss["ss_dev"].shape[1]), int(ss["S_perm"]), float(model_params["pre1"]),
-                   float(model_params["pil_bar"]), _lib.ptr(fused["stats"]), _lib.ptr(fused["ws"]), _lib.ptr(fused["rest"]))
+                   float(model_params["pil_bar"]), _lib.ptr(fused["stats"]), _lib.ptr(fused["ws"]), _lib.ptr(fused["rest"]),
+                   _lib.ptr(self._theta_dev))
         return fused["stats"]
 
     def E_step(self, model_params, my_suff_stat, my_data):
@@ -362,6 +368,13 @@ class BSC(Model):
                    _lib.ptr(ws) if ws is not False else None, int(ws.numel()) if ws is not False else 0)
         return stats
 
+    def em_graph(self, model_params, my_suff_stat, my_data, max_iterations=4096):
+        """Whole EM iterations as one replayed CUDA graph: `g = model.em_graph(theta, ss, data); F, S_nunique, S_sub =
+        g.run(n); theta = g.theta_out()` equals n calls of `step` (emgraph.py)."""
+        from .emgraph import EMGraph
+
+        return EMGraph(self, model_params, my_suff_stat, my_data, max_iterations)
+
     def M_step(self, model_params, my_suff_stat, my_data):
         dd = self.device_data(my_data)
         stats = self._stats_enqueue(model_params, my_suff_stat, dd)
@@ -372,7 +385,7 @@ class BSC(Model):
         pend = self._solve_enqueue(model_params, my_suff_stat, dd, stats)
         return self._solve_finish(model_params, my_suff_stat, dd, pend, pend["scal"].cpu().numpy())
 
-    def _solve_enqueue(self, model_params, my_suff_stat, dd, stats):
+    def _solve_enqueue(self, model_params, my_suff_stat, dd, stats, out=None):
         """Parameter update from the reduced statistics (bsc.py:226-275) by `evo_bsc_solve` (block Gaussian
         elimination of [Wq | Wp] on the device), enqueued without a host read; `scal` = (info, pi, sigma, W finite) is
         read once by the caller together with the E-step scalars."""
@@ -382,9 +395,13 @@ class BSC(Model):
             nb = int(self.lib.evo_bsc_solve_workspace_bytes(D, H))
             ws = self._solve_ws = torch.empty(nb, dtype=torch.uint8, device=self.device)
         learn_W = "W" in self.to_learn
-        W_out = torch.empty((D, H), dtype=torch.float64, device=self.device) if learn_W else None
-        pies = torch.empty(H, dtype=torch.float64, device=self.device)
-        scal = torch.empty(4, dtype=torch.float64, device=self.device)
+        if out is not None:  # caller-owned static buffers (emgraph.py); W is not an input of the solve: in place is safe
+            W_out, pies, scal = out
+            W_out = W_out if learn_W else None
+        else:
+            W_out = torch.empty((D, H), dtype=torch.float64, device=self.device) if learn_W else None
+            pies = torch.empty(H, dtype=torch.float64, device=self.device)
+            scal = torch.empty(4, dtype=torch.float64, device=self.device)
         self._call("evo_bsc_solve", _lib.ptr(stats), float(dd.N_total), D, H, int(learn_W),
                    int(bool(my_suff_stat["permanent"]["background"])), float(dd.n_obs_total) if dd.incomplete else -1.0,
                    float(model_params["sigma"]), _lib.ptr(W_out), _lib.ptr(pies), _lib.ptr(scal), _lib.ptr(ws))

@@ -160,6 +160,9 @@ static int estep_impl(const evo_estep_args *x, const evo_evolve_args *t, void *s
     int rc = estep_dims(x, dv);
     if (rc) return rc;
   }
+  dv.theta_dev = x->theta_dev;
+  EVO_REQUIRE(!x->theta_dev || x->eval == EVO_EVAL_BSC_GRAM || x->eval == EVO_EVAL_BSC_DIRECT,
+              "theta_dev is for the BSC evaluators");
   if (x->fs_rest) {
     EVO_REQUIRE(x->fs_stats && x->fs_wp_workspace, "fused statistics need fs_stats, fs_wp_workspace and fs_rest");
     EVO_REQUIRE(x->N < 2147483647LL, "fused statistics: N must fit int32");

@@ -164,8 +164,10 @@ __global__ void __launch_bounds__(256) bsc_suffstats_kernel(const uint32_t *__re
                                                           const float *__restrict__ Ym, int64_t N, int D, int H, int Hw,
                                                           int S, int S_perm, double pre1, double pil_bar,
                                                           double *__restrict__ stats, float *__restrict__ Es_out,
-                                                          WpLists lists, const int32_t *__restrict__ n_list) {
+                                                          WpLists lists, const int32_t *__restrict__ n_list,
+                                                          const double *__restrict__ theta_dev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  if (theta_dev) { pre1 = theta_dev[0]; pil_bar = theta_dev[1]; }  // CUDA-graph replay: scalars from device memory
   const int cols = S + S_perm;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
   unsigned char *mine = smem_raw + (size_t)warp * suffstats_warp_bytes(H, Hw, cols);
@@ -612,7 +614,7 @@ static bool wp_lists_applicable(int H) { return wp_smem(H) <= 227 * 1024 && H <=
 
 int evo::bsc_suffstats_pass1(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H, int S,
                              int S_perm, double pre1, double pil_bar, double *stats, float *Es_out, WpLists lists,
-                             cudaStream_t stream, const int32_t *n_list) {
+                             cudaStream_t stream, const int32_t *n_list, const double *theta_dev) {
   const int Hw = words_for(H);
   EVO_REQUIRE(H <= 65535, "H > 65535 not supported by the statistics kernel");
   const size_t per_warp = suffstats_warp_bytes(H, Hw, S + S_perm);
@@ -626,7 +628,7 @@ int evo::bsc_suffstats_pass1(const uint32_t *states, const double *lpj, const fl
   auto k = bsc_suffstats_kernel;
   if (smem > 48 * 1024) EVO_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   k<<<grid_for((const void *)k, 32 * wpc, smem, (N + wpc - 1) / wpc), 32 * wpc, smem, stream>>>(
-      states, lpj, Ym, N, D, H, Hw, S, S_perm, pre1, pil_bar, stats, Es_out, lists, n_list);
+      states, lpj, Ym, N, D, H, Hw, S, S_perm, pre1, pil_bar, stats, Es_out, lists, n_list, theta_dev);
   EVO_LAUNCH_CHECK("bsc_suffstats");
   return EVO_OK;
 }

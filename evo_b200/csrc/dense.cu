@@ -922,7 +922,7 @@ extern "C" int evo_bsc_wp_tc_begin(int64_t N, int D, int H, void *workspace, voi
 
 static int wp_tc_finish(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H, int S,
                         int S_perm, double pre1, double pil_bar, double *stats, float *Es_out, void *workspace,
-                        const int32_t *rest, bool all, cudaStream_t st);
+                        const int32_t *rest, bool all, const double *theta_dev, cudaStream_t st);
 
 extern "C" int evo_bsc_suffstats_tc(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H,
                                     int S, int S_perm, double pre1, double pil_bar, double *stats, float *Es_out,
@@ -930,22 +930,22 @@ extern "C" int evo_bsc_suffstats_tc(const uint32_t *states, const double *lpj, c
   EVO_REQUIRE(states && lpj && stats && workspace && N > 0 && D > 0 && H > 0 && S > 0, "bad arguments");
   int rc = evo_bsc_wp_tc_begin(N, D, H, workspace, stream);
   if (rc) return rc;
-  return wp_tc_finish(states, lpj, Ym, N, D, H, S, S_perm, pre1, pil_bar, stats, Es_out, workspace, nullptr, true,
+  return wp_tc_finish(states, lpj, Ym, N, D, H, S, S_perm, pre1, pil_bar, stats, Es_out, workspace, nullptr, true, nullptr,
                       (cudaStream_t)stream);
 }
 
 extern "C" int evo_bsc_suffstats_tc_finish(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D,
                                            int H, int S, int S_perm, double pre1, double pil_bar, double *stats,
-                                           void *workspace, const int32_t *rest, void *stream) {
+                                           void *workspace, const int32_t *rest, const double *theta_dev, void *stream) {
   EVO_REQUIRE(states && lpj && stats && workspace && N > 0 && D > 0 && H > 0 && S > 0, "bad arguments");
   EVO_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   return wp_tc_finish(states, lpj, Ym, N, D, H, S, S_perm, pre1, pil_bar, stats, nullptr, workspace, rest, rest == nullptr,
-                      (cudaStream_t)stream);
+                      theta_dev, (cudaStream_t)stream);
 }
 
 static int wp_tc_finish(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H, int S,
                         int S_perm, double pre1, double pil_bar, double *stats, float *Es_out, void *workspace,
-                        const int32_t *rest, bool all, cudaStream_t st) {
+                        const int32_t *rest, bool all, const double *theta_dev, cudaStream_t st) {
   dense::WGeometry g = dense::wgeometry(N, D, H);
   uint8_t *ws = reinterpret_cast<uint8_t *>(workspace);
   __half *yt = reinterpret_cast<__half *>(ws + 256);
@@ -954,7 +954,7 @@ static int wp_tc_finish(const uint32_t *states, const double *lpj, const float *
   lists.et_hi = et;
   lists.et_lo = et + (size_t)g.Hr * g.Np;
   lists.et_ld = g.Np;
-  int rc = bsc_suffstats_pass1(states, lpj, Ym, N, D, H, S, S_perm, pre1, pil_bar, stats, Es_out, lists, st, all ? nullptr : rest);
+  int rc = bsc_suffstats_pass1(states, lpj, Ym, N, D, H, S, S_perm, pre1, pil_bar, stats, Es_out, lists, st, all ? nullptr : rest, theta_dev);
   if (rc) return rc;
   CUtensorMap ta, tb;
   rc = dense::encode_2d(&ta, et, (uint64_t)g.Np, (uint64_t)(2 * g.Hr), (uint32_t)dense::BM);

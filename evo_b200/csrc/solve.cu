@@ -354,6 +354,7 @@ __global__ void bsc_finish_kernel(const double *__restrict__ Mx, int64_t ld, int
     }
   }
 }
+__global__ void set_int_kernel(int *p, int v) { *p = v; }
 __global__ void flag_to_scal_kernel(const int *flag, double *scal, int slot) { scal[slot] = (double)flag[0]; }
 
 struct SolveWs {
@@ -470,10 +471,8 @@ extern "C" int evo_bsc_solve(const double *stats, double N_total, int D, int H, 
   cudaStream_t st = (cudaStream_t)stream;
   SolveWs w = carve_ws(workspace, H, D);
   EVO_CUDA(cudaMemsetAsync(workspace, 0, 64, st));  // scale, info
-  {
-    int one = 1;
-    EVO_CUDA(cudaMemcpyAsync(w.finite, &one, sizeof(int), cudaMemcpyHostToDevice, st));
-  }
+  set_int_kernel<<<1, 1, 0, st>>>(w.finite, 1);  // a kernel, not a copy from the host stack: capturable in a CUDA graph
+  EVO_LAUNCH_CHECK("set_int");
   if (learn_W) {
     const double *Wp = stats, *Wq = stats + (int64_t)H * D;
     load_matrix_kernel<<<ew_grid((int64_t)w.Hp * w.Hp), 256, 0, st>>>(Wq, H, w.Hp, 0, 0.0, w.Mx, w.Wd,
@@ -514,10 +513,8 @@ extern "C" int evo_es3c_update(const evo_es3c_update_args *x, void *stream) {
   int *infoP = reinterpret_cast<int *>(tr + 1);  // second info word (Psi solve)
   EVO_CUDA(cudaMemsetAsync(x->workspace, 0, 64, st));
   EVO_CUDA(cudaMemsetAsync(tr, 0, 16, st));
-  {
-    int one = 1;
-    EVO_CUDA(cudaMemcpyAsync(w.finite, &one, sizeof(int), cudaMemcpyHostToDevice, st));
-  }
+  set_int_kernel<<<1, 1, 0, st>>>(w.finite, 1);  // a kernel, not a copy from the host stack: capturable in a CUDA graph
+  EVO_LAUNCH_CHECK("set_int");
   // ---- W = Wp inv(sum_szsz)  <=>  sum_szsz' W' = WpT  (sssc.py:692-694) --------------------------------------------------
   if (x->learn_W) {
     SolveWs ww = w;
@@ -562,6 +559,45 @@ extern "C" int evo_es3c_update(const evo_es3c_update_args *x, void *stream) {
   es3c_scal_kernel<<<1, 1, 0, st>>>(w.info, infoP, w.finite, tr, x->incomplete, x->ysq, trace, x->n_obs_total, x->sigma2_old,
                                     x->N_total, D, x->eps_sigma2, x->learn_sigma2, x->scal);
   EVO_LAUNCH_CHECK("es3c_scal");
+  return EVO_OK;
+}
+
+// ---- evo_bsc_em_advance: the host's share of an EM iteration (check_params + E_step_precompute + logging) on the device --
+// One thread.  rec row: [0..8) acc, [8..12) scal, [12] ljc, [13] pi, [14] sigma, [15] iteration -- all of the iteration
+// that just ran; then theta <- the clamped new parameters and their precomputed scalars, iteration + 1.
+__global__ void bsc_em_advance_kernel(const double *__restrict__ acc, const double *__restrict__ scal, double *theta, double *rec,
+                                      int max_rec, int D, int H, int learn_pi, int learn_sigma, double pi_lo, double pi_hi,
+                                      double sigma_lo, double sigma_hi) {
+  const int r = (int)theta[7];
+  if (rec && r < max_rec) {
+    double *row = rec + (int64_t)r * 16;
+    for (int i = 0; i < 8; ++i) row[i] = acc[i];
+    for (int i = 0; i < 4; ++i) row[8 + i] = scal[i];
+    row[12] = theta[6]; row[13] = theta[4]; row[14] = theta[5]; row[15] = theta[3];
+  }
+  theta[7] = (double)(r + 1);
+  double pi = theta[4], sigma = theta[5];
+  if (learn_pi) pi = scal[1];
+  if (learn_sigma) sigma = scal[2] == scal[2] ? scal[2] : 0.0;  // NaN root of a negative statistic: clamped below
+  if (pi < pi_lo) pi = pi_lo;                                   // check_params (_models.py:102-159)
+  if (pi >= pi_hi) pi = pi_hi;
+  if (sigma < sigma_lo) sigma = sigma_lo;
+  if (sigma >= sigma_hi) sigma = sigma_hi;
+  theta[4] = pi; theta[5] = sigma;
+  theta[0] = -1.0 / 2.0 / sigma / sigma;                         // E_step_precompute (bsc.py:100-125)
+  theta[1] = log(pi / (1.0 - pi));
+  theta[2] = pi * (double)H;
+  theta[6] = (double)H * log(1.0 - pi) - (double)D / 2.0 * log(2.0 * 3.14159265358979323846 * sigma * sigma);
+  theta[3] += 1.0;
+}
+
+extern "C" int evo_bsc_em_advance(const double *acc, const double *scal, double *theta_dev, double *rec, int max_rec, int D,
+                                  int H, int learn_pi, int learn_sigma, double pi_lo, double pi_hi, double sigma_lo,
+                                  double sigma_hi, void *stream) {
+  EVO_REQUIRE(acc && scal && theta_dev && D > 0 && H > 0, "bad arguments");
+  bsc_em_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(acc, scal, theta_dev, rec, max_rec, D, H, learn_pi, learn_sigma, pi_lo,
+                                                           pi_hi, sigma_lo, sigma_hi);
+  EVO_LAUNCH_CHECK("bsc_em_advance");
   return EVO_OK;
 }
 

@@ -27,7 +27,7 @@ struct WpLists {
 // the statistics pass (bsc.cu); lists select where <s>_n goes (all null: straight to Wp by atomics)
 int bsc_suffstats_pass1(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H, int S,
                         int S_perm, double pre1, double pil_bar, double *stats, float *Es_out, WpLists lists,
-                        cudaStream_t st, const int32_t *n_list = nullptr);
+                        cudaStream_t st, const int32_t *n_list = nullptr, const double *theta_dev = nullptr);
 
 // the <s> planes of a tensor-core Wp workspace (dense.cu geometry): et_hi / et_lo / et_ld of `out`
 int wp_tc_planes(void *workspace, int64_t N, int D, int H, WpLists *out);

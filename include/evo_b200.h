@@ -152,6 +152,10 @@ typedef struct evo_estep_args {
   double *fs_stats;
   void *fs_wp_workspace;
   int32_t *fs_rest;
+  /* CUDA-GRAPH REPLAY (optional, BSC evaluators).  NULL: the scalars above are used.  Otherwise the kernels read
+   * pre1, pil_bar, sparseness and iteration from theta_dev[0..3] (device memory, written by evo_bsc_em_advance), so a
+   * captured launch stays valid while the parameters change from iteration to iteration. */
+  const double *theta_dev;
 } evo_estep_args;
 int evo_estep(const evo_estep_args *args, void *stream);
 
@@ -227,11 +231,12 @@ int evo_bsc_suffstats_tc(const uint32_t *states, const double *lpj, const float 
                          void *workspace, void *stream);
 /* The two halves of evo_bsc_suffstats_tc around a fused E-step (evo_estep_args.fs_*): `begin` clears the <s> planes of
  * the workspace BEFORE evo_estep; `finish` adds the statistics of the datapoints listed in `rest` ([0] = count; NULL =
- * all N) and runs the split-K Wp GEMM. */
+ * all N) and runs the split-K Wp GEMM.  theta_dev != NULL: pre1 / pil_bar are read from theta_dev[0..1] on the device
+ * (CUDA-graph replay, see evo_bsc_em_advance) and the two arguments are ignored. */
 int evo_bsc_wp_tc_begin(int64_t N, int D, int H, void *workspace, void *stream);
 int evo_bsc_suffstats_tc_finish(const uint32_t *states, const double *lpj, const float *Ym, int64_t N, int D, int H,
                                 int S, int S_perm, double pre1, double pil_bar, double *stats, void *workspace,
-                                const int32_t *rest, void *stream);
+                                const int32_t *rest, const double *theta_dev, void *stream);
 /* y_rec[n][d] = sum_h <s_h>_n W[d][h] where recon_mask[n][d] == 0 (x false); other entries copy y;
  * rows whose infer_mask is all zero are left untouched (_models.py:646-648). */
 int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double *W, const float *Y,
@@ -252,6 +257,16 @@ int evo_bsc_reconstruct(const uint32_t *states, const double *lpj, const double 
 int64_t evo_bsc_solve_workspace_bytes(int D, int H);
 int evo_bsc_solve(const double *stats, double N_total, int D, int H, int learn_W, int background, double n_obs_total,
                   double sigma_old, double *W, double *pies, double *scal, void *workspace, void *stream);
+/* evo_bsc_em_advance -- the host's share of BSC.step between two iterations, on the device, so that a whole EM
+ * iteration can be captured in ONE CUDA graph and replayed without a host round trip: logs the iteration that just ran
+ * into rec[r][16] = {acc[8] (reduced E-step scalars), scal[4] (evo_bsc_solve), ljc, pi, sigma, iteration}, r = theta_dev[7]
+ * (rows beyond max_rec are dropped; rec may be NULL), then applies check_params (_models.py:102-159: lo <= v, v >= hi -> hi)
+ * to the new pi / sigma (scal[1], scal[2]; kept when not learned) and E_step_precompute (bsc.py:100-125):
+ *   theta_dev[8] = {pre1, pil_bar, piH, iteration + 1, pi, sigma, ljc, r + 1}
+ * which evo_estep (evo_estep_args.theta_dev) and evo_bsc_suffstats_tc_finish read.  Complete data only. */
+int evo_bsc_em_advance(const double *acc, const double *scal, double *theta_dev, double *rec, int max_rec, int D, int H,
+                       int learn_pi, int learn_sigma, double pi_lo, double pi_hi, double sigma_lo, double sigma_hi,
+                       void *stream);
 /* evo_bsc_solve_static -- NO counterpart in the reference: added for callers
  * that cannot allocate device memory (CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).
  * Same arguments, outputs and error behaviour as evo_bsc_solve without the workspace: the elimination scratch is a
