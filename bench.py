@@ -424,6 +424,32 @@ def timed_window(job, steps, barrier, sampler=None):
             "launches": int(lib.evo_launch_count() - l0)}
 
 
+def graph_window(job, steps, barrier, warm=3):
+    """The same EM iterations as ONE replayed CUDA graph per iteration (evo_b200/emgraph.py; BSC, complete data): `warm`
+    iterations (1 eager, capture, replays), then `steps` replays between CUDA events, the run's single host read after."""
+    import torch
+
+    g = job.model.em_graph(job.theta, job.cont, job.data, max_iterations=warm + steps)
+    g.run(warm)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    F, _, _ = g.run(steps)
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=job.device)
+    if job.world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    lpj = float(g.records[:, 6].sum())
+    job.theta = g.theta_out()
+    job.iters_done += warm + steps
+    return {"steps": steps, "warmup": warm, "after_iterations": job.iters_done - steps, "ms_per_step": ms / steps,
+            "value": lpj / (ms * 1e-3), "unit": UNIT, "em_iters_per_sec": steps / (ms * 1e-3), "free_energy": F[-1],
+            "host_reads": 1, "note": "one CUDA graph replay per EM iteration, scalars and logging on the device"}
+
+
 def roofline_of(job, win, peak, peak_src, fma=None):
     """`roofline` of the dominant call: algorithmic bytes / its mean CUDA-event duration / measured HBM
     peak; for the ES3C E-step also the algorithmic flops against the measured FMA peaks (bound = max of the two)."""
@@ -591,6 +617,14 @@ def run_ours(args):
                  for k, v in th_host.items()}
     del Yh, hdata
 
+    # ---- the SAME iterations (fresh job, same warm-up) with one replayed CUDA graph per EM iteration --------------
+    graph_rec = None
+    if world == 1 and w["model"] == "bsc" and not w.get("missing") and args.stats in ("tc", "auto") and not args.no_graph:
+        jg = Job(name, N_total, args, rank, world, device, comm)
+        graph_rec = graph_window(jg, args.steps, barrier, warm=max(args.warmup, 3))
+        del jg
+        torch.cuda.empty_cache()
+
     # ---- converged window: the E-step gets dearer as the states densify ----------
     at_density = None
     if args.density_iters > 0:
@@ -616,6 +650,11 @@ def run_ours(args):
                            "dtype": dtype_string(j2.w, args), "kernels": kernels_record(w2),
                            "roofline": roofline_of(j2, w2, peak, peak_src, fma), "gpu_launches": w2["launches"]}
             del j2
+            if WORKLOADS[other]["model"] == "bsc" and not WORKLOADS[other].get("missing") and args.stats in ("tc", "auto") \
+                    and not args.no_graph:
+                j3 = Job(other, WORKLOADS[other]["N"], args, rank, world, device, comm)  # fresh: the same iterations
+                also[other]["graph"] = graph_window(j3, 200 if other == "cfg1" else 3, barrier)
+                del j3
 
     if rank != 0:
         if world > 1:
@@ -634,7 +673,7 @@ def run_ours(args):
         "gpu_launches": win["launches"],
         "kernels": kernels_record(win),
         "roofline": roof, "comm": comm_rec, "clocks": clocks, "at_density": at_density,
-        "fma_peak_TFLOPs": fma, "also": also,
+        "fma_peak_TFLOPs": fma, "graph": graph_rec, "also": also,
     }
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_arm(name, steps=1, warmup=1)
@@ -779,6 +818,7 @@ def main():
     ap.add_argument("--n", type=int, default=0, help="datapoints IN TOTAL over all GPUs (default: the workload's N)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-also", action="store_true", help="skip the short sub-records of the other workloads")
+    ap.add_argument("--no-graph", action="store_true", help="skip the CUDA-graph replay windows")
     ap.add_argument("--density-iters", type=int, default=40,
                     help="also time a window after this many EM iterations (0 = off): states are denser by then")
     ap.add_argument("--tables", default="tc", choices=["tc", "f64"],

@@ -116,7 +116,7 @@ class EMGraph:
         for i, k in enumerate(("reset_lpj_isnan", "reset_lpj_smaller_eps_lpj", "reset_lpj_isinf")):
             dict.__setitem__(self.ss, k, int(rec[-1, 3 + i]))
         self.model.last_counts = {"lpj_evaluated": float(rec[-1, 6])}
-        self.last = rec[-1]
+        self.last, self.records = rec[-1], rec
         return F, (rec[:, 1] / N_total).tolist(), (rec[:, 2] / N_total).tolist()
 
     def theta_out(self):

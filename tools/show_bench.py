@@ -19,7 +19,11 @@ for f in sys.argv[1:]:
     if ad:
         print(" at_density ms %.2f act %.2f" % (ad["ms_per_step"], ad["mean_active_latents_per_state"]),
               {k: round(v["mean_ms"], 3) for k, v in ad["kernels"].items()})
+    if d.get("graph"):
+        print(" graph ms %.3f it/s %.1f" % (d["graph"]["ms_per_step"], d["graph"]["em_iters_per_sec"]))
     for k, v in (d.get("also") or {}).items():
+        if v.get("graph"):
+            print("  also", k, "graph ms %.3f it/s %.1f" % (v["graph"]["ms_per_step"], v["graph"]["em_iters_per_sec"]))
         print("  also", k, "ms %.2f value %.3g" % (v["ms_per_step"], v["value"]), {kk: round(vv["mean_ms"], 2) for kk, vv in v["kernels"].items()},
               "roof", round(v["roofline"]["frac"], 4) if v["roofline"] else None)
     if "cpu_baseline" in d:
