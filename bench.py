@@ -619,7 +619,7 @@ def run_ours(args):
 
     # ---- the SAME iterations (fresh job, same warm-up) with one replayed CUDA graph per EM iteration --------------
     graph_rec = None
-    if world == 1 and w["model"] == "bsc" and not w.get("missing") and args.stats in ("tc", "auto") and not args.no_graph:
+    if w["model"] == "bsc" and not w.get("missing") and args.stats in ("tc", "auto") and not args.no_graph:
         jg = Job(name, N_total, args, rank, world, device, comm)
         graph_rec = graph_window(jg, args.steps, barrier, warm=max(args.warmup, 3))
         del jg

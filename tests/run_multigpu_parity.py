@@ -62,6 +62,42 @@ def main():
             print("%s world=%d: K sets identical=%s  F rel err=%.2e  W rel err=%.2e" % (model_name, world, same, ferr, werr))
             ok &= same and ferr < 1e-10 and werr < 1e-8
         dist.barrier()
+    # ---- CUDA-graph replay with the NCCL all-reduce captured inside (evo_b200/emgraph.py) against step-by-step ----
+    from evo_b200.bsc import BSC
+    from evo_b200.variational import init_states
+
+    rng = np.random.RandomState(5)
+    N, D, H, K, iters = 2001, 24, 40, 16, 6
+    Wg = rng.normal(size=(D, H)) * 2
+    s = rng.rand(N, H) < 3.0 / H
+    Y = (s @ Wg.T + rng.normal(size=(N, D))).astype(np.float32)
+    lo, hi = shard_bounds(N, world, rank)
+    res = []
+    for use_graph in (False, True):
+        m = BSC(D, H, K, comm=Comm(), device=device)
+        m.tables = m.stats = "tc"
+        data = {"y": torch.as_tensor(Y[lo:hi], device=device), "x_infr": None}
+        cont = init_states(hi - lo, K, H, "fit", "randflip", 4, 3, 2, device=device, seed=7, n_offset=lo)
+        th = {"W": np.random.RandomState(9).normal(size=(D, H)), "pi": 0.1, "sigma": 1.5}
+        if use_graph:
+            g = m.em_graph(th, cont, data)
+            Fs, _, _ = g.run(iters)
+            th = g.theta_out()
+        else:
+            Fs = []
+            for _ in range(iters):
+                F, _, _, th = m.step(th, cont, data)
+                Fs.append(F)
+        res.append((np.array(Fs), cont["ss_dev"].cpu().numpy(), np.asarray(th["W"])))
+    same = np.array_equal(res[0][1], res[1][1])
+    ferr = float(np.max(np.abs(res[0][0] - res[1][0]) / np.abs(res[0][0])))
+    werr = float(np.abs(res[0][2] - res[1][2]).max() / np.abs(res[0][2]).max())
+    flags = torch.tensor([int(same and ferr < 1e-8 and werr < 1e-6)], device=device)
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("bsc graph replay world=%d: K sets identical=%s  F rel err=%.2e  W rel err=%.2e  all ranks ok=%d"
+              % (world, same, ferr, werr, int(flags.item())))
+        ok &= bool(flags.item())
     if rank == 0:
         print("MULTIGPU_PARITY", "OK" if ok else "FAIL")
     dist.destroy_process_group()
