@@ -463,6 +463,9 @@ def roofline_of(job, win, peak, peak_src, fma=None):
     roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
             "traffic": (NCU_TRAFFIC.get("%s:%d" % (job.name, job.N), {}) or {}).get(dom), "peak_source": peak_src,
             "launch_ms": kern[dom][1], "algorithmic_bytes_per_launch": alg[dom]}
+    if dom == "evo_estep" and "evo_bsc_suffstats_tc_finish" in kern:
+        roof["note"] = ("evo_estep also forms the M-step statistics of its datapoints in its tail (fs_*): its duration covers "
+                        "rows a'+c AND most of row d of SURVEY 8(d); the bytes counted are rows a'+c only")
     wi = ((NCU_TRAFFIC.get("%s:%d" % (job.name, job.N), {}) or {}).get("warp_inst") or {}).get(dom)
     if wi:
         # the kernel is bound by instruction issue, not by HBM: warp instructions per launch (ncu, same command) against

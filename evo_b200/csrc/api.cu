@@ -194,10 +194,12 @@ static int estep_impl(const evo_estep_args *x, const evo_evolve_args *t, void *s
     EVO_REQUIRE(x->G && x->B && x->ynorm2, "gram evaluator needs G, B, ynorm2");
     EVO_REQUIRE(x->mask == nullptr, "gram evaluator needs complete data");
     BscGramEval ev{x->G, x->B, x->ynorm2, x->pre1, x->pil_bar, dv.H, dv.Hw, nullptr, nullptr, 0.0};
+    ev.theta = x->theta_dev;
     return launch_estep_any(dv, ev, st);
   } else if (x->eval == EVO_EVAL_BSC_DIRECT) {
     EVO_REQUIRE(x->W && x->Y, "direct evaluator needs W, Y");
     BscDirectEval ev{x->W, x->Y, x->mask, x->pre1, x->pil_bar, dv.D, dv.H, dv.Hw, nullptr, nullptr, 0.0};
+    ev.theta = x->theta_dev;
     return launch_estep_any(dv, ev, st);
   } else if (x->eval == EVO_EVAL_ES3C) {
     return es3c_launch_estep(dv, x, st);

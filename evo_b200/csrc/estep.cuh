@@ -58,19 +58,10 @@ struct EstepDev {
   uint32_t mask_c, mask_s, mask_p;  // index-code masks (pow2 - 1) for Ctot, S, PK (order_key)
 };
 
-// theta_dev overrides the scalars that were kernel arguments (BSC evaluators; other evaluators have none)
-__device__ __forceinline__ void theta_set(BscGramEval &ev, const double *t) { ev.pre1 = t[0]; ev.pil_bar = t[1]; }
-__device__ __forceinline__ void theta_set(BscDirectEval &ev, const double *t) { ev.pre1 = t[0]; ev.pil_bar = t[1]; }
-template <class Eval>
-__device__ __forceinline__ void theta_set(Eval &, const double *) {}
-template <class Eval>
-__device__ __forceinline__ void theta_override(EstepDev &a, Eval &ev) {
-  if (a.theta_dev) {
-    theta_set(ev, a.theta_dev);
-    a.sparseness = a.theta_dev[2];
-    a.iteration = (uint32_t)a.theta_dev[3];
-  }
-}
+// CUDA-graph replay: the per-iteration scalars are re-read from device memory at their points of use (theta_dev NULL: the
+// kernel arguments; the BSC evaluators do the same for pre1 / pil_bar).  The argument structs are never written.
+__device__ __forceinline__ uint32_t th_iteration(const EstepDev &a) { return a.theta_dev ? (uint32_t)a.theta_dev[3] : a.iteration; }
+__device__ __forceinline__ double th_sparseness(const EstepDev &a) { return a.theta_dev ? a.theta_dev[2] : a.sparseness; }
 
 constexpr int TAG_EMPTY = -1;
 constexpr int TAG_CHILD = 1 << 24;
@@ -383,7 +374,6 @@ template <class Eval, int T, bool FAST = false, bool LIST = false>
 __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   EstepSmem s;
-  theta_override(a, ev);
   estep_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
   const int Hw = LIST ? LIST_WORDS : a.Hr, Hg = a.Hw, Hs = LIST ? LIST_WORDS + 1 : a.Hs, S = a.S;  // Hw: words of a shared-memory row, Hg: of a global row
@@ -395,7 +385,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
   const int64_t n_total = a.n_list ? (int64_t)a.n_list[0] : a.N;
   for (int64_t it = blockIdx.x; it < n_total; it += gridDim.x) {
     const int64_t n = a.n_list ? (int64_t)a.n_list[1 + it] : it;
-    RngCtx rng(a.seed, a.n_offset + n, a.iteration);
+    RngCtx rng(a.seed, a.n_offset + n, th_iteration(a));
     gsync<T>();  // previous datapoint fully done with shared memory
     // ---- load K^n, evaluator tables ---------------------------------------------------------
     {
@@ -501,7 +491,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
             if (bgu) dst[(a.H - 1) >> 5] &= ~(1u << ((a.H - 1) & 31));
             if (LIST) { if (!list_toggle(dst, s.slot[c])) s.sh[0] = 1; }
             else if (FAST || mut == EVO_MUT_RANDFLIP) flip_bit(dst, s.slot[c]);
-            else sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_MUTATE, gr, (uint32_t)c);
+            else sparseflip_state(dst, Hm, th_sparseness(a), a.p_bf, rng, RNG_MUTATE, gr, (uint32_t)c);
             if (bgu) dst[(a.H - 1) >> 5] |= 1u << ((a.H - 1) & 31);
             if (!FAST && a.tr_pos) {
               int32_t *tp = a.tr_pos + ((n * (int64_t)a.n_generations + g) * a.Cg + c) * 2;
@@ -537,7 +527,7 @@ __global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
                 fp = (int)urange(r2.x, (uint32_t)Hm);
                 flip_bit(dst, fp);
               } else if (mut == EVO_MUT_CROSS_SPARSEFLIP) {
-                sparseflip_state(dst, Hm, a.sparseness, a.p_bf, rng, RNG_FLIP2, gr, cidx);
+                sparseflip_state(dst, Hm, th_sparseness(a), a.p_bf, rng, RNG_FLIP2, gr, cidx);
               }
               if (a.tr_pos) {
                 int32_t *tp = a.tr_pos + ((n * (int64_t)a.n_generations + g) * a.Cg + cidx) * 2;

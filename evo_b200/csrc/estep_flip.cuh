@@ -277,9 +277,9 @@ __device__ __forceinline__ double flip_fused_stats(const EstepDev &a, const Flip
       const uint16_t *e = reinterpret_cast<const uint16_t *>(frow[k] >= 0 ? scr + (size_t)frow[k] * FL_STRIDE : s.rows + (size_t)k * FL_STRIDE);
       const int na = e[31];
       for (int x = 0; x < na; ++x) atomicOr(&ubm[e[x] >> 5], 1u << (e[x] & 31));
-      sg += qk * (s.lpj[k] - ev.pil_bar * (double)na) / ev.pre1;
+      sg += qk * (s.lpj[k] - ev.pil_bar_now() * (double)na) / ev.pre1_now();
     }
-    if (a.S_perm > 0 && tid == 0) sg += exp(lpj_perm - mx) * inv * lpj_perm / ev.pre1;  // all-zero state: |y|^2
+    if (a.S_perm > 0 && tid == 0) sg += exp(lpj_perm - mx) * inv * lpj_perm / ev.pre1_now();  // all-zero state: |y|^2
   }
   gsync<T>();
   // ---- ascending list of the union (warp 0) -----------------------------------------------------------------------------------
@@ -343,7 +343,6 @@ template <int T>
 __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval ev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FlipSmem s;
-  theta_override(a, ev);
   flip_carve(a, smem_raw, &s);
   const int tid = threadIdx.x;
   const int Hg = a.Hw, S = a.S, Hm = a.H, C = a.n_children;
@@ -351,7 +350,7 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
   unsigned long long cnt_nan = 0, cnt_small = 0, cnt_inf = 0;
 
   for (int64_t n = blockIdx.x; n < a.N; n += gridDim.x) {
-    RngCtx rng(a.seed, a.n_offset + n, a.iteration);
+    RngCtx rng(a.seed, a.n_offset + n, th_iteration(a));
     const double *bg = ev.B + n * (int64_t)ev.H;
     const double yn2 = __ldg(ev.ynorm2 + n);
     gsync<T>();  // previous datapoint fully done with shared memory
@@ -395,7 +394,7 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
         sg += __ldg(Gr + h) + 2.0 * t;
       }
       s.sb[i] = sb; s.sg[i] = sg; s.hash[i] = hs; s.cnt[i] = (unsigned char)na;
-      s.lpj[i] = lpj_sanitise(__fma_rn(ev.pre1, __dadd_rn(__fma_rn(-2.0, sb, yn2), sg), __dmul_rn(ev.pil_bar, (double)na)), fl0);
+      s.lpj[i] = lpj_sanitise(__fma_rn(ev.pre1_now(), __dadd_rn(__fma_rn(-2.0, sb, yn2), sg), __dmul_rn(ev.pil_bar_now(), (double)na)), fl0);
       s.pool[i] = i;
     }
     fl0 = group_or<T>(fl0, s.red_i);
@@ -403,7 +402,7 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
     double lpj_perm = 0.0;
     if (a.S_perm > 0) {
       unsigned f0 = 0;
-      lpj_perm = lpj_sanitise(ev.pre1 * yn2, f0);
+      lpj_perm = lpj_sanitise(ev.pre1_now() * yn2, f0);
       if (tid == 0 && f0) { if (f0 & 1) ++cnt_nan; else if (f0 & 2) ++cnt_small; else ++cnt_inf; }
     }
     gsync<T>();
@@ -479,7 +478,7 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
         s.hash[idx] = present ? s.hash[pu] - mix_latent((uint32_t)pos) : s.hash[pu] + mix_latent((uint32_t)pos);
         s.nw_par[idx - S] = (uint16_t)prow; s.nw_pos[idx - S] = (uint16_t)pos;
         unsigned f1 = 0;
-        s.lpj[idx] = lpj_sanitise(__fma_rn(ev.pre1, __dadd_rn(__fma_rn(-2.0, sb, yn2), sg), __dmul_rn(ev.pil_bar, (double)nn)), f1);
+        s.lpj[idx] = lpj_sanitise(__fma_rn(ev.pre1_now(), __dadd_rn(__fma_rn(-2.0, sb, yn2), sg), __dmul_rn(ev.pil_bar_now(), (double)nn)), f1);
         if (a.S_perm > 0 && nn == 0) stt = 0;  // the permanent all-zero state
         s.status[c] = stt ? (unsigned char)(1u | (f1 << 4)) : 0;  // reset flags ride along: only new unique states count
       }

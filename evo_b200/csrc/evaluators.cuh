@@ -25,6 +25,9 @@ struct BscGramEval {
   uint16_t *idx;   // smem [MAXA][T] active-latent lists, one column per thread
   double yn2;
   const double *bg;  // this datapoint's row of B in global memory (the list form reads it through L1/L2)
+  const double *theta;  // CUDA-graph replay: pre1 / pil_bar are re-read from theta[0..1] (device memory); NULL = the members
+  __device__ __forceinline__ double pre1_now() const { return theta ? theta[0] : pre1; }
+  __device__ __forceinline__ double pil_bar_now() const { return theta ? theta[1] : pil_bar; }
   static constexpr int MAXA = 24;
   static constexpr bool kList = true;  // can evaluate index-list rows (estep.cuh LIST representation)
 
@@ -49,7 +52,7 @@ struct BscGramEval {
   // pre1 (|y|^2 - 2 sum b + sum G) + pil_bar |s| with the contraction spelled out, so that every
   // evaluation form (bits, scratch lists, list rows) rounds alike
   __device__ __forceinline__ double combine(double sb, double sg, int a) const {
-    return __fma_rn(pre1, __dadd_rn(__fma_rn(-2.0, sb, yn2), sg), __dmul_rn(pil_bar, (double)a));
+    return __fma_rn(pre1_now(), __dadd_rn(__fma_rn(-2.0, sb, yn2), sg), __dmul_rn(pil_bar_now(), (double)a));
   }
 
   // generic form: any number of active latents, no scratch
@@ -131,7 +134,7 @@ struct BscGramEval {
     for (int i = threadIdx.x; i < cnt; i += T)
       out[i] = lpj_sanitise(LIST ? eval_list(st + (size_t)i * ld) : eval_one<T>(st + (size_t)i * ld), flags);
   }
-  __device__ double eval_zero(unsigned &flags) const { return lpj_sanitise(pre1 * yn2, flags); }
+  __device__ double eval_zero(unsigned &flags) const { return lpj_sanitise(pre1_now() * yn2, flags); }
 };
 
 // ------------------------------------------------------------------------------------------
@@ -148,6 +151,9 @@ struct BscDirectEval {
   double *y;       // smem [D]  (0 where masked)
   uint8_t *m;      // smem [D]
   double yn2;
+  const double *theta;  // as in BscGramEval
+  __device__ __forceinline__ double pre1_now() const { return theta ? theta[0] : pre1; }
+  __device__ __forceinline__ double pil_bar_now() const { return theta ? theta[1] : pil_bar; }
 
   static constexpr bool kList = false;
   __host__ __device__ size_t smem_bytes(int, bool = false) const { return (size_t)D * sizeof(double) + (((size_t)D + 7) & ~(size_t)7); }
@@ -181,7 +187,7 @@ struct BscDirectEval {
       double r = mean - y[d];
       resid += r * r;
     }
-    return pre1 * resid + pil_bar * (double)popc_state(st, Hw);
+    return pre1_now() * resid + pil_bar_now() * (double)popc_state(st, Hw);
   }
 
   template <int T, bool LIST = false>
@@ -191,7 +197,7 @@ struct BscDirectEval {
   __device__ double eval_zero(unsigned &flags) const {
     double s = 0.0;
     for (int d = 0; d < D; ++d) s += y[d] * y[d];
-    return lpj_sanitise(pre1 * s, flags);
+    return lpj_sanitise(pre1_now() * s, flags);
   }
 };
 
