@@ -33,8 +33,12 @@ __global__ void unpack_kernel(const uint32_t *__restrict__ packed, uint8_t *__re
 // S distinct Bernoulli(p) states per datapoint, none equal to the permanent all-zero state when
 // S_perm > 0; with a background unit the last latent is always on (utils.py:96-138).  One warp per
 // datapoint; a state is redrawn until it differs from all earlier ones of that datapoint.
+// `use_hash`: a 64-bit hash of every accepted state of the warp's datapoint is kept in shared memory and the words are
+// compared only on a hash match (same accept / reject decisions as the plain word compare, S^2 Hw / 2 fewer loads).
 __global__ void init_states_kernel(uint32_t *__restrict__ states, int64_t N, int S, int H, int Hw, int S_perm,
-                                   int background, double p, uint64_t seed, int64_t n_offset) {
+                                   int background, double p, uint64_t seed, int64_t n_offset, int use_hash) {
+  extern __shared__ unsigned long long hash_sm[];  // [warps per block][S]
+  unsigned long long *hk = hash_sm + (size_t)(threadIdx.x >> 5) * S;
   int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -46,6 +50,7 @@ __global__ void init_states_kernel(uint32_t *__restrict__ states, int64_t N, int
     uint32_t attempt = 0;
     for (int k = 0; k < S;) {
       // lanes build the words of candidate state k cooperatively
+      unsigned long long hv = 0;
       for (int w = lane; w < Hw; w += 32) {
         uint32_t word = 0;
         for (int q = 0; q < 8; ++q) {
@@ -58,7 +63,11 @@ __global__ void init_states_kernel(uint32_t *__restrict__ states, int64_t N, int
         }
         if (background && ((H - 1) >> 5) == w) word |= 1u << ((H - 1) & 31);
         base[(int64_t)k * Hw + w] = word;
+        hv += ((unsigned long long)word + 1ull) * (0x9E3779B97F4A7C15ull + 2ull * (unsigned long long)w);
       }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) hv += __shfl_xor_sync(0xffffffffu, hv, o);
+      hv ^= hv >> 29;
       __syncwarp();
       ++attempt;
       // reject duplicates / permanent state
@@ -69,13 +78,17 @@ __global__ void init_states_kernel(uint32_t *__restrict__ states, int64_t N, int
         bad = !__any_sync(0xffffffffu, nz);
       }
       for (int j = lane; j < k && !bad; j += 32) {
+        if (use_hash && hk[j] != hv) continue;
         bool same = true;
         for (int w = 0; w < Hw; ++w) same &= (base[(int64_t)j * Hw + w] == base[(int64_t)k * Hw + w]);
         if (same) bad = true;
       }
       bad = __any_sync(0xffffffffu, bad);
       // with p tiny and S large the space of likely states is small; raise p after many failures
-      if (!bad) ++k;
+      if (!bad) {
+        if (use_hash && lane == 0) hk[k] = hv;
+        ++k;
+      }
       __syncwarp();
     }
   }
@@ -118,7 +131,10 @@ extern "C" int evo_states_init(uint32_t *states, int64_t N, int S, int H, int S_
   int Hw = words_for(H);
   int64_t warps = N;
   int blocks = (int)((warps * 32 + 127) / 128 < (int64_t)sm_count() * 16 ? (warps * 32 + 127) / 128 : (int64_t)sm_count() * 16);
-  init_states_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(states, N, S, H, Hw, S_perm, background, p, seed, n_offset);
+  const size_t hbytes = (size_t)4 * S * sizeof(unsigned long long);
+  const int use_hash = hbytes <= 48 * 1024;
+  init_states_kernel<<<blocks, 128, use_hash ? hbytes : 0, (cudaStream_t)stream>>>(states, N, S, H, Hw, S_perm, background, p, seed,
+                                                                                  n_offset, use_hash);
   EVO_LAUNCH_CHECK("init_states");
   return EVO_OK;
 }
