@@ -382,7 +382,13 @@ class Job:
     def step(self):
         F, nu, nsub, self.theta = self.model.step(self.theta, self.cont, self.data, do_reconstruction=self.recon)
         self.iters_done += 1
+        self.last_sub = nsub
         return F, nu, self.model.last_counts["lpj_evaluated"]
+
+    def fused_rest_fraction(self):
+        """share of this shard's datapoints whose statistics the fused E-step tail handed to the separate pass (last step)"""
+        r = self.model.device_data(self.data).cache.get("fs_rest")
+        return None if r is None else float(r[0].item()) / max(1, self.N)
 
     def mean_active(self, sample=2000):
         """mean |s|, |s|^2, |s|^3 over the K sets of the first datapoints of the shard"""
@@ -421,7 +427,8 @@ def timed_window(job, steps, barrier, sampler=None):
     kern = job.model.timing_summary()
     job.model.timing = None
     return {"ms": float(ms.item()), "lpj": lpj_total, "U_mean": U_sum / steps, "F": F, "kern": kern,
-            "launches": int(lib.evo_launch_count() - l0)}
+            "launches": int(lib.evo_launch_count() - l0), "sub": getattr(job, "last_sub", None),
+            "rest": job.fused_rest_fraction()}
 
 
 def graph_window(job, steps, barrier, warm=3):
@@ -637,7 +644,8 @@ def run_ours(args):
         win2 = timed_window(job, k2, barrier)
         at_density = {"after_iterations": job.iters_done - k2, "steps": k2, "ms_per_step": win2["ms"] / k2,
                       "value": win2["lpj"] / (win2["ms"] * 1e-3), "mean_active_latents_per_state": job.mean_active()[0],
-                      "free_energy": win2["F"], "kernels": kernels_record(win2)}
+                      "free_energy": win2["F"], "kernels": kernels_record(win2),
+                      "substituted_per_datapoint": win2["sub"], "fused_statistics_rest_fraction": win2["rest"]}
 
     # ---- short sub-records of the other single-GPU workloads (N = 1 only) -------------------------------------
     also = {}
@@ -671,6 +679,7 @@ def run_ours(args):
         "em_iters_per_sec": args.steps / (ms * 1e-3),
         "lpj_per_step": lpj_total / args.steps, "new_unique_per_datapoint": win["U_mean"], "free_energy": F,
         "mean_active_latents_per_state": act_timed,
+        "substituted_per_datapoint": win["sub"], "fused_statistics_rest_fraction": win["rest"],
         "e2e": {"value": e2e_lpj / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": win["launches"],

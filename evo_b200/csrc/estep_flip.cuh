@@ -9,8 +9,11 @@
 //   * every state carries its sums sb = sum_{h in s} b_h and sg = sum_{h,h' in s} G_hh' (lpj = pre1 (|y|^2 - 2 sb + sg)
 //     + pil_bar |s|), so a child costs O(|s|) loads: sb' = sb +- b_p, sg' = sg + G_pp +- 2 sum_{h in parent} G_ph
 //     instead of the O(|s|^2) walk of a fresh evaluation (K^n itself is evaluated in full: theta changed);
-//   * de-duplication hashes SETS: h(s) = sum_{h in s} mix(h) mod 2^64, so h(child) = h(parent) +- mix(p); a table hit
-//     on the 64-bit hash is always verified exactly (merge walk over the two parent lists).
+//   * de-duplication hashes SETS: h(s) = sum_{h in s} mix(h) mod 2^32, so h(child) = h(parent) +- mix(p); a table hit
+//     on the hash is always verified exactly (merge walk over the two parent lists);
+//   * shared memory per datapoint decides how many datapoints an SM holds (the kernel is latency-bound): arrays that
+//     are dead after the generations (sb, sg, hash) are reused by vary_Kn and by the fused statistics, and sb / sg are
+//     not kept for the children of the last generation.
 // Datapoints whose K^n or children need more than 31 active latents are handed, untouched, to the packed-bits kernel
 // through `ovf_list` (same protocol as before).  Results do not depend on which kernel handled a datapoint: K sets
 // bit-identical, lpj equal to the full evaluation within rounding (<= 1e-12 relative; tests/test_evolve_gpu.py chains
@@ -23,11 +26,14 @@ namespace evo {
 constexpr int FL_CAP = 31, FL_WORDS = 16, FL_STRIDE = 17;  // list row: 32 x uint16 (+ one pad word: conflict-free rows)
 
 struct FlipSmem {
-  double *lpj, *sb, *sg;     // [S + Ctot]
+  double *lpj;               // [S + Ctot]
+  double *sb, *sg;           // [S + Ctot - Cg]: the children of the LAST generation never become parents
   double *keys;              // [PK + 2] selection keys; later vkeys of vary_Kn
   double *vkeys;             // [Ctot + S + 2] (aliases the hash table)
   double *red_d;             // [8]
-  unsigned long long *hash;  // [S + Ctot]
+  uint32_t *hash;            // [S + Ctot] low half of the 64-bit set hash (additive mod 2^32; hits are verified exactly)
+  double *es_u;              // fused statistics: <s> over the union (in the dead table region, behind old_by_rank)
+  int es_cap;
   uint32_t *rows;            // [S + PB][FL_STRIDE]
   int *table;                // [HT]
   int *pool;                 // [PK]
@@ -52,21 +58,41 @@ __host__ __device__ inline size_t flip_carve(const EstepDev &a, unsigned char *b
     off = align16(off + sizeof(type) * (size_t)(count));          \
   } while (0)
   CARVE(lpj, double, U);
-  CARVE(sb, double, U);
-  CARVE(sg, double, U);
+  // [sb | sg | hash] are dead once the generations are over: vary_Kn's scratch (vkeys, rnk, eidx) aliases them when it
+  // fits, and the fused statistics carve their scratch rows from the same span
+  const size_t dead0 = off;
+  CARVE(sb, double, U - a.Cg);
+  CARVE(sg, double, U - a.Cg);
+  CARVE(hash, uint32_t, U);
+  const size_t dead1 = off;
   CARVE(keys, double, a.PK + 2);
   CARVE(red_d, double, 8);
-  CARVE(hash, unsigned long long, U);
   CARVE(rows, uint32_t, ((size_t)a.S + PB) * FL_STRIDE);
+  const size_t n_vk = (size_t)((a.Ctot + 1) & ~1) + a.S + 2, n_ct = a.Ctot > 0 ? a.Ctot : 1;
+  const bool alias = align16(sizeof(double) * n_vk) + 2 * align16(sizeof(int) * n_ct) <= dead1 - dead0;
+  if (alias) {
+    const size_t keep = off;
+    off = dead0;
+    CARVE(vkeys, double, n_vk);
+    CARVE(rnk, int, n_ct);
+    CARVE(eidx, int, n_ct);
+    off = keep;
+  }
   {
     const size_t base_off = off;
     CARVE(table, int, a.HT);
     const size_t end_gen = off;
     off = base_off;
-    CARVE(vkeys, double, (size_t)((a.Ctot + 1) & ~1) + a.S + 2);
-    CARVE(rnk, int, a.Ctot > 0 ? a.Ctot : 1);
+    if (!alias) {
+      CARVE(vkeys, double, n_vk);
+      CARVE(rnk, int, n_ct);
+      CARVE(eidx, int, n_ct);
+    }
     CARVE(old_by_rank, int, a.S);
-    CARVE(eidx, int, a.Ctot > 0 ? a.Ctot : 1);
+    if (s) {
+      s->es_u = reinterpret_cast<double *>(base + off);
+      s->es_cap = end_gen > off ? (int)((end_gen - off) / sizeof(double)) : 0;
+    }
     if (off < end_gen) off = end_gen;
   }
   CARVE(pool, int, a.PK);
@@ -207,7 +233,7 @@ __device__ __forceinline__ bool flip_equal(const FlipSmem &s, int S, int i, int 
 // concurrent insert of uniq index idx; equal states converge on one slot holding the smallest index.  Returns the slot.
 __device__ __forceinline__ int flip_insert(const EstepDev &a, const FlipSmem &s, int idx) {
   const uint32_t mask = (uint32_t)a.HT - 1u;
-  uint32_t p = (uint32_t)(s.hash[idx] >> 32) & mask;
+  uint32_t p = s.hash[idx] & mask;
   for (int it = 0; it < a.HT; ++it) {
     int cur = s.table[p];
     if (cur == TAG_EMPTY) {
@@ -235,14 +261,14 @@ template <int T>
 __device__ __forceinline__ double flip_fused_stats(const EstepDev &a, const FlipSmem &s, const BscGramEval &ev, int64_t n,
                                                    double mx, double se, double lpj_perm) {
   const int tid = threadIdx.x, S = a.S, Hw = a.Hw;
-  uint32_t *scr = reinterpret_cast<uint32_t *>(s.sb);  // sb, sg: dead after the generations
+  uint32_t *scr = reinterpret_cast<uint32_t *>(s.sb);  // sb, sg, hash (and vary_Kn's scratch over them): dead by now
   const int R = (int)((reinterpret_cast<unsigned char *>(s.keys) - reinterpret_cast<unsigned char *>(s.sb)) / (FL_STRIDE * 4));
   uint32_t *ubm = reinterpret_cast<uint32_t *>(s.keys);                        // union bitmap [Hw]
   const int keys_bytes = (a.PK + 2) * 8, bm_bytes = (4 * Hw + 7) & ~7;
   uint16_t *act = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(s.keys) + bm_bytes);
-  double *es_u = reinterpret_cast<double *>(s.hash);                           // [S + Ctot] doubles, dead too
+  double *es_u = s.es_u;                                                       // the dead hash-table region
   int capU = keys_bytes > bm_bytes ? (keys_bytes - bm_bytes) / 2 : 0;
-  if (capU > S + a.Ctot) capU = S + a.Ctot;
+  if (capU > s.es_cap) capU = s.es_cap;
   int *frow = s.old_by_rank;  // scratch row of a replaced slot, -1 = the slot's own row
   bool ok = capU >= 32;
   // ---- scratch rows for the replaced slots ----------------------------------------------------------------------------
@@ -382,10 +408,10 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
       const uint16_t *e = reinterpret_cast<const uint16_t *>(s.rows + (size_t)i * FL_STRIDE);
       const int na = e[31];
       double sb = 0.0, sg = 0.0;
-      uint64_t hs = 0;
+      uint32_t hs = 0;
       for (int x = 0; x < na; ++x) {
         const int h = e[x];
-        hs += mix_latent((uint32_t)h);
+        hs += (uint32_t)mix_latent((uint32_t)h);
         sb += __ldg(bg + h);
         const double *Gr = ev.G + (int64_t)h * ev.H;
         double t = 0.0;
@@ -452,6 +478,7 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
       }
       draw_flip_positions<T>(rng, (uint32_t)g, take, C, Hm, s.slot, s.red_i);
       const int nc = take * C;
+      const bool keep_sums = g + 1 < a.n_generations;  // only states that can still become parents need sb / sg
       // ---- children: implicit (parent row, position), sums and lpj from the parent's in O(|s|) ----------------------
       unsigned fl = 0;
       _Pragma("unroll 1") for (int c = tid; c < nc; c += T) {
@@ -474,8 +501,9 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
         const double gpp = __ldg(Gr + pos), bp = __ldg(bg + pos);
         const double sb = present ? s.sb[pu] - bp : s.sb[pu] + bp;
         const double sg = present ? (s.sg[pu] + gpp) - 2.0 * t : (s.sg[pu] + gpp) + 2.0 * t;
-        s.sb[idx] = sb; s.sg[idx] = sg; s.cnt[idx] = (unsigned char)nn;
-        s.hash[idx] = present ? s.hash[pu] - mix_latent((uint32_t)pos) : s.hash[pu] + mix_latent((uint32_t)pos);
+        if (keep_sums) { s.sb[idx] = sb; s.sg[idx] = sg; }
+        s.cnt[idx] = (unsigned char)nn;
+        s.hash[idx] = present ? s.hash[pu] - (uint32_t)mix_latent((uint32_t)pos) : s.hash[pu] + (uint32_t)mix_latent((uint32_t)pos);
         s.nw_par[idx - S] = (uint16_t)prow; s.nw_pos[idx - S] = (uint16_t)pos;
         unsigned f1 = 0;
         s.lpj[idx] = lpj_sanitise(__fma_rn(ev.pre1_now(), __dadd_rn(__fma_rn(-2.0, sb, yn2), sg), __dmul_rn(ev.pil_bar_now(), (double)nn)), f1);
@@ -497,18 +525,20 @@ __global__ void __launch_bounds__(T) estep_flip_kernel(EstepDev a, BscGramEval e
         if (c < nc && s.status[c] && owner >= 0 && owner < S + U) s.redisc[owner] = 1;  // reproduced an existing state
         // winners move down to S + U + u_g + off (<= their provisional place): read, barrier, write
         double v_l = 0, v_b = 0, v_g = 0;
-        unsigned long long v_h = 0;
+        uint32_t v_h = 0;
         unsigned v_pp = 0;
         unsigned char v_c = 0;
         if (win) { fl |= (unsigned)(s.status[c] >> 4);
-                   v_l = s.lpj[idx]; v_b = s.sb[idx]; v_g = s.sg[idx]; v_h = s.hash[idx]; v_c = s.cnt[idx];
+                   v_l = s.lpj[idx]; v_h = s.hash[idx]; v_c = s.cnt[idx];
+                   if (keep_sums) { v_b = s.sb[idx]; v_g = s.sg[idx]; }
                    v_pp = ((unsigned)s.nw_par[idx - S] << 16) | s.nw_pos[idx - S]; }
         int tot;
         const int off = group_scan_flag<T>(win, tot, s.red_i);
         gsync<T>();
         if (win) {
           const int dst = S + U + u_g + off;
-          s.lpj[dst] = v_l; s.sb[dst] = v_b; s.sg[dst] = v_g; s.hash[dst] = v_h; s.cnt[dst] = v_c;
+          s.lpj[dst] = v_l; s.hash[dst] = v_h; s.cnt[dst] = v_c;
+          if (keep_sums) { s.sb[dst] = v_b; s.sg[dst] = v_g; }
           s.nw_par[dst - S] = (uint16_t)(v_pp >> 16); s.nw_pos[dst - S] = (uint16_t)(v_pp & 0xFFFFu);
           s.table[sl] = dst;  // the entry follows its state
         }
