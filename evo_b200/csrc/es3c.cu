@@ -118,8 +118,17 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
     }
     __syncthreads();
     if (ev.masked == 1) ev.yn2 = ev.masked_yn2();
-    // ---- per-state moments, one warp per state -------------------------------------------------
     const uint32_t *stn = a.states + n * (int64_t)S * Hw;
+    // ---- per-state moments: states with <= SMALL_A active latents (most of a sparse model) by one THREAD each ... -----
+    if (ev.masked != 1) {
+      for (int k = threadIdx.x; k < S; k += T) {
+        const double qk = q[a.S_perm + k];
+        if (!(qk > a.q_skip)) continue;
+        if (ev.small_moments(stn + (int64_t)k * Hw, qk, xs, xsz, sum_ss, sum_szsz)) q[a.S_perm + k] = 0.0;  // done
+      }
+      __syncthreads();
+    }
+    // ---- ... the others by one warp each -------------------------------------------------------------------------------
     for (int k = warp; k < S; k += T / 32) {
       double qk = q[a.S_perm + k];
       if (!(qk > a.q_skip)) continue;

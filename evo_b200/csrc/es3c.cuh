@@ -565,6 +565,125 @@ struct Es3cEval {
     return -0.5 * (logdet + s2i * rn2 - wx) + prior;
   }
 
+  // Posterior moments of a state with at most SMALL_A active latents by ONE thread (the statistics pass, sssc.py:553-646):
+  // x = N^-1 v, kappa = Psi_A x + mu_A, Lambda = Psi_A N^-1 from the same N, v as small_lpj (LU with partial pivoting,
+  // unit padding), accumulated with weight qk into the per-datapoint vectors xs / xsz (shared memory) and the global
+  // pair sums sum_ss / sum_szsz.  Returns false (nothing done) for larger states.
+  __device__ __forceinline__ bool small_moments(const uint32_t *st, double qk, double *xs, double *xsz, double *sum_ss,
+                                                double *sum_szsz) const {
+    constexpr int MA = SMALL_A;
+    int hs[MA];
+    int a = 0;
+#pragma unroll
+    for (int i = 0; i < MA; ++i) hs[i] = 0;
+    for (int w = 0; w < Hw; ++w) {
+      uint32_t m = st[w];
+      while (m) {
+        const int h = (w << 5) + __ffs(m) - 1;
+        m &= m - 1;
+#pragma unroll
+        for (int i = 0; i < MA; ++i) if (i == a) hs[i] = h;
+        ++a;
+      }
+    }
+    if (a > MA) return false;
+    if (a == 0) return true;
+    double g[MA][MA], ps[MA][MA], mu[MA], b[MA];
+#pragma unroll
+    for (int i = 0; i < MA; ++i) {
+      const bool oi = i < a;
+      mu[i] = oi ? __ldg(mus + hs[i]) : 0.0;
+      b[i] = oi ? vec[hs[i]] : 0.0;
+#pragma unroll
+      for (int j = 0; j < MA; ++j) {
+        const bool on = oi && j < a;
+        ps[i][j] = on ? __ldg(Psi + (int64_t)hs[i] * H + hs[j]) : 0.0;
+        if (j <= i) {
+          double v = on ? __ldg(G + (int64_t)hs[i] * H + hs[j]) : 0.0;
+          if (on && masked == 2) v -= miss_corr(hs[i], hs[j]);
+          g[i][j] = v;
+          g[j][i] = v;
+        }
+      }
+    }
+    double v[MA], n[MA][MA], r[MA][MA];
+#pragma unroll
+    for (int i = 0; i < MA; ++i) {
+      double ti = 0.0;
+#pragma unroll
+      for (int l = 0; l < MA; ++l) ti += g[i][l] * mu[l];
+      v[i] = s2i * (b[i] - ti);
+#pragma unroll
+      for (int j = 0; j < MA; ++j) {
+        double acc = 0.0;
+#pragma unroll
+        for (int l = 0; l < MA; ++l) acc += g[i][l] * ps[l][j];
+        n[i][j] = (i == j ? 1.0 : 0.0) + s2i * acc;
+        r[i][j] = (i == j ? 1.0 : 0.0);
+      }
+    }
+    // Gauss-Jordan with partial pivoting on [N | I | v]
+#pragma unroll
+    for (int k = 0; k < MA; ++k) {
+      int p = k;
+      double best = fabs(n[k][k]);
+#pragma unroll
+      for (int i = k + 1; i < MA; ++i) { const double m2 = fabs(n[i][k]); if (m2 > best) { best = m2; p = i; } }
+#pragma unroll
+      for (int i = k + 1; i < MA; ++i) {
+        if (i == p) {
+#pragma unroll
+          for (int c = 0; c < MA; ++c) {
+            double x = n[k][c]; n[k][c] = n[i][c]; n[i][c] = x;
+            x = r[k][c]; r[k][c] = r[i][c]; r[i][c] = x;
+          }
+          const double x = v[k]; v[k] = v[i]; v[i] = x;
+        }
+      }
+      const double piv = n[k][k];
+#pragma unroll
+      for (int i = 0; i < MA; ++i) {
+        if (i == k) continue;
+        const double f = n[i][k] / piv;
+#pragma unroll
+        for (int c = 0; c < MA; ++c) { n[i][c] -= f * n[k][c]; r[i][c] -= f * r[k][c]; }
+        v[i] -= f * v[k];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < MA; ++i) {
+      const double inv = 1.0 / n[i][i];
+#pragma unroll
+      for (int c = 0; c < MA; ++c) r[i][c] *= inv;
+      v[i] *= inv;
+    }
+    double kappa[MA];
+#pragma unroll
+    for (int i = 0; i < MA; ++i) {
+      double kq = mu[i];
+#pragma unroll
+      for (int l = 0; l < MA; ++l) kq += ps[i][l] * v[l];
+      kappa[i] = kq;
+    }
+#pragma unroll
+    for (int i = 0; i < MA; ++i) {
+      if (i >= a) continue;
+      atomicAdd(&xs[hs[i]], qk);
+      atomicAdd(&xsz[hs[i]], qk * kappa[i]);
+#pragma unroll
+      for (int j = 0; j < MA; ++j) {
+        if (j >= a) continue;
+        double lam = 0.0;
+#pragma unroll
+        for (int l = 0; l < MA; ++l) lam += ps[i][l] * r[l][j];
+        const int64_t off = (int64_t)hs[i] * H + hs[j];
+        atomicAdd(sum_szsz + off, qk * (lam + kappa[i] * kappa[j]));
+        atomicAdd(sum_ss + off, qk);
+      }
+    }
+    return true;
+  }
+
   template <int T, bool LIST = false>
   __device__ void eval_batch(const uint32_t *st, int ld, int cnt, double *out, unsigned &flags) {
     if (masked == 1) yn2 = masked_yn2();
