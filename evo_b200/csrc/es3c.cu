@@ -22,6 +22,7 @@ int es3c_launch_estep(const EstepDev &dv, const evo_estep_args *x, cudaStream_t 
   EVO_REQUIRE(x->sigma2 > 0.0, "sigma2 must be positive");
   Es3cEval ev;
   memset(&ev, 0, sizeof(ev));
+  ev.budget_estep();
   ev.Psi = x->Psi; ev.mus = x->mus; ev.pil_bar = x->pil_bar_h;
   ev.s2i = (double)(1.0L / (long double)x->sigma2);
   ev.D = dv.D; ev.H = dv.H; ev.Hw = dv.Hw;
@@ -246,6 +247,7 @@ extern "C" int evo_es3c_suffstats(const evo_es3c_stats_args *x, void *stream) {
   if (x->N == 0) return EVO_OK;
   Es3cEval ev;
   memset(&ev, 0, sizeof(ev));
+  ev.budget_stats();
   ev.Psi = x->Psi; ev.mus = x->mus; ev.pil_bar = x->mus;  // pil_bar is not used by the moments
   ev.s2i = (double)(1.0L / (long double)x->sigma2);
   ev.D = x->D; ev.H = x->H; ev.Hw = words_for(x->H);
@@ -287,6 +289,7 @@ extern "C" int evo_es3c_lpj(const uint32_t *states, int shared_states, int64_t N
   if (N == 0) return EVO_OK;
   Es3cEval ev;
   memset(&ev, 0, sizeof(ev));
+  ev.budget_estep();
   ev.Psi = Psi; ev.mus = mus; ev.pil_bar = pil_bar_h;
   ev.s2i = (double)(1.0L / (long double)sigma2);
   ev.D = D; ev.H = H; ev.Hw = words_for(H);
@@ -325,6 +328,7 @@ extern "C" int evo_es3c_full_logsumexp(int64_t N, int D, int H, int background, 
   if (N == 0) return EVO_OK;
   Es3cEval ev;
   memset(&ev, 0, sizeof(ev));
+  ev.budget_estep();
   ev.Psi = Psi; ev.mus = mus; ev.pil_bar = pil_bar_h;
   ev.s2i = (double)(1.0L / (long double)sigma2);
   ev.D = D; ev.H = H; ev.Hw = 1;

@@ -32,6 +32,12 @@ struct Es3cEval {
   double *scratch;       // global per-warp workspaces for 16 < a <= 32 (or NULL)
   int scratch_warps;     // capacity of `scratch` in warps
   int max_batch;         // largest cnt eval_batch will see (index lists of the small / large systems); 0 = no lists
+  // shared-memory budget of the launching kernel (set by the host; shared memory per datapoint decides how many
+  // datapoints an SM holds): the E-step wants the packed 8-lane area and b staged, the statistics pass -- warp and
+  // thread paths only -- a smaller warp area and no staging
+  int as_cap, as_ld;     // warp path in shared memory: systems up to as_cap x as_cap, leading dimension as_ld
+  int warp_bytes;        // per-warp area
+  int stage_b;           // stage this datapoint's row of B in shared memory (else read it through L1 / L2)
   // per datapoint (setup)
   double *vec;           // smem: b [H] (complete) or y [D] (incomplete)
   uint8_t *m;            // smem [D] (incomplete)
@@ -55,15 +61,17 @@ struct Es3cEval {
   static constexpr int G8 = 8, LD8 = 9;      // packed path: 4 states per warp, 8 lanes each (a <= 8)
   static constexpr size_t G8_BYTES = 16 + 3 * G8 * LD8 * sizeof(double);
   static constexpr size_t WARP_SMEM = 4 * G8_BYTES > 64 + 3 * AS * LDS * sizeof(double) ? 4 * G8_BYTES : 64 + 3 * AS * LDS * sizeof(double);
+  __host__ void budget_estep() { as_cap = AS; as_ld = LDS; warp_bytes = (int)WARP_SMEM; stage_b = 1; }
+  __host__ void budget_stats() { as_cap = 12; as_ld = 13; warp_bytes = 64 + 3 * 12 * 13 * (int)sizeof(double); stage_b = 0; }
   static constexpr size_t WARP_SCRATCH = 3 * AG * LDGL;  // doubles
 
   __host__ __device__ size_t head_bytes() const {
     if (masked == 1) return align8((size_t)D * sizeof(double)) + align8((size_t)D);
-    return align8((size_t)H * sizeof(double)) + (masked == 2 ? align8(48 + (size_t)2 * D) : 0);
+    return (stage_b ? align8((size_t)H * sizeof(double)) : 0) + (masked == 2 ? align8(48 + (size_t)2 * D) : 0);
   }
   __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(16 + (size_t)6 * max_batch) : 0; }
   static constexpr bool kList = false;
-  __host__ __device__ size_t smem_bytes(int T, bool = false) const { return head_bytes() + (size_t)(T / 32) * WARP_SMEM + list_bytes(); }
+  __host__ __device__ size_t smem_bytes(int T, bool = false) const { return head_bytes() + (size_t)(T / 32) * warp_bytes + list_bytes(); }
   // measured (cfg3/cfg4, 64 states + 64 children): complete data is fastest with 4 warps and more resident
   // CTAs, masked data (a D-long Gram gather per system) with 8 warps per datapoint
   __host__ int threads_hint(int work) const { return work < 64 ? 64 : (masked == 1 ? 256 : 128); }
@@ -80,10 +88,14 @@ struct Es3cEval {
       }
     } else {
       const double *src = B + n * (int64_t)H;
-      for (int i = threadIdx.x; i < H; i += T) vec[i] = __ldg(src + i);
+      if (stage_b) {
+        for (int i = threadIdx.x; i < H; i += T) vec[i] = __ldg(src + i);
+      } else {
+        vec = const_cast<double *>(src);  // read-only from here on
+      }
       yn2 = __ldg(ynorm2 + n);
       if (masked == 2) {  // ordered list of this datapoint's missing observables: [8 ints scratch | count | uint16 list]
-        int *scr = reinterpret_cast<int *>(smem + align8((size_t)H * sizeof(double)));
+        int *scr = reinterpret_cast<int *>(smem + (stage_b ? align8((size_t)H * sizeof(double)) : 0));
         miss = reinterpret_cast<uint16_t *>(scr + 12);
         int cnt = 0;
         for (int d0 = 0; d0 < D; d0 += T) {
@@ -100,7 +112,7 @@ struct Es3cEval {
       }
     }
     wsm = smem + head_bytes();
-    lsm = wsm + (size_t)(T / 32) * WARP_SMEM;
+    lsm = wsm + (size_t)(T / 32) * warp_bytes;
   }
 
   // |y_obs|^2 for incomplete data (needs the loaded y); call after the post-setup barrier
@@ -136,13 +148,13 @@ struct Es3cEval {
   // workspaces for a state of size a: three matrices with leading dimension ld
   __device__ __forceinline__ bool workspace(int a, uint16_t *&idx, double *&A1, double *&A2, double *&A3, int &ld) const {
     const int warp = threadIdx.x >> 5;
-    unsigned char *base = wsm + (size_t)warp * WARP_SMEM;
+    unsigned char *base = wsm + (size_t)warp * warp_bytes;
     idx = reinterpret_cast<uint16_t *>(base);
-    if (a <= AS) {
+    if (a <= as_cap) {
       A1 = reinterpret_cast<double *>(base + 64);
-      A2 = A1 + AS * LDS;
-      A3 = A2 + AS * LDS;
-      ld = LDS;
+      A2 = A1 + as_cap * as_ld;
+      A3 = A2 + as_cap * as_ld;
+      ld = as_ld;
       return true;
     }
     int gw = blockIdx.x * (blockDim.x >> 5) + warp;
@@ -326,7 +338,7 @@ struct Es3cEval {
   __device__ __forceinline__ double group8_lpj(const uint32_t *st) const {
     const int lane = threadIdx.x & 31, sl = lane & 7, gid = lane >> 3;
     const unsigned gm = 0xFFu << (8 * gid);
-    unsigned char *base = wsm + (size_t)(threadIdx.x >> 5) * WARP_SMEM + (size_t)gid * G8_BYTES;
+    unsigned char *base = wsm + (size_t)(threadIdx.x >> 5) * warp_bytes + (size_t)gid * G8_BYTES;
     uint16_t *idx = reinterpret_cast<uint16_t *>(base);
     double *A1 = reinterpret_cast<double *>(base + 16), *A2 = A1 + G8 * LD8, *A3 = A2 + G8 * LD8;
     // active latents (the caller guarantees |s| <= 8)

@@ -67,7 +67,7 @@ def main():
     from evo_b200.variational import init_states
 
     rng = np.random.RandomState(5)
-    N, D, H, K, iters = 2001, 24, 40, 16, 6
+    N, D, H, K, iters = 2001, 24, 40, 16, 4
     Wg = rng.normal(size=(D, H)) * 2
     s = rng.rand(N, H) < 3.0 / H
     Y = (s @ Wg.T + rng.normal(size=(N, D))).astype(np.float32)
