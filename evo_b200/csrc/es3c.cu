@@ -191,10 +191,14 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
       atomicAdd(sum_s + h, xs[h]);
       atomicAdd(sum_sz + h, xsz[h]);
     }
-    for (int p = threadIdx.x; p < na * na; p += T) {
-      int h = act[p / na], h2 = act[p % na];
-      if (a.learn_psi) atomicAdd(sum_s_sz + (int64_t)h * H + h2, xs[h] * xsz[h2]);
-      if (!ev.masked) atomicAdd(sum_outer + (int64_t)h * H + h2, xsz[h] * xsz[h2]);
+    for (int i = warp; i < na; i += T / 32) {  // rows over warps, columns over lanes: no integer division per pair
+      const int h = act[i];
+      const double xh = xs[h], zh = xsz[h];
+      for (int j = lane; j < na; j += 32) {
+        const int h2 = act[j];
+        if (a.learn_psi) atomicAdd(sum_s_sz + (int64_t)h * H + h2, xh * xsz[h2]);
+        if (!ev.masked) atomicAdd(sum_outer + (int64_t)h * H + h2, zh * xsz[h2]);
+      }
     }
     // estimator, masked trace, W numerator (threads over d, Wt rows are contiguous in d)
     for (int d = threadIdx.x; d < D; d += T) {
@@ -215,11 +219,14 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
       ybuf[d] = yuse;
     }
     __syncthreads();
-    for (int i = 0; i < na; ++i) {
-      int h = act[i];
-      double e = xsz[h];
-      double *row = WpT + (int64_t)h * D;
-      for (int d = threadIdx.x; d < D; d += T) atomicAdd(row + d, e * ybuf[d]);
+    {  // all (latent, observable) pairs over all threads (D need not divide T); (i, d) advanced without a division
+      int i = threadIdx.x / D, d = threadIdx.x - i * D;
+      while (i < na) {
+        const int h = act[i];
+        atomicAdd(WpT + (int64_t)h * D + d, xsz[h] * ybuf[d]);
+        d += T;
+        while (d >= D) { d -= D; ++i; }
+      }
     }
   }
   trace_acc = group_sum<T>(trace_acc, red_d);
