@@ -69,8 +69,11 @@ struct Es3cEval {
     if (masked == 1) return align8((size_t)D * sizeof(double)) + align8((size_t)D);
     return (stage_b ? align8((size_t)H * sizeof(double)) : 0) + (masked == 2 ? align8(48 + (size_t)2 * D) : 0);
   }
-  __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(16 + (size_t)6 * max_batch) : 0; }
+  __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(16 + (size_t)8 * max_batch) : 0; }
   static constexpr bool kList = false;
+  // resident threads per SM the register allocation should allow: shared memory holds 4 datapoints of 128 threads, so
+  // up to 128 registers per thread cost nothing (ptxas otherwise settles on 96 registers and spills in the solvers)
+  static constexpr int kThreadsPerSM = 512;
   __host__ __device__ size_t smem_bytes(int T, bool = false) const { return head_bytes() + (size_t)(T / 32) * warp_bytes + list_bytes(); }
   // measured (cfg3/cfg4, 64 states + 64 children): complete data is fastest with 4 warps and more resident
   // CTAs, masked data (a D-long Gram gather per system) with 8 warps per datapoint
@@ -329,26 +332,30 @@ struct Es3cEval {
   // Same arithmetic as warp_lpj (gather -> N = I + s2i G_AA Psi_A -> LU with partial pivoting -> quad
   // form), with every shuffle / redux / sync restricted to the group's 8-lane mask, so the four
   // groups of a warp run their own trip counts.
-  __device__ __forceinline__ double g8_sum(unsigned gm, double v) const {
-    v += __shfl_xor_sync(gm, v, 4, 8);
-    v += __shfl_xor_sync(gm, v, 2, 8);
-    v += __shfl_xor_sync(gm, v, 1, 8);
+  // W = 8 lanes per state (a <= 8, four states per warp) or W = 4 (a <= 4, eight states per warp)
+  template <int W>
+  __device__ __forceinline__ double gw_sum(unsigned gm, double v) const {
+#pragma unroll
+    for (int o = W / 2; o > 0; o >>= 1) v += __shfl_xor_sync(gm, v, o, W);
     return v;
   }
-  __device__ __forceinline__ double group8_lpj(const uint32_t *st) const {
-    const int lane = threadIdx.x & 31, sl = lane & 7, gid = lane >> 3;
-    const unsigned gm = 0xFFu << (8 * gid);
-    unsigned char *base = wsm + (size_t)(threadIdx.x >> 5) * warp_bytes + (size_t)gid * G8_BYTES;
+  template <int W>
+  __device__ __forceinline__ double group_lpj(const uint32_t *st) const {
+    constexpr int G8 = W, LD8 = W + 1;  // (the names of the 8-lane form)
+    constexpr size_t GBYTES = 16 + 3 * W * (W + 1) * sizeof(double);
+    const int lane = threadIdx.x & 31, sl = lane & (W - 1), gid = lane / W;
+    const unsigned gm = ((1u << W) - 1u) << (W * gid);
+    unsigned char *base = wsm + (size_t)(threadIdx.x >> 5) * warp_bytes + (size_t)gid * GBYTES;
     uint16_t *idx = reinterpret_cast<uint16_t *>(base);
     double *A1 = reinterpret_cast<double *>(base + 16), *A2 = A1 + G8 * LD8, *A3 = A2 + G8 * LD8;
     // active latents (the caller guarantees |s| <= 8)
     int a = 0;
-    for (int w0 = 0; w0 < Hw; w0 += 8) {
+    for (int w0 = 0; w0 < Hw; w0 += W) {
       uint32_t word = (w0 + sl < Hw) ? st[w0 + sl] : 0u;
       const int c = __popc(word);
       int pre = c;
 #pragma unroll
-      for (int o = 1; o < 8; o <<= 1) { int t = __shfl_up_sync(gm, pre, o, 8); if (sl >= o) pre += t; }
+      for (int o = 1; o < W; o <<= 1) { int t = __shfl_up_sync(gm, pre, o, W); if (sl >= o) pre += t; }
       int pos = a + pre - c;
       while (word) {
         int bp = __ffs(word) - 1;
@@ -356,7 +363,7 @@ struct Es3cEval {
         if (pos < G8) idx[pos] = (uint16_t)(((w0 + sl) << 5) + bp);
         ++pos;
       }
-      a += __shfl_sync(gm, pre, 7, 8);
+      a += __shfl_sync(gm, pre, W - 1, W);
     }
     __syncwarp(gm);
     if (a == 0) return -0.5 * s2i * yn2;
@@ -382,15 +389,15 @@ struct Es3cEval {
       for (int i = 0; i < a; ++i) {
         const double *wi = Wt + (int64_t)idx[i] * D;
         double pb = 0.0;
-        for (int d = sl; d < D; d += 8) pb += __ldg(wi + d) * vec[d];
-        pb = g8_sum(gm, pb);
+        for (int d = sl; d < D; d += W) pb += __ldg(wi + d) * vec[d];
+        pb = gw_sum<W>(gm, pb);
         if (sl == i) bi = pb;
         for (int j = 0; j <= i; ++j) {
           const double *wj = Wt + (int64_t)idx[j] * D;
           double p = 0.0;
-          for (int d = sl; d < D; d += 8)
+          for (int d = sl; d < D; d += W)
             if (m[d]) p += __ldg(wi + d) * __ldg(wj + d);
-          p = g8_sum(gm, p);
+          p = gw_sum<W>(gm, p);
           if (sl == 0) { A1[i * LD8 + j] = p; A1[j * LD8 + i] = p; }
         }
       }
@@ -404,14 +411,14 @@ struct Es3cEval {
     const double mu = act ? __ldg(mus + idx[sl]) : 0.0;
     double t = 0.0;
     for (int l = 0; l < a; ++l) {
-      double ml = __shfl_sync(gm, mu, l, 8);
+      double ml = __shfl_sync(gm, mu, l, W);
       if (act) t += A1[sl * LD8 + l] * ml;
     }
     const double v = act ? s2i * (bi - t) : 0.0;
-    const double rn2 = yn2 + g8_sum(gm, act ? mu * (t - 2.0 * bi) : 0.0);
+    const double rn2 = yn2 + gw_sum<W>(gm, act ? mu * (t - 2.0 * bi) : 0.0);
     double w = 0.0;
     for (int l = 0; l < a; ++l) {
-      double vl = __shfl_sync(gm, v, l, 8);
+      double vl = __shfl_sync(gm, v, l, W);
       if (act) w += A2[l * LD8 + sl] * vl;
     }
     if (act) {
@@ -427,11 +434,11 @@ struct Es3cEval {
     int esum = 0;
     for (int k = 0; k < a; ++k) {
       unsigned key = 0u;
-      if (act && sl >= k) key = (__float_as_uint(fabsf((float)A3[sl * LD8 + k])) & ~7u) | (unsigned)(7 - sl);
-      const int p = 7 - (int)(__reduce_max_sync(gm, key) & 7u);
+      if (act && sl >= k) key = (__float_as_uint(fabsf((float)A3[sl * LD8 + k])) & ~(unsigned)(W - 1)) | (unsigned)(W - 1 - sl);
+      const int p = W - 1 - (int)(__reduce_max_sync(gm, key) & (unsigned)(W - 1));
       if (p != k) {
         if (act) { double x = A3[k * LD8 + sl]; A3[k * LD8 + sl] = A3[p * LD8 + sl]; A3[p * LD8 + sl] = x; }
-        double rk = __shfl_sync(gm, rhs, k, 8), rp = __shfl_sync(gm, rhs, p, 8);
+        double rk = __shfl_sync(gm, rhs, k, W), rp = __shfl_sync(gm, rhs, p, W);
         if (sl == k) rhs = rp;
         if (sl == p) rhs = rk;
       }
@@ -449,7 +456,7 @@ struct Es3cEval {
           esum += e2 - 1023;
         }
       }
-      const double rhs_k = __shfl_sync(gm, rhs, k, 8);
+      const double rhs_k = __shfl_sync(gm, rhs, k, W);
       if (act && sl > k) {
         const double f = A3[sl * LD8 + k] / piv;
         for (int c = k + 1; c < a; ++c) A3[sl * LD8 + c] -= f * A3[k * LD8 + c];
@@ -458,13 +465,13 @@ struct Es3cEval {
       __syncwarp(gm);
     }
     for (int k = a - 1; k >= 0; --k) {
-      const double xk = __shfl_sync(gm, rhs, k, 8) / A3[k * LD8 + k];
+      const double xk = __shfl_sync(gm, rhs, k, W) / A3[k * LD8 + k];
       if (sl == k) rhs = xk;
       if (act && sl < k) rhs -= A3[sl * LD8 + k] * xk;
     }
     const double logdet = log(fabs(prod)) + (double)esum * 0.693147180559945309417232121458 + extra;
-    const double quad = s2i * rn2 - g8_sum(gm, act ? w * rhs : 0.0);
-    const double prior = g8_sum(gm, act ? __ldg(pil_bar + idx[sl]) : 0.0);
+    const double quad = s2i * rn2 - gw_sum<W>(gm, act ? w * rhs : 0.0);
+    const double prior = gw_sum<W>(gm, act ? __ldg(pil_bar + idx[sl]) : 0.0);
     __syncwarp(gm);
     return -0.5 * (logdet + quad) + prior;
   }
@@ -705,21 +712,26 @@ struct Es3cEval {
     const bool listed = max_batch > 0 && cnt <= max_batch;
     int *cn = reinterpret_cast<int *>(lsm);
     uint16_t *small = reinterpret_cast<uint16_t *>(lsm + 16), *big = small + max_batch, *tiny = big + max_batch;
-    int ns = 0, nb = cnt, nt = 0;
+    uint16_t *quad = tiny + max_batch;
+    int ns = 0, nb = cnt, nt = 0, nq = 0;
     if (listed) {
       const int tiny_max = masked == 1 ? -1 : SMALL_A;  // the register path reads the Gram tables
+      // eight 4-lane systems per warp: measured faster only where the gather is dear (the missing-data correction of
+      // masked == 2: cfg4 E-step 64.0 -> 59.9 ms; complete data cfg3 51.4 -> 59.6 ms with it, so off there)
+      const int quad_max = masked == 2 ? 4 : 0;
       gsync<T>();
-      if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; cn[2] = 0; }
+      if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; cn[2] = 0; cn[3] = 0; }
       gsync<T>();
 #pragma unroll 1
       for (int i = threadIdx.x; i < cnt; i += T) {
         const int a = popc_state(st + (size_t)i * ld, Hw);
         if (a <= tiny_max) tiny[atomicAdd(&cn[2], 1)] = (uint16_t)i;
+        else if (a <= quad_max) quad[atomicAdd(&cn[3], 1)] = (uint16_t)i;
         else if (a <= G8) small[atomicAdd(&cn[0], 1)] = (uint16_t)i;
         else big[atomicAdd(&cn[1], 1)] = (uint16_t)i;
       }
       gsync<T>();
-      ns = cn[0], nb = cn[1], nt = cn[2];
+      ns = cn[0], nb = cn[1], nt = cn[2], nq = cn[3];
     }
 #pragma unroll 1
     for (int j = threadIdx.x; j < nt; j += T) {
@@ -727,11 +739,22 @@ struct Es3cEval {
       out[i] = lpj_sanitise(small_lpj(st + (size_t)i * ld), flags);
     }
 #pragma unroll 1
+    for (int q = warp; q * 8 < nq; q += T / 32) {
+      const int j = q * 8 + (lane >> 2);
+      if (j < nq) {  // whole 4-lane groups take or skip this branch together
+        const int i = quad[j];
+        double v = group_lpj<4>(st + (size_t)i * ld);
+        v = lpj_sanitise(v, flags);
+        if ((lane & 3) == 0) out[i] = v;
+      }
+    }
+    __syncwarp();
+#pragma unroll 1
     for (int q = warp; q * 4 < ns; q += T / 32) {
       const int j = q * 4 + (lane >> 3);
       if (j < ns) {  // whole 8-lane groups take or skip this branch together
         const int i = small[j];
-        double v = group8_lpj(st + (size_t)i * ld);
+        double v = group_lpj<8>(st + (size_t)i * ld);
         v = lpj_sanitise(v, flags);
         if ((lane & 7) == 0) out[i] = v;
       }

@@ -371,7 +371,7 @@ __device__ inline void sparseflip_state(uint32_t *st, int Hm, double sparseness,
 // other operators are compiled out, which shrinks the kernel's instruction footprint.
 // LIST = states live in shared memory as index lists (see above); requires FAST and an evaluator with eval_batch<T, true>.
 template <class Eval, int T, bool FAST = false, bool LIST = false>
-__global__ void __launch_bounds__(T) estep_kernel(EstepDev a, Eval ev) {
+__global__ void __launch_bounds__(T, Eval::kThreadsPerSM / T) estep_kernel(EstepDev a, Eval ev) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   EstepSmem s;
   estep_carve(a, smem_raw, &s);

@@ -30,6 +30,7 @@ struct BscGramEval {
   __device__ __forceinline__ double pil_bar_now() const { return theta ? theta[1] : pil_bar; }
   static constexpr int MAXA = 24;
   static constexpr bool kList = true;  // can evaluate index-list rows (estep.cuh LIST representation)
+  static constexpr int kThreadsPerSM = 0;  // launch bounds: no minimum number of resident CTAs
 
   __host__ __device__ size_t smem_bytes(int T, bool list = false) const {
     // list form: no staging at all -- a state touches |s| entries of the row, and the shared memory
@@ -156,6 +157,7 @@ struct BscDirectEval {
   __device__ __forceinline__ double pil_bar_now() const { return theta ? theta[1] : pil_bar; }
 
   static constexpr bool kList = false;
+  static constexpr int kThreadsPerSM = 0;
   __host__ __device__ size_t smem_bytes(int, bool = false) const { return (size_t)D * sizeof(double) + (((size_t)D + 7) & ~(size_t)7); }
   __host__ int threads_hint(int work) const { return work <= 32 ? 32 : (work <= 64 ? 64 : 128); }
 
