@@ -512,12 +512,33 @@ struct Es3cEval {
         const bool on = oi && j < a;
         ps[i][j] = on ? __ldg(Psi + (int64_t)hs[i] * H + hs[j]) : 0.0;
         if (j <= i) {
-          double v = on ? __ldg(G + (int64_t)hs[i] * H + hs[j]) : 0.0;
-          if (on && masked == 2) v -= miss_corr(hs[i], hs[j]);
+          const double v = on ? __ldg(G + (int64_t)hs[i] * H + hs[j]) : 0.0;
           g[i][j] = v;
           g[j][i] = v;
         }
       }
+    }
+    if (masked == 2) {  // minus the missing observables' share of every pair: ONE walk over the list, a loads per entry
+      const int nm = *nmiss_ptr;
+      double c[MA][MA];
+#pragma unroll
+      for (int i = 0; i < MA; ++i)
+#pragma unroll
+        for (int j = 0; j < MA; ++j) c[i][j] = 0.0;
+      for (int q = 0; q < nm; ++q) {
+        const int d = miss[q];
+        double wv[MA];
+#pragma unroll
+        for (int i = 0; i < MA; ++i) wv[i] = i < a ? __ldg(Wt + (int64_t)hs[i] * D + d) : 0.0;
+#pragma unroll
+        for (int i = 0; i < MA; ++i)
+#pragma unroll
+          for (int j = 0; j <= i; ++j) c[i][j] += wv[i] * wv[j];
+      }
+#pragma unroll
+      for (int i = 0; i < MA; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) { g[i][j] -= c[i][j]; if (j < i) g[j][i] -= c[i][j]; }
     }
     double t[MA], v[MA], w[MA], n[MA][MA];
     double rn2 = yn2;
@@ -618,12 +639,33 @@ struct Es3cEval {
         const bool on = oi && j < a;
         ps[i][j] = on ? __ldg(Psi + (int64_t)hs[i] * H + hs[j]) : 0.0;
         if (j <= i) {
-          double v = on ? __ldg(G + (int64_t)hs[i] * H + hs[j]) : 0.0;
-          if (on && masked == 2) v -= miss_corr(hs[i], hs[j]);
+          const double v = on ? __ldg(G + (int64_t)hs[i] * H + hs[j]) : 0.0;
           g[i][j] = v;
           g[j][i] = v;
         }
       }
+    }
+    if (masked == 2) {  // minus the missing observables' share of every pair: ONE walk over the list, a loads per entry
+      const int nm = *nmiss_ptr;
+      double c[MA][MA];
+#pragma unroll
+      for (int i = 0; i < MA; ++i)
+#pragma unroll
+        for (int j = 0; j < MA; ++j) c[i][j] = 0.0;
+      for (int q = 0; q < nm; ++q) {
+        const int d = miss[q];
+        double wv[MA];
+#pragma unroll
+        for (int i = 0; i < MA; ++i) wv[i] = i < a ? __ldg(Wt + (int64_t)hs[i] * D + d) : 0.0;
+#pragma unroll
+        for (int i = 0; i < MA; ++i)
+#pragma unroll
+          for (int j = 0; j <= i; ++j) c[i][j] += wv[i] * wv[j];
+      }
+#pragma unroll
+      for (int i = 0; i < MA; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) { g[i][j] -= c[i][j]; if (j < i) g[j][i] -= c[i][j]; }
     }
     double v[MA], n[MA][MA], r[MA][MA];
 #pragma unroll
