@@ -374,11 +374,26 @@ struct Es3cEval {
       if (act) {
         const int h = idx[sl];
         const double *Gr = G + (int64_t)h * H;
-        if (masked == 2) {
-          for (int l = 0; l <= sl; ++l) {
-            const double v = __ldg(Gr + idx[l]) - miss_corr(h, idx[l]);
-            A1[sl * LD8 + l] = v;
-            A1[l * LD8 + sl] = v;
+        if (masked == 2) {  // (W'W)_hl minus the missing observables' share, l <= sl: one walk over the missing list
+          double c[W];
+#pragma unroll
+          for (int l = 0; l < W; ++l) c[l] = 0.0;
+          const int nm = *nmiss_ptr;
+          const double *wh = Wt + (int64_t)h * D;
+          for (int q = 0; q < nm; ++q) {
+            const int d = miss[q];
+            const double x = __ldg(wh + d);
+#pragma unroll
+            for (int l = 0; l < W; ++l)
+              if (l <= sl) c[l] += x * __ldg(Wt + (int64_t)idx[l] * D + d);
+          }
+#pragma unroll
+          for (int l = 0; l < W; ++l) {
+            if (l <= sl) {
+              const double v = __ldg(Gr + idx[l]) - c[l];
+              A1[sl * LD8 + l] = v;
+              A1[l * LD8 + sl] = v;
+            }
           }
         } else {
           for (int l = 0; l < a; ++l) A1[sl * LD8 + l] = __ldg(Gr + idx[l]);
