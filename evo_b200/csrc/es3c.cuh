@@ -496,7 +496,8 @@ struct Es3cEval {
   // lpj = -1/2 (log|det N| + s2i |r|^2 - w' N^-1 v) + sum pil -- on a fixed SMALL_A x SMALL_A system padded with the
   // identity (fully unrolled LU with partial pivoting, no divergence between states of different size).  Most states
   // of a sparse model are this small, and a warp (or 8 lanes) per such state is mostly idle.
-  static constexpr int SMALL_A = 2;
+  static constexpr int SMALL_A = 3;
+  static constexpr int SMALL_M = 2;  // the same bound for the moments of the statistics pass (3 costs it two resident CTAs)
   __device__ __forceinline__ double small_lpj(const uint32_t *st) const {
     constexpr int MA = SMALL_A;
     int hs[MA];
@@ -626,7 +627,7 @@ struct Es3cEval {
   // pair sums sum_ss / sum_szsz.  Returns false (nothing done) for larger states.
   __device__ __forceinline__ bool small_moments(const uint32_t *st, double qk, double *xs, double *xsz, double *sum_ss,
                                                 double *sum_szsz) const {
-    constexpr int MA = SMALL_A;
+    constexpr int MA = SMALL_M;
     int hs[MA];
     int a = 0;
 #pragma unroll
