@@ -69,7 +69,7 @@ struct Es3cEval {
     if (masked == 1) return align8((size_t)D * sizeof(double)) + align8((size_t)D);
     return (stage_b ? align8((size_t)H * sizeof(double)) : 0) + (masked == 2 ? align8(48 + (size_t)2 * D) : 0);
   }
-  __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(16 + (size_t)8 * max_batch) : 0; }
+  __host__ __device__ size_t list_bytes() const { return max_batch > 0 ? align8(16 + (size_t)6 * max_batch) : 0; }
   static constexpr bool kList = false;
   // resident threads per SM the register allocation should allow: shared memory holds 4 datapoints of 128 threads, so
   // up to 128 registers per thread cost nothing (ptxas otherwise settles on 96 registers and spills in the solvers)
@@ -332,7 +332,8 @@ struct Es3cEval {
   // Same arithmetic as warp_lpj (gather -> N = I + s2i G_AA Psi_A -> LU with partial pivoting -> quad
   // form), with every shuffle / redux / sync restricted to the group's 8-lane mask, so the four
   // groups of a warp run their own trip counts.
-  // W = 8 lanes per state (a <= 8, four states per warp) or W = 4 (a <= 4, eight states per warp)
+  // W lanes per state (a <= W), 32 / W states per warp; instantiated for W = 8 (W = 4 was measured: it only paid before the
+  // thread path covered 3..4 active latents)
   template <int W>
   __device__ __forceinline__ double gw_sum(unsigned gm, double v) const {
 #pragma unroll
@@ -496,7 +497,7 @@ struct Es3cEval {
   // lpj = -1/2 (log|det N| + s2i |r|^2 - w' N^-1 v) + sum pil -- on a fixed SMALL_A x SMALL_A system padded with the
   // identity (fully unrolled LU with partial pivoting, no divergence between states of different size).  Most states
   // of a sparse model are this small, and a warp (or 8 lanes) per such state is mostly idle.
-  static constexpr int SMALL_A = 3;
+  static constexpr int SMALL_A = 4;
   static constexpr int SMALL_M = 2;  // the same bound for the moments of the statistics pass (3 costs it two resident CTAs)
   __device__ __forceinline__ double small_lpj(const uint32_t *st) const {
     constexpr int MA = SMALL_A;
@@ -770,43 +771,27 @@ struct Es3cEval {
     const bool listed = max_batch > 0 && cnt <= max_batch;
     int *cn = reinterpret_cast<int *>(lsm);
     uint16_t *small = reinterpret_cast<uint16_t *>(lsm + 16), *big = small + max_batch, *tiny = big + max_batch;
-    uint16_t *quad = tiny + max_batch;
-    int ns = 0, nb = cnt, nt = 0, nq = 0;
+    int ns = 0, nb = cnt, nt = 0;
     if (listed) {
       const int tiny_max = masked == 1 ? -1 : SMALL_A;  // the register path reads the Gram tables
-      // eight 4-lane systems per warp: measured faster only where the gather is dear (the missing-data correction of
-      // masked == 2: cfg4 E-step 64.0 -> 59.9 ms; complete data cfg3 51.4 -> 59.6 ms with it, so off there)
-      const int quad_max = masked == 2 ? 4 : 0;
       gsync<T>();
-      if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; cn[2] = 0; cn[3] = 0; }
+      if (threadIdx.x == 0) { cn[0] = 0; cn[1] = 0; cn[2] = 0; }
       gsync<T>();
 #pragma unroll 1
       for (int i = threadIdx.x; i < cnt; i += T) {
         const int a = popc_state(st + (size_t)i * ld, Hw);
         if (a <= tiny_max) tiny[atomicAdd(&cn[2], 1)] = (uint16_t)i;
-        else if (a <= quad_max) quad[atomicAdd(&cn[3], 1)] = (uint16_t)i;
         else if (a <= G8) small[atomicAdd(&cn[0], 1)] = (uint16_t)i;
         else big[atomicAdd(&cn[1], 1)] = (uint16_t)i;
       }
       gsync<T>();
-      ns = cn[0], nb = cn[1], nt = cn[2], nq = cn[3];
+      ns = cn[0], nb = cn[1], nt = cn[2];
     }
 #pragma unroll 1
     for (int j = threadIdx.x; j < nt; j += T) {
       const int i = tiny[j];
       out[i] = lpj_sanitise(small_lpj(st + (size_t)i * ld), flags);
     }
-#pragma unroll 1
-    for (int q = warp; q * 8 < nq; q += T / 32) {
-      const int j = q * 8 + (lane >> 2);
-      if (j < nq) {  // whole 4-lane groups take or skip this branch together
-        const int i = quad[j];
-        double v = group_lpj<4>(st + (size_t)i * ld);
-        v = lpj_sanitise(v, flags);
-        if ((lane & 3) == 0) out[i] = v;
-      }
-    }
-    __syncwarp();
 #pragma unroll 1
     for (int q = warp; q * 4 < ns; q += T / 32) {
       const int j = q * 4 + (lane >> 3);
