@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ double red_d[8];
   __shared__ int red_i[8];
-  __shared__ int n_act;
+  __shared__ int n_act, n_g8, n_big;
   const int H = a.H, D = a.D, S = a.S, Hw = ev.Hw, cols = a.S + a.S_perm;
   const int64_t H2 = (int64_t)H * H;
   // smem: xs[H] xsz[H] q[cols] ybuf[D] act[H] | evaluator area
@@ -96,7 +96,9 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
   double *q = xsz + H;
   double *ybuf = q + cols;
   int *act = reinterpret_cast<int *>(ybuf + D);
-  unsigned char *ev_smem = reinterpret_cast<unsigned char *>(act + H + (H & 1));
+  uint16_t *g8list = reinterpret_cast<uint16_t *>(act + H + (H & 1));  // live states with 3..8 active latents
+  uint16_t *biglist = g8list + ((S + 3) & ~3);                          // ... with more
+  unsigned char *ev_smem = reinterpret_cast<unsigned char *>(biglist + ((S + 3) & ~3));
   double *sum_s = a.stats, *sum_sz = sum_s + H, *sum_ss = sum_sz + H, *sum_szsz = sum_ss + H2;
   double *sum_s_sz = sum_szsz + H2, *sum_outer = sum_s_sz + H2, *WpT = sum_outer + H2, *trace = WpT + (int64_t)H * D;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -120,19 +122,32 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
     __syncthreads();
     if (ev.masked == 1) ev.yn2 = ev.masked_yn2();
     const uint32_t *stn = a.states + n * (int64_t)S * Hw;
-    // ---- per-state moments: states with <= SMALL_A active latents (most of a sparse model) by one THREAD each ... -----
-    if (ev.masked != 1) {
-      for (int k = threadIdx.x; k < S; k += T) {
-        const double qk = q[a.S_perm + k];
-        if (!(qk > a.q_skip)) continue;
-        if (ev.small_moments(stn + (int64_t)k * Hw, qk, xs, xsz, sum_ss, sum_szsz)) q[a.S_perm + k] = 0.0;  // done
-      }
-      __syncthreads();
-    }
-    // ---- ... the others by one warp each -------------------------------------------------------------------------------
-    for (int k = warp; k < S; k += T / 32) {
-      double qk = q[a.S_perm + k];
+    // ---- per-state moments: states with <= SMALL_M active latents (most of a sparse model) by one THREAD each, ... -----
+    if (threadIdx.x == 0) { n_g8 = 0; n_big = 0; }
+    __syncthreads();
+    for (int k = threadIdx.x; k < S; k += T) {
+      const double qk = q[a.S_perm + k];
       if (!(qk > a.q_skip)) continue;
+      int na = ev.masked != 1 ? ev.small_moments(stn + (int64_t)k * Hw, qk, xs, xsz, sum_ss, sum_szsz)
+                              : popc_state(stn + (int64_t)k * Hw, Hw);
+      if (na == 0 || (ev.masked != 1 && na <= Es3cEval::SMALL_M)) continue;
+      if (na <= Es3cEval::G8) g8list[atomicAdd(&n_g8, 1)] = (uint16_t)k;
+      else biglist[atomicAdd(&n_big, 1)] = (uint16_t)k;
+    }
+    __syncthreads();
+    // ---- ... up to 8 latents by 8 lanes each (four states per warp) ... ---------------------------------------------------
+    for (int g = warp; g * 4 < n_g8; g += T / 32) {
+      const int j = g * 4 + (lane >> 3);
+      if (j < n_g8) {  // whole 8-lane groups take or skip this branch together
+        const int k = g8list[j];
+        ev.template group_moments<8>(stn + (int64_t)k * Hw, q[a.S_perm + k], xs, xsz, sum_ss, sum_szsz);
+      }
+    }
+    __syncwarp();
+    // ---- ... the others by one warp each -------------------------------------------------------------------------------
+    for (int b = warp; b < n_big; b += T / 32) {
+      const int k = biglist[b];
+      double qk = q[a.S_perm + k];
       uint16_t *idx;
       double *A1, *A2, *A3;
       int ld;
@@ -269,7 +284,8 @@ extern "C" int evo_es3c_suffstats(const evo_es3c_stats_args *x, void *stream) {
   }
   constexpr int T = 128;
   int H = x->H, cols = x->S + x->S_perm;
-  size_t smem = sizeof(double) * ((size_t)2 * H + cols + x->D) + sizeof(int) * (size_t)(H + (H & 1)) + ev.smem_bytes(T);
+  size_t smem = sizeof(double) * ((size_t)2 * H + cols + x->D) + sizeof(int) * (size_t)(H + (H & 1)) +
+                2 * sizeof(uint16_t) * (size_t)((x->S + 3) & ~3) + ev.smem_bytes(T);
   auto k = es3c_suffstats_kernel<T>;
   if (smem > 227 * 1024) {
     set_error("evo_es3c_suffstats: %zu bytes of shared memory exceed 227 KB", smem);

@@ -62,7 +62,7 @@ struct Es3cEval {
   static constexpr size_t G8_BYTES = 16 + 3 * G8 * LD8 * sizeof(double);
   static constexpr size_t WARP_SMEM = 4 * G8_BYTES > 64 + 3 * AS * LDS * sizeof(double) ? 4 * G8_BYTES : 64 + 3 * AS * LDS * sizeof(double);
   __host__ void budget_estep() { as_cap = AS; as_ld = LDS; warp_bytes = (int)WARP_SMEM; stage_b = 1; }
-  __host__ void budget_stats() { as_cap = 12; as_ld = 13; warp_bytes = 64 + 3 * 12 * 13 * (int)sizeof(double); stage_b = 0; }
+  __host__ void budget_stats() { as_cap = AS; as_ld = LDS; warp_bytes = (int)WARP_SMEM; stage_b = 0; }
   static constexpr size_t WARP_SCRATCH = 3 * AG * LDGL;  // doubles
 
   __host__ __device__ size_t head_bytes() const {
@@ -492,6 +492,175 @@ struct Es3cEval {
     return -0.5 * (logdet + quad) + prior;
   }
 
+  // Posterior moments of a state with a <= W active latents by W lanes (32 / W states per warp): the statistics pass's
+  // counterpart of group_lpj -- same N and v, then the inverse instead of the factorisation.
+  template <int W>
+  __device__ __forceinline__ void group_moments(const uint32_t *st, double qk, double *xs, double *xsz, double *sum_ss,
+                                                double *sum_szsz) const {
+    constexpr int G8 = W, LD8 = W + 1;  // (the names of the 8-lane form)
+    constexpr size_t GBYTES = 16 + 3 * W * (W + 1) * sizeof(double);
+    const int lane = threadIdx.x & 31, sl = lane & (W - 1), gid = lane / W;
+    const unsigned gm = ((1u << W) - 1u) << (W * gid);
+    unsigned char *base = wsm + (size_t)(threadIdx.x >> 5) * warp_bytes + (size_t)gid * GBYTES;
+    uint16_t *idx = reinterpret_cast<uint16_t *>(base);
+    double *A1 = reinterpret_cast<double *>(base + 16), *A2 = A1 + G8 * LD8, *A3 = A2 + G8 * LD8;
+    // active latents (the caller guarantees |s| <= 8)
+    int a = 0;
+    for (int w0 = 0; w0 < Hw; w0 += W) {
+      uint32_t word = (w0 + sl < Hw) ? st[w0 + sl] : 0u;
+      const int c = __popc(word);
+      int pre = c;
+#pragma unroll
+      for (int o = 1; o < W; o <<= 1) { int t = __shfl_up_sync(gm, pre, o, W); if (sl >= o) pre += t; }
+      int pos = a + pre - c;
+      while (word) {
+        int bp = __ffs(word) - 1;
+        word &= word - 1;
+        if (pos < G8) idx[pos] = (uint16_t)(((w0 + sl) << 5) + bp);
+        ++pos;
+      }
+      a += __shfl_sync(gm, pre, W - 1, W);
+    }
+    __syncwarp(gm);
+    if (a == 0) return;
+    const bool act = sl < a;
+    // gather G_AA -> A1, Psi_AA -> A2, b_i
+    double bi = 0.0;
+    if (masked != 1) {
+      if (act) {
+        const int h = idx[sl];
+        const double *Gr = G + (int64_t)h * H;
+        if (masked == 2) {  // (W'W)_hl minus the missing observables' share, l <= sl: one walk over the missing list
+          double c[W];
+#pragma unroll
+          for (int l = 0; l < W; ++l) c[l] = 0.0;
+          const int nm = *nmiss_ptr;
+          const double *wh = Wt + (int64_t)h * D;
+          for (int q = 0; q < nm; ++q) {
+            const int d = miss[q];
+            const double x = __ldg(wh + d);
+#pragma unroll
+            for (int l = 0; l < W; ++l)
+              if (l <= sl) c[l] += x * __ldg(Wt + (int64_t)idx[l] * D + d);
+          }
+#pragma unroll
+          for (int l = 0; l < W; ++l) {
+            if (l <= sl) {
+              const double v = __ldg(Gr + idx[l]) - c[l];
+              A1[sl * LD8 + l] = v;
+              A1[l * LD8 + sl] = v;
+            }
+          }
+        } else {
+          for (int l = 0; l < a; ++l) A1[sl * LD8 + l] = __ldg(Gr + idx[l]);
+        }
+        bi = vec[h];
+      }
+    } else {
+      for (int i = 0; i < a; ++i) {
+        const double *wi = Wt + (int64_t)idx[i] * D;
+        double pb = 0.0;
+        for (int d = sl; d < D; d += W) pb += __ldg(wi + d) * vec[d];
+        pb = gw_sum<W>(gm, pb);
+        if (sl == i) bi = pb;
+        for (int j = 0; j <= i; ++j) {
+          const double *wj = Wt + (int64_t)idx[j] * D;
+          double p = 0.0;
+          for (int d = sl; d < D; d += W)
+            if (m[d]) p += __ldg(wi + d) * __ldg(wj + d);
+          p = gw_sum<W>(gm, p);
+          if (sl == 0) { A1[i * LD8 + j] = p; A1[j * LD8 + i] = p; }
+        }
+      }
+    }
+    if (act) {
+      const double *Pr = Psi + (int64_t)idx[sl] * H;
+      for (int l = 0; l < a; ++l) A2[sl * LD8 + l] = __ldg(Pr + idx[l]);
+    }
+    __syncwarp(gm);
+    // v, |r|^2, w = Psi_A' v, N -> A3
+    const double mu = act ? __ldg(mus + idx[sl]) : 0.0;
+    double t = 0.0;
+    for (int l = 0; l < a; ++l) {
+      double ml = __shfl_sync(gm, mu, l, W);
+      if (act) t += A1[sl * LD8 + l] * ml;
+    }
+    const double v = act ? s2i * (bi - t) : 0.0;
+    const double rn2 = yn2 + gw_sum<W>(gm, act ? mu * (t - 2.0 * bi) : 0.0);
+    double w = 0.0;
+    for (int l = 0; l < a; ++l) {
+      double vl = __shfl_sync(gm, v, l, W);
+      if (act) w += A2[l * LD8 + sl] * vl;
+    }
+    if (act) {
+      for (int j = 0; j < a; ++j) {
+        double acc = 0.0;
+        for (int l = 0; l < a; ++l) acc += A1[sl * LD8 + l] * A2[l * LD8 + j];
+        A3[sl * LD8 + j] = (sl == j ? 1.0 : 0.0) + s2i * acc;
+      }
+    }
+    __syncwarp(gm);
+    // Gauss-Jordan with partial pivoting on [N | R] (R = A1: G_AA is no longer needed), x <- N^-1 v -- gj_inverse on W lanes
+    double x = v;
+    double *R = A1;
+    if (act)
+      for (int c = 0; c < a; ++c) R[sl * LD8 + c] = (sl == c) ? 1.0 : 0.0;
+    __syncwarp(gm);
+    for (int k = 0; k < a; ++k) {
+      unsigned key = 0u;
+      if (act && sl >= k) key = (__float_as_uint(fabsf((float)A3[sl * LD8 + k])) & ~(unsigned)(W - 1)) | (unsigned)(W - 1 - sl);
+      const int p = W - 1 - (int)(__reduce_max_sync(gm, key) & (unsigned)(W - 1));
+      if (p != k) {
+        if (act) {
+          double tt = A3[k * LD8 + sl]; A3[k * LD8 + sl] = A3[p * LD8 + sl]; A3[p * LD8 + sl] = tt;
+          tt = R[k * LD8 + sl]; R[k * LD8 + sl] = R[p * LD8 + sl]; R[p * LD8 + sl] = tt;
+        }
+        const double xk = __shfl_sync(gm, x, k, W), xp = __shfl_sync(gm, x, p, W);
+        if (sl == k) x = xp;
+        if (sl == p) x = xk;
+      }
+      __syncwarp(gm);
+      const double piv = A3[k * LD8 + k];
+      const double x_k = __shfl_sync(gm, x, k, W);
+      if (act && sl != k) {
+        const double f = A3[sl * LD8 + k] / piv;
+        for (int c = k + 1; c < a; ++c) A3[sl * LD8 + c] -= f * A3[k * LD8 + c];
+        for (int c = 0; c < a; ++c) R[sl * LD8 + c] -= f * R[k * LD8 + c];
+        x -= f * x_k;
+      }
+      __syncwarp(gm);
+    }
+    if (act) {
+      const double inv = 1.0 / A3[sl * LD8 + sl];
+      for (int c = 0; c < a; ++c) R[sl * LD8 + c] *= inv;
+      x *= inv;
+    }
+    __syncwarp(gm);
+    // kappa = Psi_A x + mu ; Lambda = Psi_A N^-1 ; accumulate with weight qk (as the warp path of es3c_suffstats_kernel)
+    double kappa = 0.0;
+    for (int l = 0; l < a; ++l) {
+      const double xl = __shfl_sync(gm, x, l, W);
+      if (act) kappa += A2[sl * LD8 + l] * xl;
+    }
+    kappa += mu;
+    const int h = act ? idx[sl] : 0;
+    if (act) {
+      atomicAdd(&xs[h], qk);
+      atomicAdd(&xsz[h], qk * kappa);
+    }
+    for (int j = 0; j < a; ++j) {
+      const double kj = __shfl_sync(gm, kappa, j, W);
+      if (act) {
+        double lam = 0.0;
+        for (int l = 0; l < a; ++l) lam += A2[sl * LD8 + l] * R[l * LD8 + j];
+        const int64_t off = (int64_t)h * H + idx[j];
+        atomicAdd(sum_szsz + off, qk * (lam + kappa * kj));
+        atomicAdd(sum_ss + off, qk);
+      }
+    }
+    __syncwarp(gm);
+  }
+
   // ---- states with at most SMALL_A active latents: one THREAD per state, everything in registers -------------------
   // Same quantities as build() / lu_solve() -- N = I + s2i G_AA Psi_A, v = s2i (b - G mu), |r|^2, w = Psi_A' v,
   // lpj = -1/2 (log|det N| + s2i |r|^2 - w' N^-1 v) + sum pil -- on a fixed SMALL_A x SMALL_A system padded with the
@@ -625,8 +794,8 @@ struct Es3cEval {
   // Posterior moments of a state with at most SMALL_A active latents by ONE thread (the statistics pass, sssc.py:553-646):
   // x = N^-1 v, kappa = Psi_A x + mu_A, Lambda = Psi_A N^-1 from the same N, v as small_lpj (LU with partial pivoting,
   // unit padding), accumulated with weight qk into the per-datapoint vectors xs / xsz (shared memory) and the global
-  // pair sums sum_ss / sum_szsz.  Returns false (nothing done) for larger states.
-  __device__ __forceinline__ bool small_moments(const uint32_t *st, double qk, double *xs, double *xsz, double *sum_ss,
+  // pair sums sum_ss / sum_szsz.  Returns |s|; nothing is done for states larger than SMALL_M.
+  __device__ __forceinline__ int small_moments(const uint32_t *st, double qk, double *xs, double *xsz, double *sum_ss,
                                                 double *sum_szsz) const {
     constexpr int MA = SMALL_M;
     int hs[MA];
@@ -643,8 +812,7 @@ struct Es3cEval {
         ++a;
       }
     }
-    if (a > MA) return false;
-    if (a == 0) return true;
+    if (a > MA || a == 0) return a;  // larger states: the caller's group / warp paths
     double g[MA][MA], ps[MA][MA], mu[MA], b[MA];
 #pragma unroll
     for (int i = 0; i < MA; ++i) {
@@ -759,7 +927,7 @@ struct Es3cEval {
         atomicAdd(sum_ss + off, qk);
       }
     }
-    return true;
+    return a;
   }
 
   template <int T, bool LIST = false>
