@@ -82,79 +82,19 @@ __device__ __forceinline__ void gj_inverse(int a, double *A3, double *R, int ld,
 }
 
 
-template <int T>
-__global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a, Es3cEval ev) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ double red_d[8];
-  __shared__ int red_i[8];
-  __shared__ int n_act, n_g8, n_big;
-  const int H = a.H, D = a.D, S = a.S, Hw = ev.Hw, cols = a.S + a.S_perm;
-  const int64_t H2 = (int64_t)H * H;
-  // smem: xs[H] xsz[H] q[cols] ybuf[D] act[H] | evaluator area
-  double *xs = reinterpret_cast<double *>(smem_raw);
-  double *xsz = xs + H;
-  double *q = xsz + H;
-  double *ybuf = q + cols;
-  int *act = reinterpret_cast<int *>(ybuf + D);
-  uint16_t *g8list = reinterpret_cast<uint16_t *>(act + H + (H & 1));  // live states with 3..8 active latents
-  uint16_t *biglist = g8list + ((S + 3) & ~3);                          // ... with more
-  unsigned char *ev_smem = reinterpret_cast<unsigned char *>(biglist + ((S + 3) & ~3));
-  double *sum_s = a.stats, *sum_sz = sum_s + H, *sum_ss = sum_sz + H, *sum_szsz = sum_ss + H2;
-  double *sum_s_sz = sum_szsz + H2, *sum_outer = sum_s_sz + H2, *WpT = sum_outer + H2, *trace = WpT + (int64_t)H * D;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double trace_acc = 0.0;
-  for (int64_t n = blockIdx.x; n < a.N; n += gridDim.x) {
-    __syncthreads();
-    for (int h = threadIdx.x; h < H; h += T) { xs[h] = 0.0; xsz[h] = 0.0; }
-    ev.template setup<T>(n, ev_smem);
-    // posterior over all S + S_perm columns (the tiny eps of sssc.py:602 is below f64 resolution here)
-    {
-      const double *row = a.lpj + n * cols;
-      double mx = -DBL_MAX;
-      for (int i = threadIdx.x; i < cols; i += T) { double v = row[i]; q[i] = v; mx = fmax(mx, v); }
-      mx = group_max<T>(mx, red_d);
-      double se = 0.0;
-      for (int i = threadIdx.x; i < cols; i += T) { double e = exp(q[i] - mx); q[i] = e; se += e; }
-      se = group_sum<T>(se, red_d);
-      double inv = 1.0 / (se + DBL_MIN);
-      for (int i = threadIdx.x; i < cols; i += T) q[i] *= inv;
-    }
-    __syncthreads();
-    if (ev.masked == 1) ev.yn2 = ev.masked_yn2();
-    const uint32_t *stn = a.states + n * (int64_t)S * Hw;
-    // ---- per-state moments: states with <= SMALL_M active latents (most of a sparse model) by one THREAD each, ... -----
-    if (threadIdx.x == 0) { n_g8 = 0; n_big = 0; }
-    __syncthreads();
-    for (int k = threadIdx.x; k < S; k += T) {
-      const double qk = q[a.S_perm + k];
-      if (!(qk > a.q_skip)) continue;
-      int na = ev.masked != 1 ? ev.small_moments(stn + (int64_t)k * Hw, qk, xs, xsz, sum_ss, sum_szsz)
-                              : popc_state(stn + (int64_t)k * Hw, Hw);
-      if (na == 0 || (ev.masked != 1 && na <= Es3cEval::SMALL_M)) continue;
-      if (na <= Es3cEval::G8) g8list[atomicAdd(&n_g8, 1)] = (uint16_t)k;
-      else biglist[atomicAdd(&n_big, 1)] = (uint16_t)k;
-    }
-    __syncthreads();
-    // ---- ... up to 8 latents by 8 lanes each (four states per warp) ... ---------------------------------------------------
-    for (int g = warp; g * 4 < n_g8; g += T / 32) {
-      const int j = g * 4 + (lane >> 3);
-      if (j < n_g8) {  // whole 8-lane groups take or skip this branch together
-        const int k = g8list[j];
-        ev.template group_moments<8>(stn + (int64_t)k * Hw, q[a.S_perm + k], xs, xsz, sum_ss, sum_szsz);
-      }
-    }
-    __syncwarp();
-    // ---- ... the others by one warp each -------------------------------------------------------------------------------
-    for (int b = warp; b < n_big; b += T / 32) {
-      const int k = biglist[b];
-      double qk = q[a.S_perm + k];
+// Posterior moments of one state by one warp (lane = row), accumulated with weight qk.  cta > 0: the warp owns the areas of
+// all warps of the CTA for this call (Es3cEval::workspace_cta).
+__device__ __forceinline__ void warp_state_moments(const Es3cEval &ev, const uint32_t *st, double qk, int cta, int H, double *xs,
+                                                   double *xsz, double *sum_ss, double *sum_szsz) {
+  const int lane = threadIdx.x & 31;
+  {
       uint16_t *idx;
       double *A1, *A2, *A3;
       int ld;
-      ev.workspace(0, idx, A1, A2, A3, ld);
-      int na = ev.active_list(stn + (int64_t)k * Hw, idx);
-      if (na == 0) continue;
-      if (!ev.workspace(na, idx, A1, A2, A3, ld)) continue;  // rejected state (lowest lpj, zero weight)
+      if (cta > 0) ev.workspace_cta(cta, idx, A1, A2, A3, ld); else ev.workspace(0, idx, A1, A2, A3, ld);
+      int na = ev.active_list(st, idx);
+      if (na == 0) return;
+      if (!(cta > 0 && na <= cta) && !ev.workspace(na, idx, A1, A2, A3, ld)) return;  // rejected state (lowest lpj, zero weight)
       double ynorm;
       double bi = ev.gather(na, idx, A1, A2, ld, ynorm);
       double v, rn2, w, mu;
@@ -185,6 +125,86 @@ __global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a
         }
       }
       __syncwarp();
+      }
+}
+
+template <int T>
+__global__ void __launch_bounds__(T) es3c_suffstats_kernel(evo_es3c_stats_args a, Es3cEval ev) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ double red_d[8];
+  __shared__ int red_i[8];
+  __shared__ int n_act, n_g8, n_big, n_huge;
+  const int H = a.H, D = a.D, S = a.S, Hw = ev.Hw, cols = a.S + a.S_perm;
+  const int64_t H2 = (int64_t)H * H;
+  // smem: xs[H] xsz[H] q[cols] ybuf[D] act[H] | evaluator area
+  double *xs = reinterpret_cast<double *>(smem_raw);
+  double *xsz = xs + H;
+  double *q = xsz + H;
+  double *ybuf = q + cols;
+  int *act = reinterpret_cast<int *>(ybuf + D);
+  uint16_t *g8list = reinterpret_cast<uint16_t *>(act + H + (H & 1));  // live states with 3..8 active latents
+  uint16_t *biglist = g8list + ((S + 3) & ~3);                          // ... with up to as_cap (or beyond the CTA area)
+  uint16_t *hugelist = biglist + ((S + 3) & ~3);                        // ... in between: the CTA-wide shared workspace
+  unsigned char *ev_smem = reinterpret_cast<unsigned char *>(hugelist + ((S + 3) & ~3));
+  const int ccap = ev.cta_cap(T / 32);
+  double *sum_s = a.stats, *sum_sz = sum_s + H, *sum_ss = sum_sz + H, *sum_szsz = sum_ss + H2;
+  double *sum_s_sz = sum_szsz + H2, *sum_outer = sum_s_sz + H2, *WpT = sum_outer + H2, *trace = WpT + (int64_t)H * D;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double trace_acc = 0.0;
+  for (int64_t n = blockIdx.x; n < a.N; n += gridDim.x) {
+    __syncthreads();
+    for (int h = threadIdx.x; h < H; h += T) { xs[h] = 0.0; xsz[h] = 0.0; }
+    ev.template setup<T>(n, ev_smem);
+    // posterior over all S + S_perm columns (the tiny eps of sssc.py:602 is below f64 resolution here)
+    {
+      const double *row = a.lpj + n * cols;
+      double mx = -DBL_MAX;
+      for (int i = threadIdx.x; i < cols; i += T) { double v = row[i]; q[i] = v; mx = fmax(mx, v); }
+      mx = group_max<T>(mx, red_d);
+      double se = 0.0;
+      for (int i = threadIdx.x; i < cols; i += T) { double e = exp(q[i] - mx); q[i] = e; se += e; }
+      se = group_sum<T>(se, red_d);
+      double inv = 1.0 / (se + DBL_MIN);
+      for (int i = threadIdx.x; i < cols; i += T) q[i] *= inv;
+    }
+    __syncthreads();
+    if (ev.masked == 1) ev.yn2 = ev.masked_yn2();
+    const uint32_t *stn = a.states + n * (int64_t)S * Hw;
+    // ---- per-state moments: states with <= SMALL_M active latents (most of a sparse model) by one THREAD each, ... -----
+    if (threadIdx.x == 0) { n_g8 = 0; n_big = 0; n_huge = 0; }
+    __syncthreads();
+    for (int k = threadIdx.x; k < S; k += T) {
+      const double qk = q[a.S_perm + k];
+      if (!(qk > a.q_skip)) continue;
+      int na = ev.masked != 1 ? ev.small_moments(stn + (int64_t)k * Hw, qk, xs, xsz, sum_ss, sum_szsz)
+                              : popc_state(stn + (int64_t)k * Hw, Hw);
+      if (na == 0 || (ev.masked != 1 && na <= Es3cEval::SMALL_M)) continue;
+      if (na <= Es3cEval::G8) g8list[atomicAdd(&n_g8, 1)] = (uint16_t)k;
+      else if (na <= ev.as_cap || na > ccap) biglist[atomicAdd(&n_big, 1)] = (uint16_t)k;
+      else hugelist[atomicAdd(&n_huge, 1)] = (uint16_t)k;
+    }
+    __syncthreads();
+    // ---- ... up to 8 latents by 8 lanes each (four states per warp) ... ---------------------------------------------------
+    for (int g = warp; g * 4 < n_g8; g += T / 32) {
+      const int j = g * 4 + (lane >> 3);
+      if (j < n_g8) {  // whole 8-lane groups take or skip this branch together
+        const int k = g8list[j];
+        ev.template group_moments<8>(stn + (int64_t)k * Hw, q[a.S_perm + k], xs, xsz, sum_ss, sum_szsz);
+      }
+    }
+    __syncwarp();
+    // ---- ... the others by one warp each -------------------------------------------------------------------------------
+    for (int b = warp; b < n_big; b += T / 32) {
+      const int k = biglist[b];
+      warp_state_moments(ev, stn + (int64_t)k * Hw, q[a.S_perm + k], 0, H, xs, xsz, sum_ss, sum_szsz);
+    }
+    if (n_huge > 0) {  // as_cap < |s| <= ccap: one state at a time in the CTA's whole workspace, by warp 0
+      __syncthreads();
+      if (warp == 0)
+        for (int b = 0; b < n_huge; ++b) {
+          const int k = hugelist[b];
+          warp_state_moments(ev, stn + (int64_t)k * Hw, q[a.S_perm + k], ccap, H, xs, xsz, sum_ss, sum_szsz);
+        }
     }
     __syncthreads();
     // ---- per-datapoint vectors -> global sums -----------------------------------------------------
@@ -285,7 +305,7 @@ extern "C" int evo_es3c_suffstats(const evo_es3c_stats_args *x, void *stream) {
   constexpr int T = 128;
   int H = x->H, cols = x->S + x->S_perm;
   size_t smem = sizeof(double) * ((size_t)2 * H + cols + x->D) + sizeof(int) * (size_t)(H + (H & 1)) +
-                2 * sizeof(uint16_t) * (size_t)((x->S + 3) & ~3) + ev.smem_bytes(T);
+                3 * sizeof(uint16_t) * (size_t)((x->S + 3) & ~3) + ev.smem_bytes(T);
   auto k = es3c_suffstats_kernel<T>;
   if (smem > 227 * 1024) {
     set_error("evo_es3c_suffstats: %zu bytes of shared memory exceed 227 KB", smem);

@@ -169,6 +169,24 @@ struct Es3cEval {
     return true;
   }
 
+  // States too large for a warp's own area (as_cap < a <= AG) can borrow the areas of ALL warps of the CTA, one state at a
+  // time, while the other warps wait at a barrier -- shared memory instead of the global scratch, whose dependent
+  // round trips to L2 made 3 % of the states most of the statistics pass at density (the E-step keeps the
+  // global scratch: there the serial phase cost more than it saved).  cta_cap: the largest a that fits.
+  __device__ __forceinline__ int cta_cap(int nwarps) const {
+    const int bytes = nwarps * warp_bytes - 64;
+    int a = AG;
+    while (a > 0 && 3 * a * (a + 1) * (int)sizeof(double) > bytes) --a;
+    return a;
+  }
+  __device__ __forceinline__ void workspace_cta(int cap, uint16_t *&idx, double *&A1, double *&A2, double *&A3, int &ld) const {
+    idx = reinterpret_cast<uint16_t *>(wsm);
+    A1 = reinterpret_cast<double *>(wsm + 64);
+    ld = cap + 1;
+    A2 = A1 + cap * ld;
+    A3 = A2 + cap * ld;
+  }
+
   // Gathers G_AA -> A1, Psi_AA -> A2 and returns this lane's b_i (W_A' y)_i; lane i <-> latent idx[i].
   __device__ __forceinline__ double gather(int a, const uint16_t *idx, double *A1, double *A2, int ld, double &ynorm) const {
     const int lane = threadIdx.x & 31;
