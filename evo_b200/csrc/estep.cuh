@@ -401,7 +401,15 @@ __global__ void __launch_bounds__(T, Eval::kThreadsPerSM / T) estep_kernel(Estep
             if (!list_from_bits(src + (size_t)i * Hg, Hg, s.st_uniq + (size_t)i * Hs) && (tid & 31) == 0) s.sh[0] = 1;
         }
       } else {
-        _Pragma("unroll 1") for (int i = tid; i < S * Hw; i += T) s.st_uniq[(i / Hw) * Hs + (i % Hw)] = src[i];
+        {  // global rows of Hw words -> shared rows of Hs words; (row, word) advanced without a division per element
+          int r = tid / Hw, c = tid - r * Hw;
+          const int dr = T / Hw, dc = T - dr * Hw;
+          _Pragma("unroll 1") for (int i = tid; i < S * Hw; i += T) {
+            s.st_uniq[r * Hs + c] = src[i];
+            r += dr; c += dc;
+            if (c >= Hw) { c -= Hw; ++r; }
+          }
+        }
       }
       _Pragma("unroll 1") for (int i = tid; i < a.HT; i += T) s.table[i] = TAG_EMPTY;
       _Pragma("unroll 1") for (int i = tid; i < S + a.Ctot; i += T) s.redisc[i] = 0;
