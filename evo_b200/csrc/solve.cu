@@ -194,9 +194,10 @@ __global__ void __launch_bounds__(256, 1) block_solve_kernel(double *Mx, int Hp,
           if (bad && threadIdx.x == 0) atomicCAS(info, 0, k + 2);
         }
         __threadfence();
-        for (int t = G; t < ti * tj; t += G) gemm_tile(u, t / tj, t % tj, sa, sb);
-      } else {
-        for (int t = me; t < ti * tj; t += G) gemm_tile(u, t / tj, t % tj, sa, sb);
+        if (G == 1)
+          for (int t = 1; t < ti * tj; ++t) gemm_tile(u, t / tj, t % tj, sa, sb);
+      } else {  // the other CTAs share the remaining tiles: CTA 0 is busy with the inversion (the critical path)
+        for (int t = me; t < ti * tj; t += G - 1) gemm_tile(u, t / tj, t % tj, sa, sb);
       }
       grid.sync();
     }
