@@ -447,7 +447,16 @@ struct TArgs {
   int accumulate;        // 0: out = C (k_chunks == 1); 1: out += C by f64 atomics
   const float *descale;  // device scalar 2^-(ea + eb)
   double *B;             // output, row stride H
+  int chunk_major;       // split-K item order: 1 = all output tiles of one k-chunk are neighbours, so the CTAs running at the
+                         // same time share the chunk's operand slabs in L2 and every operand byte comes from HBM once
 };
+// Split-K item order of the Wp GEMM, measured at cfg5 (N = 1M): tile-major 8.8 ms; tile-major with a private f64 tile per CTA
+// instead of one atomic per element per item 8.9 ms (the atomics were never the limit); chunk-major 7.5 ms (the operand slabs
+// of a k-chunk, 32 MB, stay in L2 while all 32 output tiles use them); chunks of 32 / 128 / 256 k-blocks 7.6 / 7.9 / 7.9 ms.
+__device__ __forceinline__ void item_decode(const TArgs &a, int64_t it, int64_t tiles, int64_t &tj, int &kc) {
+  if (a.chunk_major) { kc = (int)(it / tiles); tj = it - (int64_t)kc * tiles; }
+  else { tj = it / a.k_chunks; kc = (int)(it - tj * a.k_chunks); }
+}
 
 __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_constant__ CUtensorMap tmapA,
                                                                   const __grid_constant__ CUtensorMap tmapB, TArgs a) {
@@ -476,7 +485,8 @@ __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int64_t items = ((a.N + BM - 1) / BM) * a.n_tiles * a.k_chunks;
+  const int64_t tiles_all = ((a.N + BM - 1) / BM) * a.n_tiles;
+  const int64_t items = tiles_all * a.k_chunks;
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
@@ -484,9 +494,11 @@ __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_c
       uint32_t ph = 0;
       const uint32_t tx = 2u * A_BYTES + 2u * (uint32_t)a.box_rows * 128u;
       for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
-        const int64_t tj = it / a.k_chunks;
+        int64_t tj;
+        int kc;
+        item_decode(a, it, tiles_all, tj, kc);
         const int64_t t = tj / a.n_tiles;
-        const int j = (int)(tj % a.n_tiles), kb0 = (int)(it % a.k_chunks) * a.kb_chunk, kb1 = min(a.KB, kb0 + a.kb_chunk);
+        const int j = (int)(tj % a.n_tiles), kb0 = kc * a.kb_chunk, kb1 = min(a.KB, kb0 + a.kb_chunk);
           for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(EMPTY(st), ph ^ 1u);
             mbar_expect_tx(FULL(st), tx);
@@ -504,8 +516,11 @@ __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_c
       int st = 0, ts = 0;
       uint32_t ph = 0, tph = 0;
       for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
-          const int j = (int)((it / a.k_chunks) % a.n_tiles);
-          const int kb0 = (int)(it % a.k_chunks) * a.kb_chunk, kb1 = min(a.KB, kb0 + a.kb_chunk);
+          int64_t tj;
+          int kc;
+          item_decode(a, it, tiles_all, tj, kc);
+          const int j = (int)(tj % a.n_tiles);
+          const int kb0 = kc * a.kb_chunk, kb1 = min(a.KB, kb0 + a.kb_chunk);
           const int nj = min(BN, a.Hp - j * BN);
           const uint32_t idesc = umma_idesc_f16(nj);
           mbar_wait(T_EMPTY(ts), tph ^ 1u);
@@ -538,7 +553,9 @@ __global__ void __launch_bounds__(T_THREADS, 1) table_gemm_kernel(const __grid_c
     uint32_t tph = 0;
     const bool vec2 = (a.H & 1) == 0;
     for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
-      const int64_t tj = it / a.k_chunks;
+      int64_t tj;
+      int kc;
+      item_decode(a, it, tiles_all, tj, kc);
       const int64_t t = tj / a.n_tiles;
       const int j = (int)(tj % a.n_tiles);
       const int64_t n = t * BM + q * 32 + lane;
@@ -872,6 +889,7 @@ extern "C" int evo_bsc_tables_tc(const double *W, int64_t N, int D, int H, void 
   a.k_chunks = 1; a.kb_chunk = g.KB; a.accumulate = 0;
   a.descale = reinterpret_cast<const float *>(ws) + 4;
   a.B = B;
+  a.chunk_major = 0;
   EVO_CUDA(cudaFuncSetAttribute(dense::table_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)dense::T_SMEM_BYTES));
   int64_t tiles = (N + dense::BM - 1) / dense::BM * g.n_tiles;
@@ -973,6 +991,7 @@ static int wp_tc_finish(const uint32_t *states, const double *lpj, const float *
   a.kb_chunk = kb_chunk; a.k_chunks = (g.KB + kb_chunk - 1) / kb_chunk; a.accumulate = 1;
   a.descale = reinterpret_cast<const float *>(ws) + 4;
   a.B = stats;  // Wp [H][D] leads the statistics block
+  a.chunk_major = 1;
   EVO_CUDA(cudaFuncSetAttribute(dense::table_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)dense::T_SMEM_BYTES));
   const int64_t items = (int64_t)base_items * a.k_chunks;
