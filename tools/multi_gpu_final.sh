@@ -1,4 +1,4 @@
-tag=r04r
+tag=r05d
 python -m pytest -m gpu -q tests/test_multigpu_gpu.py 2>&1 | tail -3
 for n in 2 4 8; do [ -f gpurun_out/multigpu_parity_${n}gpu.log ] && cp gpurun_out/multigpu_parity_${n}gpu.log gpurun_out/${tag}_multigpu_parity_${n}gpu.log; done
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
