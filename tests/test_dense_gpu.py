@@ -323,9 +323,11 @@ def test_fused_statistics_equal_the_separate_pass(D, H, K, N, act, ea, perm):
         out[fuse] = (np.array(Fs), np.asarray(th["W"]), th["pi"], th["sigma"], cont["ss_dev"].cpu().numpy(), rest)
     a, b = out[True], out[False]
     assert np.array_equal(a[4], b[4])
-    assert np.max(np.abs(a[0] - b[0]) / np.abs(b[0])) < 1e-12
-    assert np.abs(a[1] - b[1]).max() < 1e-9 * np.abs(b[1]).max()
-    assert abs(a[2] - b[2]) < 1e-12 * b[2] and abs(a[3] - b[3]) < 1e-12 * b[3]
+    # same sums in another order of the f64 atomics (and the order varies from run to run): observed <= 1e-14 on F and
+    # <= 1e-11 on W; the bounds leave room for the solve's conditioning
+    assert np.max(np.abs(a[0] - b[0]) / np.abs(b[0])) < 1e-11
+    assert np.abs(a[1] - b[1]).max() < 1e-8 * np.abs(b[1]).max()
+    assert abs(a[2] - b[2]) < 1e-11 * b[2] and abs(a[3] - b[3]) < 1e-11 * b[3]
     if act == 24.0:
         assert 0 < a[5] < N, a[5]  # both routes took part
     elif act == 3.0:
